@@ -1,0 +1,1 @@
+// Test-infrastructure shim (oracle/_ref build only). Not product code.
