@@ -1,0 +1,904 @@
+// C ABI of libfsq_b200.so (include/fsq.h): contexts, device memory, and the orchestration of the kernels.
+// There is no CPU fallback anywhere in this file: every compute entry point launches the CUDA kernels or fails.
+#include "../../include/fsq.h"
+#include "fsq_internal.h"
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace fsq;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct phase_timer;
+
+} // namespace
+
+struct fsq_ctx
+{
+	int device{0};
+	cudaStream_t stream{nullptr};
+	cudaDeviceProp prop{};
+	std::string error;
+	std::map <std::string, int64_t> opts;
+	std::map <std::string, double> stats;
+	std::vector <std::pair <std::string, std::pair <cudaEvent_t, cudaEvent_t>>> pending;   // phase timers
+
+	int64_t opt(char const *k, int64_t dflt) const { auto it = opts.find(k); return opts.end() == it ? dflt : it->second; }
+};
+
+struct fsq_msa
+{
+	fsq_ctx *ctx{};
+	uint8_t *cols{};
+	uint64_t col_stride{};
+	uint32_t m{}, nsym{};
+	uint64_t n{}, col0{};
+};
+
+struct fsq_segmentation
+{
+	fsq_ctx *ctx{};
+	uint32_t m{};
+	uint64_t n{}, L{};
+	uint32_t K{};
+	std::vector <uint64_t> lb, rb;            // reduced
+	std::vector <uint32_t> size;
+	uint32_t *d_a{}, *d_d{};                  // reduced states on the device, count x m
+	std::vector <uint32_t> h_a, h_d;
+	std::vector <uint64_t> tb_lb, tb_rb;      // traceback before reduction
+	std::vector <uint32_t> tb_max, tb_size;
+	std::vector <uint32_t> dp_lb, dp_max, dp_size;   // keep_dp
+};
+
+struct fsq_summary
+{
+	fsq_ctx *ctx{};
+	uint32_t m{};
+	uint64_t first{}, last{};
+	uint32_t *pi{}, *delta{};
+};
+
+namespace {
+
+int fail(fsq_ctx *ctx, int code, char const *fmt, ...)
+{
+	char buf[512];
+	va_list ap;
+	va_start(ap, fmt);
+	vsnprintf(buf, sizeof buf, fmt, ap);
+	va_end(ap);
+	if (ctx) ctx->error = buf; else g_create_error = buf;
+	return code;
+}
+
+#define CK(call) do { cudaError_t e_ = (call); if (cudaSuccess != e_) return fail(ctx, FSQ_ERR_CUDA, "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while (0)
+
+// RAII device buffer
+struct dbuf
+{
+	void *p{nullptr};
+	~dbuf() { if (p) cudaFree(p); }
+	cudaError_t alloc(size_t bytes) { if (p) { cudaFree(p); p = nullptr; } return cudaMalloc(&p, bytes ? bytes : 16); }
+	template <typename T> T *as() const { return static_cast <T *>(p); }
+};
+
+struct phase
+{
+	fsq_ctx *ctx; std::string name; cudaEvent_t e0{}, e1{};
+	phase(fsq_ctx *c, char const *n): ctx(c), name(n)
+	{
+		cudaEventCreate(&e0); cudaEventCreate(&e1);
+		cudaEventRecord(e0, ctx->stream);
+	}
+	void stop()
+	{
+		cudaEventRecord(e1, ctx->stream);
+		ctx->pending.push_back({name, {e0, e1}});
+	}
+};
+
+void flush_phases(fsq_ctx *ctx)
+{
+	for (auto &p : ctx->pending)
+	{
+		float ms = 0;
+		cudaEventSynchronize(p.second.second);
+		cudaEventElapsedTime(&ms, p.second.first, p.second.second);
+		ctx->stats["ms_" + p.first] += ms;
+		cudaEventDestroy(p.second.first);
+		cudaEventDestroy(p.second.second);
+	}
+	ctx->pending.clear();
+}
+
+// The geometry of one scan: warps per block (column range), tiles per warp, columns per block.
+struct geometry
+{
+	uint32_t n_tiles, n_warps, tpw, C, cg, B;
+};
+
+geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
+{
+	geometry g;
+	uint32_t const m = msa->m;
+	g.n_tiles = (m + 31) / 32;
+	int64_t w = ctx->opt("warps", 0);
+	if (w <= 0)
+	{
+		w = 1;
+		while (w < 32 && (g.n_tiles + w - 1) / w > 16) w *= 2;
+	}
+	g.n_warps = (uint32_t) std::min <int64_t>(32, std::max <int64_t>(1, w));
+	g.tpw = (g.n_tiles + g.n_warps - 1) / g.n_warps;
+	while (g.tpw > 32 && g.n_warps < 32) { g.n_warps *= 2; g.tpw = (g.n_tiles + g.n_warps - 1) / g.n_warps; }
+
+	g.cg = (uint32_t) std::max <uint64_t>(1, 2048 / msa->col_stride);
+	int64_t C = ctx->opt("block_columns", 0);
+	if (C <= 0)
+	{
+		// enough blocks to fill every SM a few times over, but long enough to amortise the two extra passes' fixed costs
+		uint64_t const resident = (uint64_t) ctx->prop.multiProcessorCount * std::max <uint32_t>(1, std::min <uint32_t>(32, 2048 / (g.n_warps * 32)));
+		C = (int64_t) ((msa->n + resident - 1) / resident);
+		C = std::max <int64_t>(C, 64);
+		C = std::min <int64_t>(C, 4096);
+	}
+	C = std::min <int64_t>(C, 65534 - (int64_t) m - 2);
+	C = std::max <int64_t>(C, 1);
+	g.C = (uint32_t) C;
+	g.cg = std::min(g.cg, g.C);
+	g.B = (uint32_t) ((msa->n + g.C - 1) / g.C);
+	return g;
+}
+
+void fill_common(block_args &A, fsq_msa const *msa, geometry const &g)
+{
+	memset(&A, 0, sizeof A);
+	A.cols = msa->cols;
+	A.col_stride = msa->col_stride;
+	A.n_local = msa->n;
+	A.col0 = msa->col0;
+	A.m = msa->m;
+	A.n_tiles = g.n_tiles;
+	A.nsym = msa->nsym;
+	A.C = g.C;
+	A.cg = g.cg;
+}
+
+__global__ void iota_kernel(uint32_t *a, uint32_t *d, uint32_t m, uint32_t dval)
+{
+	uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < m) { a[i] = i; d[i] = dval; }
+}
+
+__global__ void gather_states_kernel(uint32_t const *src_a, uint32_t const *src_d, uint32_t const *index, uint32_t m, uint32_t *dst_a, uint32_t *dst_d)
+{
+	uint32_t const s = blockIdx.y;
+	uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i < m)
+	{
+		size_t const from = (size_t) index[s] * m + i, to = (size_t) s * m + i;
+		dst_a[to] = src_a[from];
+		dst_d[to] = src_d[from];
+	}
+}
+
+// Everything the scans share: local summaries, true block start states, their rank compression.
+struct scan_state
+{
+	geometry g;
+	dbuf sum_a, sum_d, st_a, st_d, code, oldvals, R, items;
+};
+
+// Pass A (local scans), stitch, rank compression.  After this, st_[ad] hold the exact PBWT state at every block start.
+int prepare_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
+{
+	S.g = choose_geometry(ctx, msa);
+	geometry const &g = S.g;
+	uint32_t const m = msa->m;
+	size_t const bm = (size_t) g.B * m;
+	CK(S.sum_a.alloc(bm * 4)); CK(S.sum_d.alloc(bm * 4));
+	CK(S.st_a.alloc(bm * 4)); CK(S.st_d.alloc(bm * 4));
+	CK(S.code.alloc(bm * 2)); CK(S.oldvals.alloc(bm * 4)); CK(S.R.alloc((size_t) g.B * 4));
+
+	iota_kernel <<<(m + 255) / 256, 256, 0, ctx->stream>>>(S.st_a.as <uint32_t>(), S.st_d.as <uint32_t>(), m, (uint32_t) msa->col0);
+	CK(cudaGetLastError());
+
+	if (g.B > 1)
+	{
+		phase pa(ctx, "pass_a");
+		block_args A;
+		fill_common(A, msa, g);
+		A.mode = MODE_LOCAL;
+		A.sum_a = S.sum_a.as <uint32_t>();
+		A.sum_d = S.sum_d.as <uint32_t>();
+		CK(launch_block(A, g.B - 1, g.n_warps, g.tpw, false, ctx->stream));
+		pa.stop();
+		ctx->stats["kernel_launches"] += 1;
+
+		phase ps(ctx, "stitch");
+		std::vector <stitch_item> items(g.B - 1);
+		for (uint32_t b = 0; b + 1 < g.B; ++b)
+		{
+			stitch_item &it = items[b];
+			memset(&it, 0, sizeof it);
+			it.in_a = S.st_a.as <uint32_t>() + (size_t) b * m;
+			it.in_d = S.st_d.as <uint32_t>() + (size_t) b * m;
+			it.pi = S.sum_a.as <uint32_t>() + (size_t) b * m;
+			it.delta = S.sum_d.as <uint32_t>() + (size_t) b * m;
+			it.out_a = S.st_a.as <uint32_t>() + (size_t) (b + 1) * m;
+			it.out_d = S.st_d.as <uint32_t>() + (size_t) (b + 1) * m;
+			it.s_mark = (uint32_t) (msa->col0 + (uint64_t) b * g.C);
+		}
+		CK(S.items.alloc(items.size() * sizeof(stitch_item)));
+		CK(cudaMemcpyAsync(S.items.p, items.data(), items.size() * sizeof(stitch_item), cudaMemcpyHostToDevice, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));     // items is a stack vector
+		stitch_args SA;
+		SA.items = S.items.as <stitch_item>();
+		SA.n_steps = g.B - 1;
+		SA.m = m;
+		SA.n_tiles = g.n_tiles;
+		CK(launch_stitch(SA, ctx->stream));
+		ps.stop();
+		ctx->stats["kernel_launches"] += 1;
+	}
+	{
+		phase pp(ctx, "prep");
+		CK(launch_prep(S.st_d.as <uint32_t>(), m, S.code.as <uint16_t>(), S.oldvals.as <uint32_t>(), S.R.as <uint32_t>(), 0, g.B, ctx->stream));
+		pp.stop();
+		ctx->stats["kernel_launches"] += 1;
+	}
+	return FSQ_OK;
+}
+
+// Pass C: (a_c, d_c) at the given ascending local columns c (1 <= c <= n) into dump_a / dump_d (count x m).
+int dump_states(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S, std::vector <uint64_t> const &columns, uint32_t *dump_a, uint32_t *dump_d)
+{
+	geometry const &g = S.g;
+	std::vector <uint32_t> begin(g.B + 1, 0), ids;
+	{
+		size_t i = 0;
+		for (uint32_t b = 0; b < g.B; ++b)
+		{
+			begin[b] = (uint32_t) i;
+			uint64_t const e = std::min <uint64_t>(msa->n, (uint64_t) (b + 1) * g.C);
+			while (i < columns.size() && columns[i] <= e) ++i;     // block b owns right bounds in (s, e]
+			if (i > begin[b]) ids.push_back(b);
+		}
+		begin[g.B] = (uint32_t) i;
+		if (i != columns.size())
+			return fail(ctx, FSQ_ERR_ARG, "state columns must be ascending and within [1, n]");
+	}
+	if (ids.empty()) return FSQ_OK;
+	dbuf d_cols, d_begin, d_ids;
+	CK(d_cols.alloc(columns.size() * 8)); CK(d_begin.alloc(begin.size() * 4)); CK(d_ids.alloc(ids.size() * 4));
+	CK(cudaMemcpyAsync(d_cols.p, columns.data(), columns.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(d_begin.p, begin.data(), begin.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(d_ids.p, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+	phase pc(ctx, "pass_c");
+	block_args A;
+	fill_common(A, msa, g);
+	A.mode = MODE_DUMP;
+	A.st_a = S.st_a.as <uint32_t>();
+	A.code = S.code.as <uint16_t>();
+	A.oldvals = S.oldvals.as <uint32_t>();
+	A.R = S.R.as <uint32_t>();
+	A.blk_ids = d_ids.as <uint32_t>();
+	A.dump_cols = d_cols.as <uint64_t>();
+	A.dump_begin = d_begin.as <uint32_t>();
+	A.dump_a = dump_a;
+	A.dump_d = dump_d;
+	CK(launch_block(A, (uint32_t) ids.size(), g.n_warps, g.tpw, false, ctx->stream));
+	pc.stop();
+	ctx->stats["kernel_launches"] += 1;
+	CK(cudaStreamSynchronize(ctx->stream));   // the three staging buffers die here
+	return FSQ_OK;
+}
+
+int check_shape(fsq_ctx *ctx, fsq_msa const *msa)
+{
+	if (!ctx || !msa) return fail(ctx, FSQ_ERR_ARG, "null context or alignment");
+	if (msa->ctx != ctx) return fail(ctx, FSQ_ERR_ARG, "alignment belongs to another context");
+	if (msa->m > 65000) return fail(ctx, FSQ_ERR_UNSUPPORTED, "m = %u rows: the scan kernels keep row ids and divergence codes in 16 bits (m <= 65000)", msa->m);
+	if (msa->col0 + msa->n >= (1ull << 31)) return fail(ctx, FSQ_ERR_UNSUPPORTED, "n = %llu columns: positions are kept in 32 bits (n < 2^31)", (unsigned long long) msa->n);
+	return FSQ_OK;
+}
+
+int new_msa(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint32_t nsym, fsq_msa **out)
+{
+	if (!ctx || !out) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	if (0 == m || 0 == n) return fail(ctx, FSQ_ERR_ARG, "empty alignment (m = %u, n = %llu)", m, (unsigned long long) n);
+	fsq_msa *msa = new (std::nothrow) fsq_msa;
+	if (!msa) return fail(ctx, FSQ_ERR_NOMEM, "out of host memory");
+	msa->ctx = ctx; msa->m = m; msa->n = n; msa->col0 = col0; msa->nsym = nsym;
+	msa->col_stride = (((uint64_t) m + 1) / 2 + 15) & ~15ull;
+	unsigned long long const bytes = msa->col_stride * n;
+	cudaError_t const e = cudaMalloc(&msa->cols, bytes);
+	if (cudaSuccess != e)
+	{
+		delete msa;
+		return fail(ctx, cudaErrorMemoryAllocation == e ? FSQ_ERR_NOMEM : FSQ_ERR_CUDA, "cudaMalloc of %llu bytes for the packed alignment: %s", bytes, cudaGetErrorString(e));
+	}
+	*out = msa;
+	return FSQ_OK;
+}
+
+} // namespace
+
+
+extern "C" {
+
+const char *fsq_version(void) { return "fsq_b200 0.1 (sm_100a)"; }
+
+int fsq_create(int device, fsq_ctx **out)
+{
+	if (!out) return fail(nullptr, FSQ_ERR_ARG, "null out pointer");
+	int count = 0;
+	cudaError_t e = cudaGetDeviceCount(&count);
+	if (cudaSuccess != e || 0 == count)
+		return fail(nullptr, FSQ_ERR_CUDA, "no CUDA device (%s); libfsq_b200 has no CPU fallback", cudaSuccess != e ? cudaGetErrorString(e) : "device count is 0");
+	if (device < 0 || device >= count) return fail(nullptr, FSQ_ERR_ARG, "device %d out of range [0, %d)", device, count);
+	fsq_ctx *ctx = new (std::nothrow) fsq_ctx;
+	if (!ctx) return fail(nullptr, FSQ_ERR_NOMEM, "out of host memory");
+	ctx->device = device;
+	if (cudaSuccess != (e = cudaSetDevice(device)) || cudaSuccess != (e = cudaGetDeviceProperties(&ctx->prop, device))
+		|| cudaSuccess != (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)))
+	{
+		delete ctx;
+		return fail(nullptr, FSQ_ERR_CUDA, "device %d: %s", device, cudaGetErrorString(e));
+	}
+	if (ctx->prop.major < 10)
+	{
+		int const major = ctx->prop.major, minor = ctx->prop.minor;
+		cudaStreamDestroy(ctx->stream);
+		delete ctx;
+		return fail(nullptr, FSQ_ERR_CUDA, "device %d is sm_%d%d; this library is built for sm_100a only", device, major, minor);
+	}
+	*out = ctx;
+	return FSQ_OK;
+}
+
+void fsq_destroy(fsq_ctx *ctx)
+{
+	if (!ctx) return;
+	cudaSetDevice(ctx->device);
+	flush_phases(ctx);
+	cudaStreamDestroy(ctx->stream);
+	delete ctx;
+}
+
+const char *fsq_last_error(const fsq_ctx *ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
+{
+	if (!ctx || !key) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", nullptr};
+	for (char const **k = known; *k; ++k)
+		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }
+	return fail(ctx, FSQ_ERR_ARG, "unknown option '%s'", key);
+}
+
+int fsq_get_stat(const fsq_ctx *cctx, const char *key, double *value)
+{
+	fsq_ctx *ctx = const_cast <fsq_ctx *>(cctx);
+	if (!ctx || !key || !value) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	cudaSetDevice(ctx->device);
+	flush_phases(ctx);
+	if (0 == strcmp(key, "reset")) { ctx->stats.clear(); *value = 0; return FSQ_OK; }
+	auto it = ctx->stats.find(key);
+	*value = ctx->stats.end() == it ? 0.0 : it->second;
+	return FSQ_OK;
+}
+
+// ---- alignment ---------------------------------------------------------------------------------------------------
+
+static int comp_nsym(fsq_ctx *ctx, uint8_t const comp[256], uint32_t *nsym)
+{
+	uint32_t mx = 0;
+	for (int c = 0; c < 256; ++c) mx = std::max <uint32_t>(mx, comp[c]);
+	if (mx >= FSQ_MAX_SYMS)
+		return fail(ctx, FSQ_ERR_ARG, "alphabet has %u comps; at most 15 distinct characters (plus NUL) fit the 4-bit packing", mx + 1);
+	*nsym = mx + 1;
+	return FSQ_OK;
+}
+
+int fsq_msa_from_device_rows(fsq_ctx *ctx, const uint8_t *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, const uint8_t comp[256], fsq_msa **out)
+{
+	if (!ctx || !d_rows || !comp || !out) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	CK(cudaSetDevice(ctx->device));
+	uint32_t nsym = 0;
+	int rc = comp_nsym(ctx, comp, &nsym);
+	if (rc) return rc;
+	fsq_msa *msa = nullptr;
+	if ((rc = new_msa(ctx, m, n, 0, nsym, &msa))) return rc;
+	dbuf d_comp;
+	cudaError_t e = d_comp.alloc(256);
+	if (cudaSuccess == e) e = cudaMemcpyAsync(d_comp.p, comp, 256, cudaMemcpyHostToDevice, ctx->stream);
+	if (cudaSuccess == e)
+	{
+		phase pk(ctx, "pack");
+		e = launch_pack(d_rows, row_stride, m, n, d_comp.as <uint8_t>(), msa->cols, msa->col_stride, 0, ctx->stream);
+		pk.stop();
+		ctx->stats["kernel_launches"] += 1;
+	}
+	if (cudaSuccess == e) e = cudaStreamSynchronize(ctx->stream);
+	if (cudaSuccess != e) { fsq_msa_free(msa); return fail(ctx, FSQ_ERR_CUDA, "pack: %s", cudaGetErrorString(e)); }
+	*out = msa;
+	return FSQ_OK;
+}
+
+int fsq_msa_from_rows(fsq_ctx *ctx, const uint8_t *const *rows, uint32_t m, uint64_t n, const uint8_t comp_in[256], fsq_msa **out)
+{
+	if (!ctx || !rows || !out) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	if (0 == m || 0 == n) return fail(ctx, FSQ_ERR_ARG, "empty alignment (m = %u, n = %llu)", m, (unsigned long long) n);
+	CK(cudaSetDevice(ctx->device));
+	uint8_t comp[256];
+	if (comp_in)
+		memcpy(comp, comp_in, 256);
+	else
+	{
+		// lib/libbio/include/libbio/consecutive_alphabet.hh:259-264, 309-326: NUL = 0, bytes present get 1.. in byte order
+		bool seen[256] = {false};
+		for (uint32_t r = 0; r < m; ++r)
+			for (uint64_t c = 0; c < n; ++c) seen[rows[r][c]] = true;
+		seen[0] = true;
+		uint32_t next = 0;
+		for (int c = 0; c < 256; ++c) comp[c] = seen[c] ? (uint8_t) std::min <uint32_t>(255, next++) : 0;
+	}
+	uint32_t nsym = 0;
+	int rc = comp_nsym(ctx, comp, &nsym);
+	if (rc) return rc;
+	fsq_msa *msa = nullptr;
+	if ((rc = new_msa(ctx, m, n, 0, nsym, &msa))) return rc;
+
+	// Rows go up in column chunks through a device staging matrix (row-major, m x chunk), then get packed.
+	uint64_t const chunk = std::max <uint64_t>(32, std::min <uint64_t>(n, ((256ull << 20) / m) & ~31ull));
+	uint64_t const row_stride = (chunk + 15) & ~15ull;
+	dbuf stage, d_comp;
+	cudaError_t e = stage.alloc((size_t) m * row_stride);
+	if (cudaSuccess == e) e = d_comp.alloc(256);
+	if (cudaSuccess == e) e = cudaMemcpyAsync(d_comp.p, comp, 256, cudaMemcpyHostToDevice, ctx->stream);
+	phase pk(ctx, "h2d_pack");
+	for (uint64_t c0 = 0; c0 < n && cudaSuccess == e; c0 += chunk)
+	{
+		uint64_t const nc = std::min(chunk, n - c0);
+		// one strided copy when the rows are equally spaced in host memory, else one copy per row
+		bool strided = m > 1;
+		ptrdiff_t const pitch = m > 1 ? rows[1] - rows[0] : 0;
+		for (uint32_t r = 1; r + 1 < m && strided; ++r) strided = (rows[r + 1] - rows[r]) == pitch;
+		if (strided && pitch >= (ptrdiff_t) n)
+			e = cudaMemcpy2DAsync(stage.p, row_stride, rows[0] + c0, (size_t) pitch, nc, m, cudaMemcpyHostToDevice, ctx->stream);
+		else
+			for (uint32_t r = 0; r < m && cudaSuccess == e; ++r)
+				e = cudaMemcpyAsync(stage.as <uint8_t>() + (size_t) r * row_stride, rows[r] + c0, nc, cudaMemcpyHostToDevice, ctx->stream);
+		if (cudaSuccess == e) e = launch_pack(stage.as <uint8_t>(), row_stride, m, nc, d_comp.as <uint8_t>(), msa->cols, msa->col_stride, c0, ctx->stream);
+		ctx->stats["kernel_launches"] += 1;
+	}
+	pk.stop();
+	if (cudaSuccess == e) e = cudaStreamSynchronize(ctx->stream);
+	if (cudaSuccess != e) { fsq_msa_free(msa); return fail(ctx, FSQ_ERR_CUDA, "upload/pack: %s", cudaGetErrorString(e)); }
+	*out = msa;
+	return FSQ_OK;
+}
+
+int fsq_msa_synth(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps, fsq_msa **out)
+{
+	if (!ctx || !out || 0 == founders) return fail(ctx, FSQ_ERR_ARG, "null argument or zero founders");
+	CK(cudaSetDevice(ctx->device));
+	fsq_msa *msa = nullptr;
+	int rc = new_msa(ctx, m, n, col0, gaps ? 6 : 5, &msa);
+	if (rc) return rc;
+	cudaError_t e = launch_synth_packed(msa->cols, msa->col_stride, m, n, col0, seed, founders, gaps, ctx->stream);
+	if (cudaSuccess == e) e = cudaStreamSynchronize(ctx->stream);
+	if (cudaSuccess != e) { fsq_msa_free(msa); return fail(ctx, FSQ_ERR_CUDA, "synth: %s", cudaGetErrorString(e)); }
+	ctx->stats["kernel_launches"] += 1;
+	*out = msa;
+	return FSQ_OK;
+}
+
+int fsq_synth_rows_device(fsq_ctx *ctx, uint8_t *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps)
+{
+	if (!ctx || !d_rows || 0 == founders || 0 == m || 0 == n) return fail(ctx, FSQ_ERR_ARG, "bad argument");
+	CK(cudaSetDevice(ctx->device));
+	CK(launch_synth_rows(d_rows, row_stride, m, n, col0, seed, founders, gaps, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	return FSQ_OK;
+}
+
+void fsq_msa_free(fsq_msa *msa)
+{
+	if (!msa) return;
+	if (msa->ctx) cudaSetDevice(msa->ctx->device);
+	cudaFree(msa->cols);
+	delete msa;
+}
+
+uint32_t fsq_msa_rows(const fsq_msa *msa) { return msa ? msa->m : 0; }
+uint64_t fsq_msa_columns(const fsq_msa *msa) { return msa ? msa->n : 0; }
+
+// ---- PBWT states ---------------------------------------------------------------------------------------------------
+
+int fsq_pbwt_states(fsq_ctx *ctx, const fsq_msa *msa, const uint64_t *columns, uint32_t count, uint32_t *a, uint32_t *d)
+{
+	int rc = check_shape(ctx, msa);
+	if (rc) return rc;
+	if (!columns || !a || !d) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	if (0 == count) return FSQ_OK;
+	CK(cudaSetDevice(ctx->device));
+	std::vector <uint64_t> cols(columns, columns + count);
+	for (uint32_t i = 0; i < count; ++i)
+		if (cols[i] < 1 || cols[i] > msa->n || (i && cols[i] <= cols[i - 1]))
+			return fail(ctx, FSQ_ERR_ARG, "state columns must be strictly ascending and within [1, n]");
+	scan_state S;
+	if ((rc = prepare_scan(ctx, msa, S))) return rc;
+	dbuf da, dd;
+	size_t const bytes = (size_t) count * msa->m * 4;
+	CK(da.alloc(bytes)); CK(dd.alloc(bytes));
+	if ((rc = dump_states(ctx, msa, S, cols, da.as <uint32_t>(), dd.as <uint32_t>()))) return rc;
+	CK(cudaMemcpyAsync(a, da.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(d, dd.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	return FSQ_OK;
+}
+
+// ---- long path -----------------------------------------------------------------------------------------------------
+
+int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation **out)
+{
+	int rc = check_shape(ctx, msa);
+	if (rc) return rc;
+	if (!out) return fail(ctx, FSQ_ERR_ARG, "null out pointer");
+	if (0 == L) return fail(ctx, FSQ_ERR_ARG, "segment length bound must be positive");
+	if (0 != msa->col0) return fail(ctx, FSQ_ERR_ARG, "fsq_segment needs an alignment that starts at column 0");
+	uint64_t const n = msa->n;
+	uint32_t const m = msa->m;
+	if (n < 2 * L) return fail(ctx, FSQ_ERR_SHORT, "n = %llu < 2L = %llu: short path", (unsigned long long) n, (unsigned long long) (2 * L));
+	CK(cudaSetDevice(ctx->device));
+
+	scan_state S;
+	if ((rc = prepare_scan(ctx, msa, S))) return rc;
+	geometry const &g = S.g;
+
+	// ---- pass B + DP; the top-list bound grows until the DP proves the result exact ----
+	uint64_t const dp_size = n - L + 1;
+	uint32_t const n_blk = (uint32_t) (dp_size / 64 + 1);
+	uint32_t n_levels = 1;
+	while ((1ull << n_levels) <= n_blk) ++n_levels;
+	dbuf tb_max, tb_lb, tb_size, lev, overflow, cnt, h0, toplist;
+	CK(tb_max.alloc(dp_size * 4)); CK(tb_lb.alloc(dp_size * 4)); CK(tb_size.alloc(dp_size * 4));
+	CK(lev.alloc((size_t) n_levels * n_blk * 4)); CK(overflow.alloc(4));
+	CK(cnt.alloc(n * 4)); CK(h0.alloc(n * 4));
+	uint32_t cap = (uint32_t) std::min <int64_t>(m, std::max <int64_t>(1, ctx->opt("cap", 63)));
+	while (true)
+	{
+		CK(toplist.alloc((size_t) n * (cap + 1) * sizeof(uint2)));
+		CK(cudaMemsetAsync(tb_max.p, 0xff, dp_size * 4, ctx->stream));
+		CK(cudaMemsetAsync(tb_size.p, 0xff, dp_size * 4, ctx->stream));
+		CK(cudaMemsetAsync(tb_lb.p, 0, dp_size * 4, ctx->stream));
+		CK(cudaMemsetAsync(overflow.p, 0, 4, ctx->stream));
+		{
+			phase pb(ctx, "pass_b");
+			block_args A;
+			fill_common(A, msa, g);
+			A.mode = MODE_EXACT;
+			A.st_a = S.st_a.as <uint32_t>();
+			A.code = S.code.as <uint16_t>();
+			A.oldvals = S.oldvals.as <uint32_t>();
+			A.R = S.R.as <uint32_t>();
+			A.toplist = toplist.as <uint2>();
+			A.cap = cap;
+			A.cnt = cnt.as <uint32_t>();
+			A.h0 = h0.as <uint32_t>();
+			CK(launch_block(A, g.B, g.n_warps, g.tpw, true, ctx->stream));
+			pb.stop();
+			ctx->stats["kernel_launches"] += 1;
+		}
+		{
+			phase pd(ctx, "dp");
+			dp_args D;
+			memset(&D, 0, sizeof D);
+			D.m = m; D.n = n; D.L = L;
+			D.toplist = toplist.as <uint2>(); D.cap = cap; D.cnt = cnt.as <uint32_t>(); D.h0 = h0.as <uint32_t>();
+			D.tb_max = tb_max.as <uint32_t>(); D.tb_lb = tb_lb.as <uint32_t>(); D.tb_size = tb_size.as <uint32_t>();
+			D.lev = lev.as <uint32_t>(); D.n_blk = n_blk; D.n_levels = n_levels;
+			D.overflow = overflow.as <uint32_t>();
+			CK(launch_dp(D, ctx->stream));
+			pd.stop();
+			ctx->stats["kernel_launches"] += 1;
+		}
+		uint32_t ovf = 0;
+		CK(cudaMemcpyAsync(&ovf, overflow.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));
+		if (0 == ovf) break;
+		if (cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list at column %u with cap = m", ovf - 1);
+		cap = (uint32_t) std::min <uint64_t>(m, (uint64_t) cap * 4);
+		ctx->stats["cap_retries"] += 1;
+	}
+	ctx->stats["cap"] = cap;
+	ctx->stats["block_columns"] = g.C;
+	ctx->stats["blocks"] = g.B;
+	ctx->stats["warps"] = g.n_warps;
+
+	// ---- traceback (reference: segmentation_lp_context.cc:191-224) ----
+	fsq_segmentation *seg = new (std::nothrow) fsq_segmentation;
+	if (!seg) return fail(ctx, FSQ_ERR_NOMEM, "out of host memory");
+	struct guard { fsq_segmentation *&s; bool ok{false}; ~guard() { if (!ok) { fsq_segmentation_free(s); s = nullptr; } } } gd{seg};
+	seg->ctx = ctx; seg->m = m; seg->n = n; seg->L = L;
+	{
+		phase pt(ctx, "traceback");
+		std::vector <uint32_t> h_lb(dp_size), h_max(dp_size), h_size(dp_size);
+		CK(cudaMemcpyAsync(h_lb.data(), tb_lb.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_max.data(), tb_max.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_size.data(), tb_size.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));
+		uint64_t idx = dp_size - 1;
+		while (true)
+		{
+			seg->tb_lb.push_back(h_lb[idx]);
+			seg->tb_rb.push_back(idx + L);
+			seg->tb_max.push_back(h_max[idx]);
+			seg->tb_size.push_back(h_size[idx]);
+			if (0 == h_lb[idx]) break;
+			idx = h_lb[idx] - L;
+		}
+		std::reverse(seg->tb_lb.begin(), seg->tb_lb.end());
+		std::reverse(seg->tb_rb.begin(), seg->tb_rb.end());
+		std::reverse(seg->tb_max.begin(), seg->tb_max.end());
+		std::reverse(seg->tb_size.begin(), seg->tb_size.end());
+		seg->K = seg->tb_max.back();
+		if (ctx->opt("keep_dp", 0))
+		{
+			seg->dp_lb.swap(h_lb); seg->dp_max.swap(h_max); seg->dp_size.swap(h_size);
+		}
+		pt.stop();
+	}
+	if (!(seg->K < m))
+	{
+		// generate_context.cc:192-200; the traceback stays available through the handle for inspection
+		gd.ok = true;
+		*out = seg;
+		return fail(ctx, FSQ_ERR_NOT_REDUCIBLE, "the maximum segment size %u is equal to the number of input sequences", seg->K);
+	}
+
+	// ---- pass C: states at the traceback right bounds (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35) ----
+	uint32_t const T = (uint32_t) seg->tb_rb.size();
+	dbuf st_a, st_d;
+	CK(st_a.alloc((size_t) T * m * 4)); CK(st_d.alloc((size_t) T * m * 4));
+	if ((rc = dump_states(ctx, msa, S, seg->tb_rb, st_a.as <uint32_t>(), st_d.as <uint32_t>()))) return rc;
+
+	// ---- greedy reduction (segmentation_lp_context.cc:335-390) ----
+	std::vector <uint32_t> chosen;
+	{
+		phase pr(ctx, "reduce");
+		dbuf d_rb, d_sz, d_next, d_nsize;
+		CK(d_rb.alloc((size_t) T * 8)); CK(d_sz.alloc((size_t) T * 4)); CK(d_next.alloc((size_t) T * 4)); CK(d_nsize.alloc((size_t) T * 4));
+		CK(cudaMemcpyAsync(d_rb.p, seg->tb_rb.data(), (size_t) T * 8, cudaMemcpyHostToDevice, ctx->stream));
+		CK(cudaMemcpyAsync(d_sz.p, seg->tb_size.data(), (size_t) T * 4, cudaMemcpyHostToDevice, ctx->stream));
+		reduce_args Rg;
+		Rg.m = m; Rg.T = T; Rg.K = seg->K;
+		Rg.tb_rb = d_rb.as <uint64_t>(); Rg.tb_size = d_sz.as <uint32_t>(); Rg.st_d = st_d.as <uint32_t>();
+		Rg.next = d_next.as <uint32_t>(); Rg.next_size = d_nsize.as <uint32_t>();
+		CK(launch_reduce(Rg, ctx->stream));
+		ctx->stats["kernel_launches"] += 1;
+		std::vector <uint32_t> nxt(T), nsz(T);
+		CK(cudaMemcpyAsync(nxt.data(), d_next.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(nsz.data(), d_nsize.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));
+		uint64_t cur_lb = 0;
+		for (uint32_t u = 0; u < T; )
+		{
+			uint32_t const last = nxt[u];
+			seg->lb.push_back(cur_lb);
+			seg->rb.push_back(seg->tb_rb[last]);
+			seg->size.push_back(nsz[u]);
+			chosen.push_back(last);
+			cur_lb = seg->tb_rb[last];
+			u = last + 1;
+		}
+		pr.stop();
+	}
+
+	// ---- the reduced samples: device copy for the follow-on kernels, host copy for the joiners ----
+	{
+		phase pg(ctx, "gather_d2h");
+		uint32_t const cntS = (uint32_t) chosen.size();
+		dbuf d_idx;
+		CK(d_idx.alloc((size_t) cntS * 4));
+		CK(cudaMemcpyAsync(d_idx.p, chosen.data(), (size_t) cntS * 4, cudaMemcpyHostToDevice, ctx->stream));
+		CK(cudaMalloc(&seg->d_a, (size_t) cntS * m * 4));
+		CK(cudaMalloc(&seg->d_d, (size_t) cntS * m * 4));
+		dim3 const grid((m + 255) / 256, cntS);
+		gather_states_kernel <<<grid, 256, 0, ctx->stream>>>(st_a.as <uint32_t>(), st_d.as <uint32_t>(), d_idx.as <uint32_t>(), m, seg->d_a, seg->d_d);
+		CK(cudaGetLastError());
+		ctx->stats["kernel_launches"] += 1;
+		seg->h_a.resize((size_t) cntS * m);
+		seg->h_d.resize((size_t) cntS * m);
+		CK(cudaMemcpyAsync(seg->h_a.data(), seg->d_a, (size_t) cntS * m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(seg->h_d.data(), seg->d_d, (size_t) cntS * m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		pg.stop();
+		CK(cudaStreamSynchronize(ctx->stream));
+	}
+	gd.ok = true;
+	*out = seg;
+	return FSQ_OK;
+}
+
+void fsq_segmentation_free(fsq_segmentation *seg)
+{
+	if (!seg) return;
+	if (seg->ctx) cudaSetDevice(seg->ctx->device);
+	cudaFree(seg->d_a);
+	cudaFree(seg->d_d);
+	delete seg;
+}
+
+uint32_t fsq_segmentation_count(const fsq_segmentation *seg) { return seg ? (uint32_t) seg->lb.size() : 0; }
+uint32_t fsq_segmentation_max_segment_size(const fsq_segmentation *seg) { return seg ? seg->K : 0; }
+
+int fsq_segmentation_bounds(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *size)
+{
+	if (!seg || !lb || !rb || !size) return FSQ_ERR_ARG;
+	std::copy(seg->lb.begin(), seg->lb.end(), lb);
+	std::copy(seg->rb.begin(), seg->rb.end(), rb);
+	std::copy(seg->size.begin(), seg->size.end(), size);
+	return FSQ_OK;
+}
+
+int fsq_segmentation_states(const fsq_segmentation *seg, uint32_t *a, uint32_t *d)
+{
+	if (!seg || !a || !d) return FSQ_ERR_ARG;
+	std::copy(seg->h_a.begin(), seg->h_a.end(), a);
+	std::copy(seg->h_d.begin(), seg->h_d.end(), d);
+	return FSQ_OK;
+}
+
+uint32_t fsq_segmentation_traceback_count(const fsq_segmentation *seg) { return seg ? (uint32_t) seg->tb_rb.size() : 0; }
+
+int fsq_segmentation_traceback(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
+{
+	if (!seg || !lb || !rb || !max_size || !size) return FSQ_ERR_ARG;
+	std::copy(seg->tb_lb.begin(), seg->tb_lb.end(), lb);
+	std::copy(seg->tb_rb.begin(), seg->tb_rb.end(), rb);
+	std::copy(seg->tb_max.begin(), seg->tb_max.end(), max_size);
+	std::copy(seg->tb_size.begin(), seg->tb_size.end(), size);
+	return FSQ_OK;
+}
+
+int fsq_segmentation_dp_table(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
+{
+	if (!seg || !lb || !rb || !max_size || !size) return FSQ_ERR_ARG;
+	if (seg->dp_lb.empty())
+		return fail(seg->ctx, FSQ_ERR_ARG, "the DP table was not kept; set option keep_dp = 1 before fsq_segment");
+	for (size_t t = 0; t < seg->dp_lb.size(); ++t)
+	{
+		bool const written = 0xffffffffu != seg->dp_max[t];
+		lb[t] = seg->dp_lb[t];
+		rb[t] = written ? t + seg->L : 0;
+		max_size[t] = seg->dp_max[t];
+		size[t] = seg->dp_size[t];
+	}
+	return FSQ_OK;
+}
+
+// ---- short path ----------------------------------------------------------------------------------------------------
+
+static int sets_on_device(fsq_ctx *ctx, uint32_t const *d_a, uint32_t const *d_d, uint32_t m, uint64_t lb, dbuf &off, dbuf &ids, dbuf &cls, dbuf &nruns)
+{
+	CK(off.alloc(((size_t) m + 1) * 4)); CK(ids.alloc((size_t) m * 4)); CK(cls.alloc((size_t) m * 4)); CK(nruns.alloc(4));
+	CK(launch_segment_sets(d_a, d_d, m, lb, off.as <uint32_t>(), ids.as <uint32_t>(), cls.as <uint32_t>(), nruns.as <uint32_t>(), ctx->stream));
+	ctx->stats["kernel_launches"] += 1;
+	return FSQ_OK;
+}
+
+int fsq_distinct_rows(fsq_ctx *ctx, const fsq_msa *msa, uint32_t *row_of_run, uint32_t *run_len, uint32_t *count)
+{
+	int rc = check_shape(ctx, msa);
+	if (rc) return rc;
+	if (!row_of_run || !run_len || !count) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	CK(cudaSetDevice(ctx->device));
+	uint32_t const m = msa->m;
+	scan_state S;
+	if ((rc = prepare_scan(ctx, msa, S))) return rc;
+	dbuf da, dd, off, ids, cls, nruns;
+	CK(da.alloc((size_t) m * 4)); CK(dd.alloc((size_t) m * 4));
+	std::vector <uint64_t> cols(1, msa->n);
+	if ((rc = dump_states(ctx, msa, S, cols, da.as <uint32_t>(), dd.as <uint32_t>()))) return rc;
+	if ((rc = sets_on_device(ctx, da.as <uint32_t>(), dd.as <uint32_t>(), m, 0, off, ids, cls, nruns))) return rc;
+	std::vector <uint32_t> h_off(m + 1), h_a(m);
+	uint32_t runs = 0;
+	CK(cudaMemcpyAsync(h_off.data(), off.p, ((size_t) m + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(h_a.data(), da.p, (size_t) m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(&runs, nruns.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	for (uint32_t r = 0; r < runs; ++r)
+	{
+		row_of_run[r] = h_a[h_off[r]];
+		run_len[r] = h_off[r + 1] - h_off[r];
+	}
+	*count = runs;
+	return FSQ_OK;
+}
+
+// ---- segment sets, edge weights ---------------------------------------------------------------------------------------
+
+int fsq_segment_sets(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, uint32_t *run_off, uint32_t *ids_out, uint32_t *class_of_row, uint32_t *n_runs)
+{
+	if (!ctx || !seg || !run_off || !ids_out || !class_of_row || !n_runs) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	if (s >= seg->lb.size()) return fail(ctx, FSQ_ERR_ARG, "segment %u out of range", s);
+	CK(cudaSetDevice(ctx->device));
+	uint32_t const m = seg->m;
+	dbuf off, ids, cls, nruns;
+	int rc = sets_on_device(ctx, seg->d_a + (size_t) s * m, seg->d_d + (size_t) s * m, m, seg->lb[s], off, ids, cls, nruns);
+	if (rc) return rc;
+	uint32_t runs = 0;
+	CK(cudaMemcpyAsync(&runs, nruns.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(ids_out, ids.p, (size_t) m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(class_of_row, cls.p, (size_t) m * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaMemcpyAsync(run_off, off.p, ((size_t) runs + 1) * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	*n_runs = runs;
+	return FSQ_OK;
+}
+
+int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, int32_t *W, uint32_t *runs_lhs, uint32_t *runs_rhs)
+{
+	if (!ctx || !seg || !W || !runs_lhs || !runs_rhs) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	if ((size_t) s + 1 >= seg->lb.size()) return fail(ctx, FSQ_ERR_ARG, "segment pair %u out of range", s);
+	CK(cudaSetDevice(ctx->device));
+	uint32_t const m = seg->m;
+	dbuf off_l, ids_l, cls_l, n_l, off_r, ids_r, cls_r, n_r, dW;
+	int rc;
+	if ((rc = sets_on_device(ctx, seg->d_a + (size_t) s * m, seg->d_d + (size_t) s * m, m, seg->lb[s], off_l, ids_l, cls_l, n_l))) return rc;
+	if ((rc = sets_on_device(ctx, seg->d_a + (size_t) (s + 1) * m, seg->d_d + (size_t) (s + 1) * m, m, seg->lb[s + 1], off_r, ids_r, cls_r, n_r))) return rc;
+	uint32_t rl = 0, rr = 0;
+	CK(cudaMemcpyAsync(&rl, n_l.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(&rr, n_r.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	size_t const bytes = (size_t) rl * rr * 4;
+	CK(dW.alloc(bytes));
+	CK(cudaMemsetAsync(dW.p, 0, bytes, ctx->stream));
+	CK(launch_pair_weights(cls_l.as <uint32_t>(), cls_r.as <uint32_t>(), m, rr, dW.as <int32_t>(), ctx->stream));
+	ctx->stats["kernel_launches"] += 1;
+	CK(cudaMemcpyAsync(W, dW.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	*runs_lhs = rl;
+	*runs_rhs = rr;
+	return FSQ_OK;
+}
+
+// ---- column-sharded operation -------------------------------------------------------------------------------------------
+
+int fsq_local_summary(fsq_ctx *ctx, const fsq_msa *msa, uint64_t first_column, fsq_summary **out)
+{
+	(void) first_column;
+	if (!ctx || !msa || !out) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	return fail(ctx, FSQ_ERR_UNSUPPORTED, "column-sharded operation is not built yet");
+}
+
+void fsq_summary_free(fsq_summary *s)
+{
+	if (!s) return;
+	cudaFree(s->pi);
+	cudaFree(s->delta);
+	delete s;
+}
+
+uint32_t *fsq_summary_device_pi(fsq_summary *s) { return s ? s->pi : nullptr; }
+uint32_t *fsq_summary_device_delta(fsq_summary *s) { return s ? s->delta : nullptr; }
+
+int fsq_apply_summary(fsq_ctx *ctx, const fsq_summary *s, uint32_t *d_a, uint32_t *d_d)
+{
+	(void) s; (void) d_a; (void) d_d;
+	return fail(ctx, FSQ_ERR_UNSUPPORTED, "column-sharded operation is not built yet");
+}
+
+} // extern "C"

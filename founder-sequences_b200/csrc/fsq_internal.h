@@ -1,0 +1,110 @@
+// Internal declarations shared by the translation units of libfsq_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#ifndef FSQ_MAX_SYMS
+#define FSQ_MAX_SYMS 16            // 4-bit packed symbols
+#endif
+
+namespace fsq {
+
+enum { MODE_LOCAL = 0, MODE_EXACT = 1, MODE_DUMP = 2 };
+
+// One launch of the column-block scan kernel.  Local column index k <-> global position col0 + k.
+struct block_args
+{
+	uint8_t const *cols;       // packed alignment, column-major, col_stride bytes per column
+	uint64_t col_stride;
+	uint64_t n_local;          // columns held
+	uint64_t col0;             // global index of local column 0
+	uint32_t m, n_tiles, nsym;
+	uint32_t C;                // columns per block
+	uint32_t cg;               // columns per TMA stage
+	uint32_t first_block;
+	int mode;
+
+	// start states (MODE_EXACT, MODE_DUMP)
+	uint32_t const *st_a;      // [B][m]
+	uint16_t const *code;      // [B][m] rank-compressed divergences
+	uint32_t const *oldvals;   // [B][m] code -> value
+	uint32_t const *R;         // [B] number of distinct start values
+
+	// MODE_LOCAL output: state at the block end, started from identity
+	uint32_t *sum_a, *sum_d;   // [B][m]
+
+	// MODE_EXACT output, per local column
+	uint2 *toplist;            // [(cap + 1) entries per column] (v, #{d > v}), v descending
+	uint32_t cap;
+	uint32_t *cnt;             // entries | complete << 31
+	uint32_t *h0;              // #{d == 0}
+
+	// MODE_DUMP
+	uint32_t const *blk_ids;
+	uint64_t const *dump_cols; // ascending local right bounds
+	uint32_t const *dump_begin;// [B + 1]
+	uint32_t *dump_a, *dump_d; // [n_dumps][m]
+};
+
+size_t block_smem_bytes(block_args const &A, uint32_t n_warps, bool hist);
+cudaError_t launch_block(block_args const &A, uint32_t n_blocks, uint32_t n_warps, uint32_t tpw, bool hist, cudaStream_t st);
+cudaError_t launch_prep(uint32_t const *st_d, uint32_t m, uint16_t *code, uint32_t *oldvals, uint32_t *R, uint32_t first_block, uint32_t n_blocks, cudaStream_t st);
+
+struct stitch_item
+{
+	uint32_t const *in_a, *in_d;   // incoming state at s
+	uint32_t const *pi, *delta;    // local summary of [s, e)
+	uint32_t *out_a, *out_d;       // state at e
+	uint32_t s_mark;               // delta <= s_mark: identical to the predecessor over [s, e)
+	uint32_t identity_in;          // incoming state is (identity, identity_d)
+	uint32_t identity_d;
+	uint32_t pad;
+};
+
+struct stitch_args
+{
+	stitch_item const *items;      // device array, executed in order by one CTA
+	uint32_t n_steps;
+	uint32_t m, n_tiles;
+};
+
+size_t stitch_smem_bytes(uint32_t m, uint32_t n_warps);
+cudaError_t launch_stitch(stitch_args const &A, cudaStream_t st);
+
+// ---- DP ------------------------------------------------------------------------------------------------------
+struct dp_args
+{
+	uint32_t m;
+	uint64_t n;                 // columns (global == local for one GPU)
+	uint64_t L;
+	uint2 const *toplist; uint32_t cap; uint32_t const *cnt; uint32_t const *h0;
+	uint32_t *tb_max, *tb_lb, *tb_size;   // [n - L + 1]
+	uint32_t *lev;              // [n_levels][n_blk] rmq tables
+	uint32_t n_blk, n_levels;
+	uint32_t *overflow;         // set to 1 + column when the top list was too short to be exact
+};
+
+cudaError_t launch_dp(dp_args const &A, cudaStream_t st);
+
+// next[j] / size for the greedy reduction; see fsq_dp.cu
+struct reduce_args
+{
+	uint32_t m, T, K;
+	uint64_t const *tb_rb;       // [T] right bounds of the traceback
+	uint32_t const *tb_size;     // [T]
+	uint32_t const *st_d;        // [T][m] d at every right bound
+	uint32_t *next;              // [T + 1]: entry j + 1 is for cur_lb = rb[j]; entry 0 for cur_lb = 0
+	uint32_t *next_size;         // [T + 1]
+};
+cudaError_t launch_reduce(reduce_args const &A, cudaStream_t st);
+
+cudaError_t launch_segment_sets(uint32_t const *a, uint32_t const *d, uint32_t m, uint64_t lb, uint32_t *run_off, uint32_t *ids, uint32_t *class_of_row, uint32_t *n_runs, cudaStream_t st);
+cudaError_t launch_pair_weights(uint32_t const *cls_l, uint32_t const *cls_r, uint32_t m, uint32_t runs_r, int32_t *W, cudaStream_t st);
+
+// ---- pack / synth ----------------------------------------------------------------------------------------------
+cudaError_t launch_pack(uint8_t const *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint8_t const *d_comp, uint8_t *cols, uint64_t col_stride, uint64_t col_first, cudaStream_t st);
+cudaError_t launch_synth_packed(uint8_t *cols, uint64_t col_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps, cudaStream_t st);
+cudaError_t launch_synth_rows(uint8_t *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps, cudaStream_t st);
+
+} // namespace fsq

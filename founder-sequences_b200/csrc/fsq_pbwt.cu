@@ -1,0 +1,407 @@
+// PBWT column-block kernels (sm_100a): local scan (pass A), exact scan with divergence histogram and
+// per-column top lists (pass B), re-scan to requested columns (pass C), rank compression of a block's
+// start state, and the boundary stitch.  See DESIGN.md for the scheme and fsq_step.cuh for the column step.
+#include "fsq_internal.h"
+#include "fsq_step.cuh"
+
+namespace fsq {
+
+// ---- column symbols: TMA-staged, 4-bit packed ---------------------------------------------------------------
+struct nibble_source
+{
+	uint32_t const *col;   // one packed column in shared memory
+	__device__ __forceinline__ uint32_t operator()(uint32_t x) const
+	{
+		return (col[x >> 3] >> ((x & 7u) * 4u)) & 15u;
+	}
+};
+
+__device__ __forceinline__ uint32_t hist_get(uint32_t const *H, uint32_t code)
+{
+	uint32_t const w = H[code >> 1];
+	return (code & 1u) ? (w >> 16) : (w & 0xffffu);
+}
+
+// Top list of column k for the DP (reference: the pairs of pbwt_context::output_divergence_value_counts(),
+// lib/libbio/include/libbio/pbwt.hh:157-199, read from the largest value downwards): entries (v, S) with
+// S = #{i : d[i] > v}, for every distinct v with S <= cap.  One warp.
+__device__ __forceinline__ void emit_top_list(
+	uint32_t const *H, uint32_t const top_code, uint32_t const R, uint32_t const *old, uint64_t const s_glob,
+	uint32_t const m, uint32_t const cap, uint2 *out, uint32_t *cnt_out, uint32_t *h0_out, bool const zero_present
+)
+{
+	uint32_t const lane = lane_id();
+	uint32_t const lt = (1u << lane) - 1u;
+	uint32_t S = 0, E = 0;
+	bool dropped = false;
+	int base = (int) top_code;
+	while (base >= 0 && S <= cap)
+	{
+		int const code = base - (int) lane;
+		uint32_t const c = code >= 0 ? hist_get(H, (uint32_t) code) : 0u;
+		uint32_t const inc = warp_incl_sum(c);
+		uint32_t const Sx = S + inc - c;
+		bool const keep = c > 0 && Sx <= cap;
+		uint32_t const mask = __ballot_sync(FSQ_FULL, keep);
+		dropped |= 0 != __ballot_sync(FSQ_FULL, c > 0 && !keep);
+		if (keep)
+		{
+			uint32_t const v = (uint32_t) code >= R ? (uint32_t) (s_glob + 1 + ((uint32_t) code - R)) : old[code];
+			out[E + __popc(mask & lt)] = make_uint2(v, Sx);
+		}
+		E += __popc(mask);
+		S += __shfl_sync(FSQ_FULL, inc, 31);
+		base -= 32;
+	}
+	if (0 == lane)
+	{
+		bool const complete = !dropped && S >= m;
+		*cnt_out = E | (complete ? 0x80000000u : 0u);
+		*h0_out = zero_present ? hist_get(H, 0) : 0u;
+	}
+}
+
+
+template <int TPW, bool HIST>
+__global__ void __launch_bounds__(1024) pbwt_block_kernel(block_args const A)
+{
+	extern __shared__ __align__(128) uint8_t smem_raw[];
+	uint32_t const tid = threadIdx.x;
+	uint32_t const n_warps = blockDim.x >> 5;
+	uint32_t const warp = tid >> 5;
+	uint32_t const m = A.m;
+
+	uint32_t const b = (MODE_DUMP == A.mode) ? A.blk_ids[blockIdx.x] : blockIdx.x + A.first_block;
+	uint64_t const s = (uint64_t) b * A.C;                          // local column index of the block start
+	uint64_t e = s + A.C < A.n_local ? s + A.C : A.n_local;
+	uint64_t const s_glob = A.col0 + s;
+
+	uint32_t dump_next = 0, dump_end = 0;
+	if (MODE_DUMP == A.mode)
+	{
+		dump_next = A.dump_begin[b];
+		dump_end = A.dump_begin[b + 1];
+		if (dump_next == dump_end) return;
+		e = A.dump_cols[dump_end - 1];                                // last right bound needed in this block
+	}
+
+	// ---- carve shared memory (mirrors block_smem_bytes()) ----
+	size_t off = 0;
+	auto carve = [&](size_t bytes) { void *p = smem_raw + off; off += (bytes + 15) & ~size_t(15); return p; };
+	uint8_t *colbuf = (uint8_t *) carve(2 * (size_t) A.cg * A.col_stride);
+	uint64_t *mbar = (uint64_t *) carve(2 * sizeof(uint64_t));
+	step_shared sh;
+	sh.sa = (uint16_t *) carve(sizeof(uint16_t) * m);
+	sh.sd = carve(sizeof(uint16_t) * m);
+	sh.wcnt = (uint32_t *) carve(sizeof(uint32_t) * n_warps * FSQ_MAX_SYMS);
+	sh.wcar = (uint32_t *) carve(sizeof(uint32_t) * n_warps * FSQ_MAX_SYMS);
+	sh.whas = (uint32_t *) carve(sizeof(uint32_t) * n_warps);
+	uint32_t *H = HIST ? (uint32_t *) carve(sizeof(uint32_t) * ((m + A.C + 2) / 2 + 1)) : nullptr;
+	uint16_t *sd = (uint16_t *) sh.sd;
+
+	// ---- start state ----
+	uint32_t R = 1;
+	uint32_t const *old = nullptr;
+	if (MODE_LOCAL == A.mode)
+	{
+		for (uint32_t i = tid; i < m; i += blockDim.x) { sh.sa[i] = (uint16_t) i; sd[i] = 0; }
+	}
+	else
+	{
+		R = A.R[b];
+		old = A.oldvals + (size_t) b * m;
+		uint32_t const *a0 = A.st_a + (size_t) b * m;
+		uint16_t const *c0 = A.code + (size_t) b * m;
+		for (uint32_t i = tid; i < m; i += blockDim.x) { sh.sa[i] = (uint16_t) a0[i]; sd[i] = c0[i]; }
+	}
+	if (HIST)
+	{
+		uint32_t const words = (m + A.C + 2) / 2 + 1;
+		for (uint32_t i = tid; i < words; i += blockDim.x) H[i] = 0;
+	}
+	if (0 == tid)
+	{
+		mbar_init(&mbar[0], 1);
+		mbar_init(&mbar[1], 1);
+		mbar_fence_init();
+	}
+	__syncthreads();
+	if (HIST)
+	{
+		for (uint32_t i = tid; i < m; i += blockDim.x)
+		{
+			uint32_t const c = sd[i];
+			atomicAdd(&H[c >> 1], (c & 1u) ? 0x10000u : 1u);
+		}
+	}
+	bool const zero_present = (MODE_LOCAL == A.mode) ? (0 == s_glob) : (0 == old[0]);
+
+	auto decode = [&](uint32_t c) -> uint32_t {
+		if (c >= R) return (uint32_t) (s_glob + 1 + (c - R));
+		return (MODE_LOCAL == A.mode) ? (uint32_t) s_glob : old[c];
+	};
+
+	// ---- column loop; columns arrive through a two-stage TMA ring of cg columns each ----
+	uint64_t const n_cols = e - s;
+	uint32_t const n_stages = (uint32_t) ((n_cols + A.cg - 1) / A.cg);
+	auto issue = [&](uint32_t g) {
+		uint64_t const c_first = s + (uint64_t) g * A.cg;
+		uint64_t const c_cnt = (c_first + A.cg <= e) ? A.cg : e - c_first;
+		uint32_t const bytes = (uint32_t) (c_cnt * A.col_stride);
+		mbar_expect_tx(&mbar[g & 1], bytes);
+		tma_load_1d(colbuf + (size_t) (g & 1) * A.cg * A.col_stride, A.cols + c_first * A.col_stride, bytes, &mbar[g & 1]);
+	};
+	if (0 == tid && n_stages) issue(0);
+
+	for (uint64_t j = 0; j < n_cols; ++j)
+	{
+		uint32_t const g = (uint32_t) (j / A.cg);
+		uint32_t const jj = (uint32_t) (j % A.cg);
+		if (0 == jj)
+		{
+			if (0 == tid && g + 1 < n_stages) issue(g + 1);
+			mbar_wait(&mbar[g & 1], (g >> 1) & 1u);
+		}
+		if (HIST && j > 0 && warp == n_warps - 1)
+		{
+			uint64_t const kk = s + j - 1;
+			emit_top_list(H, R + (uint32_t) (j - 1), R, old, s_glob, m, A.cap,
+				A.toplist + kk * (A.cap + 1), A.cnt + kk, A.h0 + kk, zero_present);
+		}
+		nibble_source src{(uint32_t const *) (colbuf + ((size_t) (g & 1) * A.cg + jj) * A.col_stride)};
+		column_step <uint16_t, TPW, HIST>(sh, m, A.n_tiles, A.nsym, R + (uint32_t) j, src, H);
+
+		if (MODE_DUMP == A.mode)
+		{
+			while (dump_next < dump_end && A.dump_cols[dump_next] == s + j + 1)
+			{
+				uint32_t *oa = A.dump_a + (size_t) dump_next * m;
+				uint32_t *od = A.dump_d + (size_t) dump_next * m;
+				for (uint32_t i = tid; i < m; i += blockDim.x) { oa[i] = sh.sa[i]; od[i] = decode(sd[i]); }
+				++dump_next;
+			}
+		}
+	}
+	if (HIST && n_cols && warp == n_warps - 1)
+	{
+		uint64_t const kk = s + n_cols - 1;
+		emit_top_list(H, R + (uint32_t) (n_cols - 1), R, old, s_glob, m, A.cap,
+			A.toplist + kk * (A.cap + 1), A.cnt + kk, A.h0 + kk, zero_present);
+	}
+	if (MODE_LOCAL == A.mode)
+	{
+		uint32_t *oa = A.sum_a + (size_t) b * m;
+		uint32_t *od = A.sum_d + (size_t) b * m;
+		for (uint32_t i = tid; i < m; i += blockDim.x) { oa[i] = sh.sa[i]; od[i] = decode(sd[i]); }
+	}
+}
+
+
+size_t block_smem_bytes(block_args const &A, uint32_t n_warps, bool hist)
+{
+	auto r16 = [](size_t b) { return (b + 15) & ~size_t(15); };
+	size_t t = 0;
+	t += r16(2 * (size_t) A.cg * A.col_stride);
+	t += r16(2 * sizeof(uint64_t));
+	t += r16(sizeof(uint16_t) * A.m) * 2;
+	t += r16(sizeof(uint32_t) * n_warps * FSQ_MAX_SYMS) * 2;
+	t += r16(sizeof(uint32_t) * n_warps);
+	if (hist) t += r16(sizeof(uint32_t) * ((A.m + A.C + 2) / 2 + 1));
+	return t;
+}
+
+template <int TPW, bool HIST>
+static cudaError_t launch_block_t(block_args const &A, uint32_t n_blocks, uint32_t n_warps, cudaStream_t st)
+{
+	size_t const smem = block_smem_bytes(A, n_warps, HIST);
+	auto kern = pbwt_block_kernel <TPW, HIST>;
+	cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+	if (cudaSuccess != err) return err;
+	kern <<<n_blocks, n_warps * 32, smem, st>>>(A);
+	return cudaGetLastError();
+}
+
+// Tiles per warp are a compile-time bound (the state is staged in registers); pick the smallest instantiation.
+cudaError_t launch_block(block_args const &A, uint32_t n_blocks, uint32_t n_warps, uint32_t tpw, bool hist, cudaStream_t st)
+{
+#define FSQ_CASE(T) if (tpw <= T) return hist ? launch_block_t <T, true>(A, n_blocks, n_warps, st) : launch_block_t <T, false>(A, n_blocks, n_warps, st);
+	FSQ_CASE(2) FSQ_CASE(4) FSQ_CASE(8) FSQ_CASE(16) FSQ_CASE(24) FSQ_CASE(32)
+#undef FSQ_CASE
+	return cudaErrorInvalidValue;
+}
+
+
+// ---- rank compression of a block's start divergences ------------------------------------------------------------
+// d values at a block start are arbitrary positions <= s; the scan kernels keep them as 16-bit order-preserving
+// codes (rank among the distinct start values), which double as histogram indices.
+__global__ void __launch_bounds__(1024) prep_kernel(uint32_t const *st_d, uint32_t m, uint32_t p2, uint16_t *code, uint32_t *oldvals, uint32_t *R, uint32_t first_block)
+{
+	extern __shared__ __align__(128) uint8_t smem_raw[];
+	uint32_t *buf = (uint32_t *) smem_raw;                  // [p2]
+	uint16_t *rank = (uint16_t *) (buf + p2);               // [p2]
+	__shared__ uint32_t scratch[34];
+	uint32_t const b = blockIdx.x + first_block;
+	uint32_t const tid = threadIdx.x;
+	uint32_t const *d = st_d + (size_t) b * m;
+
+	for (uint32_t i = tid; i < p2; i += blockDim.x) buf[i] = i < m ? d[i] : 0xffffffffu;
+	__syncthreads();
+	for (uint32_t k = 2; k <= p2; k <<= 1)
+		for (uint32_t j = k >> 1; j > 0; j >>= 1)
+		{
+			for (uint32_t i = tid; i < p2; i += blockDim.x)
+			{
+				uint32_t const l = i ^ j;
+				if (l > i)
+				{
+					uint32_t const x = buf[i], y = buf[l];
+					bool const up = 0 == (i & k);
+					if ((x > y) == up) { buf[i] = y; buf[l] = x; }
+				}
+			}
+			__syncthreads();
+		}
+
+	// distinct values → ranks
+	uint32_t const per = (p2 + blockDim.x - 1) / blockDim.x;
+	uint32_t const lo = tid * per, hi = min(lo + per, m);
+	uint32_t cnt = 0;
+	for (uint32_t i = lo; i < hi; ++i) cnt += (0 == i || buf[i] != buf[i - 1]);
+	uint32_t total;
+	uint32_t pos = block_excl_scan(cnt, scratch, total);
+	uint32_t *ov = oldvals + (size_t) b * m;
+	for (uint32_t i = lo; i < hi; ++i)
+	{
+		if (0 == i || buf[i] != buf[i - 1]) ov[pos++] = buf[i];
+		rank[i] = (uint16_t) (pos - 1);
+	}
+	if (0 == tid) R[b] = total;
+	__syncthreads();
+	uint16_t *co = code + (size_t) b * m;
+	for (uint32_t i = tid; i < m; i += blockDim.x)
+	{
+		uint32_t const v = d[i];
+		uint32_t l = 0, h = m;          // lower bound in buf[0..m)
+		while (l < h) { uint32_t const mid = (l + h) >> 1; if (buf[mid] < v) l = mid + 1; else h = mid; }
+		co[i] = rank[l];
+	}
+}
+
+cudaError_t launch_prep(uint32_t const *st_d, uint32_t m, uint16_t *code, uint32_t *oldvals, uint32_t *R, uint32_t first_block, uint32_t n_blocks, cudaStream_t st)
+{
+	uint32_t p2 = 32;
+	while (p2 < m) p2 <<= 1;
+	size_t const smem = (size_t) p2 * 6;
+	cudaError_t err = cudaFuncSetAttribute(prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+	if (cudaSuccess != err) return err;
+	uint32_t const threads = p2 < 1024 ? p2 : 1024;
+	prep_kernel <<<n_blocks, threads, smem, st>>>(st_d, m, p2, code, oldvals, R, first_block);
+	return cudaGetLastError();
+}
+
+
+// ---- boundary stitch ------------------------------------------------------------------------------
+// true state at e  =  one generalised PBWT step on the true state at s whose "symbol" is the class of the row in the
+// local summary (rows with identical columns [s, e) form a class, classes in local PBWT order).  The class id is
+// fed to the ordinary 16-way column step one hex digit at a time, least significant first (a stable LSD radix sort,
+// i.e. up to four virtual columns); divergences of class starts are then taken from the summary.
+struct digit_source
+{
+	uint16_t const *cls;
+	uint32_t shift;
+	__device__ __forceinline__ uint32_t operator()(uint32_t x) const { return (cls[x] >> shift) & 15u; }
+};
+
+template <int TPW>
+__global__ void __launch_bounds__(1024) stitch_kernel(stitch_args const A)
+{
+	extern __shared__ __align__(128) uint8_t smem_raw[];
+	__shared__ uint32_t scratch[34];
+	uint32_t const tid = threadIdx.x;
+	uint32_t const n_warps = blockDim.x >> 5;
+	uint32_t const m = A.m;
+	size_t off = 0;
+	auto carve = [&](size_t bytes) { void *p = smem_raw + off; off += (bytes + 15) & ~size_t(15); return p; };
+	step_shared sh;
+	sh.sa = (uint16_t *) carve(sizeof(uint16_t) * m);
+	sh.sd = carve(sizeof(uint32_t) * m);
+	uint16_t *cls = (uint16_t *) carve(sizeof(uint16_t) * m);
+	sh.wcnt = (uint32_t *) carve(sizeof(uint32_t) * n_warps * FSQ_MAX_SYMS);
+	sh.wcar = (uint32_t *) carve(sizeof(uint32_t) * n_warps * FSQ_MAX_SYMS);
+	sh.whas = (uint32_t *) carve(sizeof(uint32_t) * n_warps);
+	uint32_t *sd = (uint32_t *) sh.sd;
+
+	uint32_t const per = (m + blockDim.x - 1) / blockDim.x;
+	uint32_t const lo = min(tid * per, m), hi = min(lo + per, m);
+
+	for (uint32_t step = 0; step < A.n_steps; ++step)
+	{
+		stitch_item const it = A.items[step];
+		uint32_t const *in_a = it.in_a, *in_d = it.in_d;           // incoming state (true state or a summary)
+		uint32_t const *pi = it.pi, *delta = it.delta;             // local summary of [s, e)
+		uint32_t const s_mark = it.s_mark;                         // delta <= s_mark  <=>  same class as predecessor
+
+		// classes of the summary
+		uint32_t cnt = 0;
+		for (uint32_t i = lo; i < hi; ++i) cnt += (0 == i || delta[i] > s_mark);
+		uint32_t total;
+		uint32_t c = block_excl_scan(cnt, scratch, total);
+		for (uint32_t i = lo; i < hi; ++i)
+		{
+			if (0 == i || delta[i] > s_mark) ++c;
+			cls[pi[i]] = (uint16_t) (c - 1);
+		}
+		if (it.identity_in)
+			for (uint32_t i = tid; i < m; i += blockDim.x) { sh.sa[i] = (uint16_t) i; sd[i] = it.identity_d; }
+		else
+			for (uint32_t i = tid; i < m; i += blockDim.x) { sh.sa[i] = (uint16_t) in_a[i]; sd[i] = in_d[i]; }
+		__syncthreads();
+
+		uint32_t digits = 1;
+		while (digits < 4 && (total - 1) >> (4 * digits)) ++digits;
+		for (uint32_t p = 0; p < digits; ++p)
+		{
+			digit_source src{cls, 4 * p};
+			column_step <uint32_t, TPW, false>(sh, m, A.n_tiles, 16, 0xffffffffu, src, nullptr);
+		}
+
+		uint32_t *oa = it.out_a, *od = it.out_d;
+		for (uint32_t i = tid; i < m; i += blockDim.x)
+		{
+			uint32_t const dl = delta[i];
+			oa[i] = sh.sa[i];
+			od[i] = (0 == i || dl > s_mark) ? dl : sd[i];
+		}
+		__syncthreads();
+		__threadfence();
+	}
+}
+
+size_t stitch_smem_bytes(uint32_t m, uint32_t n_warps)
+{
+	auto r16 = [](size_t b) { return (b + 15) & ~size_t(15); };
+	return r16(2 * (size_t) m) * 2 + r16(4 * (size_t) m) + r16(4 * n_warps * FSQ_MAX_SYMS) * 2 + r16(4 * n_warps);
+}
+
+template <int TPW>
+static cudaError_t launch_stitch_t(stitch_args const &A, uint32_t n_warps, cudaStream_t st)
+{
+	size_t const smem = stitch_smem_bytes(A.m, n_warps);
+	auto kern = stitch_kernel <TPW>;
+	cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+	if (cudaSuccess != err) return err;
+	kern <<<1, n_warps * 32, smem, st>>>(A);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_stitch(stitch_args const &A, cudaStream_t st)
+{
+	uint32_t const n_warps = A.n_tiles < 32 ? A.n_tiles : 32;
+	uint32_t const tpw = (A.n_tiles + n_warps - 1) / n_warps;
+#define FSQ_CASE(T) if (tpw <= T) return launch_stitch_t <T>(A, n_warps, st);
+	FSQ_CASE(1) FSQ_CASE(2) FSQ_CASE(4) FSQ_CASE(8) FSQ_CASE(16) FSQ_CASE(32) FSQ_CASE(64)
+#undef FSQ_CASE
+	return cudaErrorInvalidValue;
+}
+
+} // namespace fsq

@@ -1,0 +1,146 @@
+/*
+ * fsq.h — C ABI of libfsq_b200.so, the B200-native PBWT + segmentation path of founder-sequences.
+ *
+ * The reference (tsnorri/founder-sequences) has no plugin / FFI interface; the entry points below replace
+ * the narrowest in-process C++ seams on the hot path.  Each cites the reference interface
+ * it stands in for.  Plain pointers and sizes only; no C++ or torch types; never throws, never aborts:
+ * every call returns an fsq_status and fsq_last_error() holds the message (the host wrapper turns a
+ * non-zero status into libbio_fail(), lib/libbio/src/assert.cc:11-20).
+ *
+ * All arithmetic is integer and results are bit-identical to the reference's.  There is no CPU
+ * fallback: without a CUDA device every compute call fails with FSQ_ERR_CUDA.
+ *
+ * Threading: a context may be used from any one host thread at a time; it owns its CUDA stream.
+ */
+#ifndef FSQ_H
+#define FSQ_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum fsq_status {
+	FSQ_OK = 0,
+	FSQ_ERR_ARG = 1,          /* bad argument (null pointer, m == 0, L == 0, more than 15 distinct characters, ...) */
+	FSQ_ERR_CUDA = 2,         /* CUDA runtime error, or no device */
+	FSQ_ERR_SHORT = 3,        /* n < 2L: the long path does not apply; use fsq_distinct_rows (generate_context.cc:379-390) */
+	FSQ_ERR_NOT_REDUCIBLE = 4,/* K == m: the reference exits with failure here (generate_context.cc:192-200) */
+	FSQ_ERR_NOMEM = 5,
+	FSQ_ERR_UNSUPPORTED = 6,  /* shape outside what the kernels are built for (m > 65535 - block columns, n >= 2^31) */
+	FSQ_ERR_INTERNAL = 7
+} fsq_status;
+
+typedef struct fsq_ctx fsq_ctx;                     /* one per device / host thread */
+typedef struct fsq_msa fsq_msa;                     /* column-major, 4-bit packed alignment resident in HBM */
+typedef struct fsq_segmentation fsq_segmentation;   /* result of the long path, device + host copies */
+typedef struct fsq_summary fsq_summary;             /* a rank's column-range scan summary (multi-GPU) */
+
+/* ---- context ------------------------------------------------------------------------------------------ */
+
+int fsq_create(int device, fsq_ctx **out);
+void fsq_destroy(fsq_ctx *ctx);
+const char *fsq_last_error(const fsq_ctx *ctx);     /* ctx may be NULL: returns the message of a failed fsq_create */
+const char *fsq_version(void);
+
+/* Tuning knobs (all have defaults): "block_columns" (columns per scan block), "cap" (initial bound on the
+ * per-column top list; grown automatically when the DP proves it too small), "keep_dp" (retain the full DP
+ * table for fsq_segmentation_dp_table), "keep_traceback_states". */
+int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value);
+int fsq_get_stat(const fsq_ctx *ctx, const char *key, double *value);   /* e.g. "ms_pack", "ms_pass_a", "ms_dp", "kernel_launches" */
+
+/* ---- alignment in HBM --------------------------------------------------------------------------------- */
+
+/* Replaces the row access `inputs[vec_idx][column_idx]` + `alphabet.char_to_comp` of
+ * libbio::pbwt::build_prefix_and_divergence_arrays (lib/libbio/include/libbio/pbwt.hh:93-95,119-121) and the
+ * sequence_vector of spans (include/founder_sequences/founder_sequences.hh:38-40).
+ * rows: m host pointers to n bytes each.  comp: the reference alphabet's 256-entry char→comp table
+ * (consecutive_alphabet.hh:259-264), or NULL to have it built here the same way (NUL = 0, bytes present get
+ * 1.. in byte order).  Copies host→device and transposes/packs on the device. */
+int fsq_msa_from_rows(fsq_ctx *ctx, const uint8_t *const *rows, uint32_t m, uint64_t n, const uint8_t comp[256], fsq_msa **out);
+
+/* Same, rows already on the device as a row-major m × n byte matrix with the given row stride; comp must be given. */
+int fsq_msa_from_device_rows(fsq_ctx *ctx, const uint8_t *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, const uint8_t comp[256], fsq_msa **out);
+
+/* Founder-mosaic synthetic alignment generated on the device, columns [col0, col0 + n) of the matrix defined by
+ * (seed, founders, gaps) — see founder-sequences_b200/synth.py for the definition.  Used by bench.py and the tests. */
+int fsq_msa_synth(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps, fsq_msa **out);
+/* The same cells as ASCII rows (row-major m × n) into a device buffer, for end-to-end runs that start from host rows. */
+int fsq_synth_rows_device(fsq_ctx *ctx, uint8_t *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps);
+
+void fsq_msa_free(fsq_msa *msa);
+uint32_t fsq_msa_rows(const fsq_msa *msa);
+uint64_t fsq_msa_columns(const fsq_msa *msa);
+
+/* ---- PBWT state tap (a1–a3) ---------------------------------------------------------------------------- */
+
+/* (a_c, d_c) — the input permutation / divergence *before* column c, i.e. after columns [0, c) — for each of
+ * the `count` ascending positions in `columns` (1 <= c <= n).  Replaces running
+ * libbio::pbwt::pbwt_context::process() to column c and reading input_permutation()/input_divergence()
+ * (lib/libbio/include/libbio/pbwt_context.hh:184-243, 439-473).  a, d: count × m. */
+int fsq_pbwt_states(fsq_ctx *ctx, const fsq_msa *msa, const uint64_t *columns, uint32_t count, uint32_t *a, uint32_t *d);
+
+/* ---- segmentation, long path (seam S1) ----------------------------------------------------------------- */
+
+/* Replaces segmentation_lp_context::generate_traceback → update_samples_to_traceback_positions →
+ * find_segments_greedy (founder-sequences/segmentation_lp_context.cc:26-390), whose result the reference hands
+ * over as a segmentation_container (include/founder_sequences/segmentation_container.hh:15-20).
+ * Blocking.  Returns FSQ_ERR_SHORT when n < 2L and FSQ_ERR_NOT_REDUCIBLE when K == m. */
+int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t segment_length_bound, fsq_segmentation **out);
+void fsq_segmentation_free(fsq_segmentation *seg);
+
+/* container.reduced_traceback.size() and container.max_segment_size */
+uint32_t fsq_segmentation_count(const fsq_segmentation *seg);
+uint32_t fsq_segmentation_max_segment_size(const fsq_segmentation *seg);
+/* reduced_traceback[i].{lb, rb, segment_size}; arrays of fsq_segmentation_count() entries */
+int fsq_segmentation_bounds(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *size);
+/* reduced_pbwt_samples[i].input_permutation() / input_divergence(); count × m each */
+int fsq_segmentation_states(const fsq_segmentation *seg, uint32_t *a, uint32_t *d);
+
+/* Test taps.  The traceback before reduction (segmentation_lp_context.cc:191-224): count, then lb/rb/max/size. */
+uint32_t fsq_segmentation_traceback_count(const fsq_segmentation *seg);
+int fsq_segmentation_traceback(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size);
+/* The whole DP table, n - L + 1 entries (needs option keep_dp = 1; entries the reference never writes hold its
+ * defaults {0, 0, UINT32_MAX, UINT32_MAX}). */
+int fsq_segmentation_dp_table(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size);
+
+/* ---- short path (seam S1') ------------------------------------------------------------------------------ */
+
+/* Replaces segmentation_sp_context::process (founder-sequences/segmentation_sp_context.cc:21-28):
+ * distinct rows in PBWT order after all n columns, as (first row of the run, run length).  Arrays of m entries. */
+int fsq_distinct_rows(fsq_ctx *ctx, const fsq_msa *msa, uint32_t *row_of_run, uint32_t *run_len, uint32_t *count);
+
+/* ---- segment texts (seam S2) and edge weights (seam S3) ---------------------------------------------------- */
+
+/* Replaces pbwt_context::unique_substring_count_idxs_lhs (lib/libbio/include/libbio/pbwt.hh:253-280, called at
+ * founder-sequences/join_context.cc:73) and the gather + per-set sort of create_segment_texts_task::execute
+ * (founder-sequences/create_segment_texts_task.cc:15-35) for reduced segment `segment`:
+ * runs in PBWT order as CSR — run_off[n_runs + 1] offsets into ids[m], row ids ascending inside a run —
+ * plus class_of_row[m] (the run each row belongs to).  The size-sort / padding to K slots (:38-82, std::sort and
+ * double ceil) stays on the host. */
+int fsq_segment_sets(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment, uint32_t *run_off, uint32_t *ids, uint32_t *class_of_row, uint32_t *n_runs);
+
+/* Replaces the K² set_intersection_size calls of merge_segments_task::execute
+ * (founder-sequences/merge_segments_task.cc:133-176; lib/libbio/include/libbio/algorithm/set_count.hh:61-89) for the
+ * adjacent reduced segments (segment, segment + 1): W[i * runs_rhs + j] = |S_i ∩ T_j| over the runs in PBWT order. */
+int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment, int32_t *W, uint32_t *runs_lhs, uint32_t *runs_rhs);
+
+/* ---- column-sharded operation (one process per GPU; the exchange itself is done by the caller over NCCL) ---- */
+
+/* Rank-local scan of this rank's columns from the identity state: the (π, δ) summary of the whole range
+ * (SURVEY.md A.10).  Summaries compose associatively. */
+int fsq_local_summary(fsq_ctx *ctx, const fsq_msa *msa, uint64_t first_column, fsq_summary **out);
+void fsq_summary_free(fsq_summary *s);
+/* Device pointers for the exchange (m uint32 each) and the column range the summary covers. */
+uint32_t *fsq_summary_device_pi(fsq_summary *s);
+uint32_t *fsq_summary_device_delta(fsq_summary *s);
+/* Given the true state (a, d on the device, m uint32 each) at the first column of the summary, produce the true
+ * state at its last column + 1 in place. */
+int fsq_apply_summary(fsq_ctx *ctx, const fsq_summary *s, uint32_t *d_a, uint32_t *d_d);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FSQ_H */

@@ -1,0 +1,185 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (ctypes over libfsq_b200.so), against the oracle on
+the same seeded inputs.  Everything here is integer work, so the bar is bit-exact equality."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+KAT_ROWS = [b"ACGTACGTAC", b"ACGTACGAAC", b"ACCTACGTAC", b"ACGTACGTAC", b"TCGTACGAAC"]
+
+
+def as_rows(lst):
+    return np.frombuffer(b"".join(lst), np.uint8).reshape(len(lst), -1).copy()
+
+
+def check_states(ctx, oracle, rows, block_columns=None, warps=None, columns=None):
+    m, n = rows.shape
+    if block_columns:
+        ctx.set_option("block_columns", block_columns)
+    ctx.set_option("warps", warps or 0)
+    if columns is None:
+        columns = np.arange(1, n + 1)
+    with oracle.open(rows) as o:
+        oa, od = o.scan_dump(n, hist=False)
+    with ctx.msa_from_rows(rows) as msa:
+        a, d = ctx.pbwt_states(msa, columns)
+    for i, c in enumerate(columns):
+        assert np.array_equal(a[i], oa[c - 1]), "a differs at column %d (m=%d n=%d C=%s W=%s)\n%s\n%s" % (c, m, n, block_columns, warps, a[i], oa[c - 1])
+        assert np.array_equal(d[i], od[c - 1]), "d differs at column %d (m=%d n=%d C=%s W=%s)\n%s\n%s" % (c, m, n, block_columns, warps, d[i], od[c - 1])
+
+
+def test_kat_states(ctx, oracle):
+    """The 5 x 10 known-answer example of SURVEY.md Appendix B (reference pbwt_context output)."""
+    rows = as_rows(KAT_ROWS)
+    with ctx.msa_from_rows(rows) as msa:
+        a, d = ctx.pbwt_states(msa, [3, 8, 10])
+    assert a[0].tolist() == [2, 0, 1, 3, 4] and d[0].tolist() == [3, 3, 0, 0, 1]
+    assert a[1].tolist() == [1, 4, 2, 0, 3] and d[1].tolist() == [8, 1, 8, 3, 0]
+    assert a[2].tolist() == [1, 4, 2, 0, 3] and d[2].tolist() == [10, 1, 8, 3, 0]
+
+
+@pytest.mark.parametrize("m,n,C,W", [
+    (5, 40, 7, 0), (33, 100, 16, 0), (64, 300, 64, 0), (64, 300, 13, 2), (100, 257, 50, 4),
+    (257, 200, 33, 0), (1000, 150, 40, 1), (1000, 150, 40, 2), (1000, 120, 64, 8), (2500, 90, 32, 0),
+])
+def test_states_every_column(ctx, oracle, synth, m, n, C, W):
+    rows = synth.synth_rows(m, n, seed=m + n, founders=max(2, m // 12), gaps=(m % 2 == 0), recomb_block=37, mu=0.02, gap=0.02)
+    check_states(ctx, oracle, rows, C, W)
+
+
+def test_states_identical_rows_and_columns(ctx, oracle):
+    """Degenerate classes: all rows equal; then one differing row; identity columns."""
+    rows = np.full((40, 90), ord("A"), np.uint8)
+    check_states(ctx, oracle, rows, 16)
+    rows[7, 50] = ord("C")
+    rows[21, 10:14] = ord("T")
+    check_states(ctx, oracle, rows, 16)
+
+
+def test_states_random_binary(ctx, oracle):
+    rng = np.random.default_rng(5)
+    for it in range(6):
+        m = int(rng.integers(2, 200))
+        n = int(rng.integers(2, 120))
+        rows = rng.choice(np.frombuffer(b"AC", np.uint8), size=(m, n), p=[0.85, 0.15])
+        check_states(ctx, oracle, rows, int(rng.integers(1, 40)))
+
+
+def test_synth_device_matches_host(ctx, fsq, synth, oracle):
+    """The device generator (packed) is the same matrix as synth.py: same PBWT states."""
+    m, n = 70, 400
+    rows = synth.synth_rows(m, n, seed=3, founders=5, gaps=True)
+    cols = [1, 7, 199, 400]
+    with ctx.msa_synth(m, n, 3, 5, gaps=True) as msa_dev, ctx.msa_from_rows(rows) as msa_host:
+        a1, d1 = ctx.pbwt_states(msa_dev, cols)
+        a2, d2 = ctx.pbwt_states(msa_host, cols)
+    assert np.array_equal(a1, a2) and np.array_equal(d1, d2)
+
+
+def compare_segmentation(ctx, oracle, rows, L, block_columns=None, cap=None, sets=True):
+    m, n = rows.shape
+    if block_columns:
+        ctx.set_option("block_columns", block_columns)
+    if cap:
+        ctx.set_option("cap", cap)
+    ctx.set_option("keep_dp", 1)
+    with oracle.open(rows) as o, ctx.msa_from_rows(rows) as msa:
+        status = o.segment(L)
+        assert status in (0, 2)
+        try:
+            seg = ctx.segment(msa, L)
+            assert status == 0
+        except Exception as e:      # K == m: the reference exits; we report NOT_REDUCIBLE and keep the traceback
+            assert status == 2 and getattr(e, "code", None) == 4, e
+            seg = e.segmentation
+        with seg:
+            olb, orb, omx, osz = o.dp()
+            lb, rb, mx, sz = seg.dp_table(len(olb))
+            bad = np.nonzero((lb != olb) | (mx != omx) | (sz != osz) | (rb != orb))[0]
+            assert len(bad) == 0, "DP table differs first at entry %d: got (%d,%d,%d,%d) want (%d,%d,%d,%d)" % (
+                bad[0], lb[bad[0]], rb[bad[0]], mx[bad[0]], sz[bad[0]], olb[bad[0]], orb[bad[0]], omx[bad[0]], osz[bad[0]])
+            for x, y in zip(seg.traceback(), o.traceback()):
+                assert np.array_equal(x, y)
+            assert seg.max_segment_size == o.K()
+            if status == 2:
+                return None
+            rlb, rrb, rsz = seg.reduced_traceback()
+            qlb, qrb, _, qsz = o.reduced()
+            assert np.array_equal(rlb, qlb) and np.array_equal(rrb, qrb) and np.array_equal(rsz, qsz)
+            a, d = seg.reduced_pbwt_samples()
+            oa, od = o.reduced_states()
+            assert np.array_equal(a, oa) and np.array_equal(d, od)
+            if sets:
+                for s in range(min(seg.count, 6)):
+                    off, ids, cls = seg.segment_sets(s)
+                    ooff, oids, ocls = o.segment_sets(s)
+                    assert np.array_equal(off, ooff) and np.array_equal(ids, oids) and np.array_equal(cls, ocls)
+                    if s + 1 < seg.count:
+                        W = seg.pair_weights(s)
+                        noff = o.segment_sets(s + 1)[0]
+                        assert np.array_equal(W, o.pair_weights(s, len(off) - 1, len(noff) - 1))
+            return seg.max_segment_size, len(rlb)
+
+
+def test_kat_segmentation(ctx, oracle):
+    rows = as_rows(KAT_ROWS)
+    compare_segmentation(ctx, oracle, rows, 2, block_columns=4)
+
+
+@pytest.mark.parametrize("m,n,L,C,founders", [
+    (16, 400, 5, 32, 3), (48, 6000, 10, 256, 6), (64, 20000, 10, 0, 8), (200, 3000, 20, 100, 8),
+    (1000, 2000, 20, 128, 16), (96, 2000, 1, 64, 6), (96, 2100, 70, 300, 6), (2500, 600, 5, 64, 24),
+])
+def test_segmentation_matches_oracle(ctx, oracle, synth, m, n, L, C, founders):
+    rows = synth.synth_rows(m, n, seed=m + L, founders=founders, gaps=(founders % 2 == 0))
+    res = compare_segmentation(ctx, oracle, rows, L, C or None)
+    assert res is not None
+
+
+def test_segmentation_edge_lengths(ctx, oracle, synth):
+    """n == 2L, n == 2L + 1, n == 3L - 1: the staging boundaries of the first pass."""
+    for n, L in [(20, 10), (21, 10), (29, 10), (30, 10), (31, 10), (130, 64), (200, 65)]:
+        rows = synth.synth_rows(24, n, seed=n, founders=3, recomb_block=11, mu=0.01)
+        compare_segmentation(ctx, oracle, rows, L, block_columns=9, sets=False)
+
+
+def test_segmentation_small_cap_retries(ctx, oracle, synth):
+    """A top-list bound far below K must be detected by the DP and retried, not silently accepted."""
+    rows = synth.synth_rows(128, 1500, seed=9, founders=40, recomb_block=50, mu=0.01)
+    ctx.reset_stats()
+    res = compare_segmentation(ctx, oracle, rows, 6, block_columns=100, cap=2, sets=False)
+    assert res is None or res[0] > 2
+    assert ctx.stat("cap_retries") >= 1
+
+
+def test_segmentation_invariant_under_block_size(ctx, oracle, synth):
+    rows = synth.synth_rows(80, 1800, seed=21, founders=7, gaps=True)
+    results = []
+    for C in (1, 17, 64, 500, 4000):
+        ctx.set_option("block_columns", C)
+        with ctx.msa_from_rows(rows) as msa, ctx.segment(msa, 12) as seg:
+            results.append((seg.max_segment_size,) + tuple(x.tobytes() for x in seg.reduced_traceback()) + tuple(x.tobytes() for x in seg.reduced_pbwt_samples()))
+    assert all(r == results[0] for r in results)
+
+
+def test_not_reducible_and_short(ctx, fsq, oracle):
+    rng = np.random.default_rng(1)
+    rows = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=(6, 40))
+    with ctx.msa_from_rows(rows) as msa:
+        with pytest.raises(fsq.FsqError) as ei:
+            ctx.segment(msa, 30)
+        assert ei.value.code == fsq.ERR_SHORT
+        row, ln = ctx.distinct_rows(msa)
+        with oracle.open(rows) as o:
+            orow, oln = o.short_path()
+        assert np.array_equal(row, orow) and np.array_equal(ln, oln)
+    compare_segmentation(ctx, oracle, rows, 3, block_columns=8, sets=False)
+
+
+def test_errors_are_loud(ctx, fsq):
+    with pytest.raises(fsq.FsqError):
+        ctx.set_option("no_such_option", 1)
+    rows = np.arange(20 * 64, dtype=np.uint8).reshape(64, 20) % 23 + 65     # 23 distinct characters
+    with pytest.raises(fsq.FsqError) as ei:
+        ctx.msa_from_rows(rows)
+    assert ei.value.code == fsq.ERR_ARG
