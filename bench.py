@@ -1,0 +1,323 @@
+#!/usr/bin/env python
+"""bench.py — PBWT + segmentation throughput (MSA cells/s) of libfsq_b200 on B200, with the kernel roofline and
+the CPU reference timed beside it.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c1|c2|...]
+
+One "step" = one pass of the hot path (fsq_segment: local scans, stitch, exact scan + top lists, DP, traceback,
+re-scan, greedy reduction) over one synthetic founder-mosaic alignment.  `value` times it with the packed
+alignment already resident in HBM; `e2e` times the same through the C ABI from host rows (pinned), with the
+host->device copy, the transpose/pack and the device->host copy of the result inside the timed region.
+
+N > 1 (torchrun, one rank per GPU): every rank segments its own alignment of the same shape (independent
+alignments, e.g. chromosomes: no data-path collective) -> "scaling": "weak".  Column-sharding ONE alignment over
+ranks is not built yet (multi-GPU).
+
+--impl reference times the reference's own CPU code for the path (oracle/_ref when it was built, else the C
+restatement in oracle/), rank 0 only, on a bounded column sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "MSA cells/sec (m x n) PBWT+segmentation"
+BYTES_PER_CELL = 16.5     # read a,d (8) + write a,d (8) + one 4-bit symbol (0.5)
+
+WORKLOADS = {
+    # name: (m, n, L, founders, gaps, seed, description)
+    "c1": (64, 100_000, 10, 8, False, 1, "synthetic 64 x 100k, sigma=4, L=10"),
+    "c2": (1000, 1_000_000, 20, 16, True, 2, "synthetic 1,000 x 1M, sigma=5 (ACGT+gap), L=20"),
+    "c2s": (1000, 200_000, 20, 16, True, 2, "synthetic 1,000 x 200k (1/5 of config 2), sigma=5, L=20"),
+    "c3s": (5000, 1_000_000, 50, 32, True, 3, "synthetic 5,000 x 1M (1/10 of config 3), sigma=5, L=50"),
+    "c4s": (2500, 1_000_000, 50, 24, True, 4, "synthetic 2,500 x 1M (1/5 of config 4), L=50"),
+}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx = float(f[1])
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md: 6.65 TB/s)"
+
+
+def cpu_baseline(rows_sample, L, want_ref=True):
+    """Reference first pass (PBWT + histogram + DP per column; single-threaded in the reference) on a
+    bounded column sample.  The only place besides tests/ and smoke() that touches oracle/."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oraclelib
+    m, nc = rows_sample.shape
+    if want_ref and oraclelib.have_ref():
+        chk, kind = oraclelib.ref(), "reference"
+    else:
+        chk, kind = oraclelib.oracle(), "port"
+    with chk.open(rows_sample) as s:
+        secs = s.time_first_pass(L, nc)
+    cells = m * (nc - L)
+    return {"value": cells / secs, "unit": "cells/s", "cores": 1, "kind": kind,
+            "sample": "first pass (PBWT + divergence histogram + DP) over the first %d columns of the workload, %.1f s" % (nc, secs)}
+
+
+def sample_columns(m, kind_ref=True):
+    # about 10-20 s of CPU work: the compiled reference does ~10-13 Mcells/s on one core, the C port ~3x that
+    target_cells = 150e6 if kind_ref else 400e6
+    return int(max(2000, min(400_000, target_cells / m)))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--block-columns", type=int, default=0)
+    ap.add_argument("--warps", type=int, default=0)
+    ap.add_argument("--cap", type=int, default=0)
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    m, n, L, founders, gaps, seed, desc = WORKLOADS[args.workload]
+
+    import numpy as np
+    import torch
+    from __graft_entry__ import load_package
+    fsq = load_package()
+
+    if args.impl == "reference" and rank != 0:
+        return 0        # rank 0 alone runs and prints the reference arm
+    return run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, torch, fsq)
+
+
+def make_rows_sample(np, torch, fsq, m, nc, seed, founders, gaps, device_ok):
+    if device_ok:
+        with fsq.Context(0) as ctx:
+            buf = torch.empty((m, nc), dtype=torch.uint8, device="cuda:0")
+            ctx.synth_rows_device(buf.data_ptr(), nc, m, nc, seed, founders, gaps)
+            return buf.cpu().numpy()
+    from __graft_entry__ import load_synth
+    return load_synth().synth_rows(m, nc, seed, founders, gaps)
+
+
+def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, torch, fsq):
+    cells = m * n
+    have_gpu = torch.cuda.is_available()
+
+    if args.impl == "reference":
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oraclelib
+        use_ref = oraclelib.have_ref()
+        nc = sample_columns(m, use_ref)
+        rows = make_rows_sample(np, torch, fsq, m, nc, seed, founders, gaps, have_gpu)
+        vals = []
+        for i in range(args.warmup + args.steps):
+            # each step is a bounded sample; warm-up steps use a shorter one
+            cols = nc if i >= args.warmup else max(2 * L + 1, nc // 8)
+            b = cpu_baseline(rows[:, :cols].copy(), L, use_ref)
+            if i >= args.warmup:
+                vals.append(b)
+        v = sum(x["value"] for x in vals) / len(vals)
+        line = {
+            "impl": "reference", "metric": METRIC, "value": v, "unit": "cells/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * (m * (nc - L)) / v, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": desc, "sample_columns": nc},
+            "cpu_baseline": {"value": v, "unit": "cells/s", "cores": 1, "kind": vals[0]["kind"], "sample": vals[0]["sample"]},
+            "e2e": {"value": v, "unit": "cells/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        }
+        print(json.dumps(line))
+        return 0
+
+    if not have_gpu:
+        print(json.dumps({"error": "no CUDA device: libfsq_b200 has no CPU fallback"}))
+        return 1
+
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    dev = local_rank
+    ctx = fsq.Context(dev)
+    if args.block_columns:
+        ctx.set_option("block_columns", args.block_columns)
+    if args.warps:
+        ctx.set_option("warps", args.warps)
+    if args.cap:
+        ctx.set_option("cap", args.cap)
+    my_seed = seed + 1000 * rank     # every rank has its own alignment
+    msa = ctx.msa_synth(m, n, my_seed, founders, gaps)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if dist is not None:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    def step():
+        seg = ctx.segment(msa, L)
+        info = (seg.max_segment_size, seg.count)
+        seg.free()
+        return info
+
+    for _ in range(args.warmup):
+        info = step()
+    ctx.reset_stats()
+    sampler = ClockSampler(dev)
+    sampler.start()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        info = step()
+    barrier()
+    t1 = time.perf_counter()
+    clocks = sampler.stop()
+    secs = t1 - t0
+    if dist is not None:
+        t = torch.tensor([secs], device="cuda:%d" % dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        secs = float(t.item())
+    phases = {}
+    for k in ("pass_a", "stitch", "prep", "pass_b", "dp", "traceback", "pass_c", "reduce", "gather"):
+        phases[k] = ctx.stat("ms_" + k) / args.steps
+    launches = ctx.stat("kernel_launches")
+    cap = ctx.stat("cap")
+    geom = {"block_columns": int(ctx.stat("block_columns")), "blocks": int(ctx.stat("blocks")), "warps_per_block": int(ctx.stat("warps")), "cap": int(cap), "cap_retries": int(ctx.stat("cap_retries"))}
+
+    # ---- end to end: host rows -> C ABI -> host results ----
+    e2e = None
+    if not args.no_e2e:
+        rows_dev = torch.empty((m, n), dtype=torch.uint8, device="cuda:%d" % dev)
+        ctx.synth_rows_device(rows_dev.data_ptr(), n, m, n, my_seed, founders, gaps)
+        rows_host = torch.empty((m, n), dtype=torch.uint8, pin_memory=True)
+        rows_host.copy_(rows_dev)
+        del rows_dev
+        torch.cuda.synchronize(dev)
+        rows_np = rows_host.numpy()
+        comp = np.zeros(256, np.uint8)
+        for i, ch in enumerate(sorted(b"-ACGT" if gaps else b"ACGT")):
+            comp[ch] = i + 1
+
+        def e2e_step():
+            with ctx.msa_from_rows(rows_np, comp) as mm, ctx.segment(mm, L) as seg:
+                lb, rb, sz = seg.reduced_traceback()
+                a, d = seg.reduced_pbwt_samples_view()
+                return seg.max_segment_size, len(lb), lb.nbytes + rb.nbytes + sz.nbytes + a.nbytes + d.nbytes
+
+        e_steps = max(1, min(args.steps, 3))
+        e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            einfo = e2e_step()
+        barrier()
+        esecs = time.perf_counter() - t0
+        if dist is not None:
+            t = torch.tensor([esecs], device="cuda:%d" % dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            esecs = float(t.item())
+        assert einfo[:2] == info, (einfo, info)
+        dp_bytes = 3 * 4 * (n - L + 1)      # the DP table columns read back for the traceback
+        e2e = {"value": world * cells * e_steps / esecs, "unit": "cells/s", "h2d_bytes_per_step": m * n + 256,
+               "d2h_bytes_per_step": int(einfo[2]) + dp_bytes, "steps": e_steps}
+
+    if rank != 0:
+        msa.free()
+        ctx.close()
+        dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = measured_peak()
+    dom = max(("pass_a", "pass_b", "pass_c"), key=lambda k: phases[k])
+    ach = cells * BYTES_PER_CELL / (phases[dom] * 1e-3) / 1e9 if phases[dom] > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": "pbwt_block_kernel (%s)" % dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+                "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": cells * BYTES_PER_CELL, "launch_ms": phases[dom]}
+    line = {
+        "metric": METRIC, "value": world * cells * args.steps / secs, "unit": "cells/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": desc, "K": info[0], "segments": info[1], "inputs": "packed alignment %.0f MB per rank (> 126 MB L2), regenerated state per step" % (msa.m / 2 * n / 1e6),
+                   "parallelism": "1 GPU" if world == 1 else "independent alignments, one per rank (no collective)", **geom},
+        "phases_ms": phases, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
+    }
+    if e2e:
+        line["e2e"] = e2e
+    if not args.no_cpu_baseline:
+        use_ref = True
+        nc = sample_columns(m, True)
+        rows = make_rows_sample(np, torch, fsq, m, nc, seed, founders, gaps, True)
+        line["cpu_baseline"] = cpu_baseline(rows, L, use_ref)
+    print(json.dumps(line))
+    msa.free()
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -29,7 +29,7 @@ EXPORTS = [
     "fsq_msa_from_rows", "fsq_msa_from_device_rows", "fsq_msa_synth", "fsq_synth_rows_device", "fsq_msa_free",
     "fsq_msa_rows", "fsq_msa_columns", "fsq_pbwt_states", "fsq_segment", "fsq_segmentation_free",
     "fsq_segmentation_count", "fsq_segmentation_max_segment_size", "fsq_segmentation_bounds",
-    "fsq_segmentation_states", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
+    "fsq_segmentation_states", "fsq_segmentation_states_view", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
     "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights",
     "fsq_local_summary", "fsq_summary_free", "fsq_summary_device_pi", "fsq_summary_device_delta",
     "fsq_apply_summary",
@@ -83,6 +83,7 @@ def load_library():
     proto("fsq_segmentation_max_segment_size", u32, [vp])
     proto("fsq_segmentation_bounds", ci, [vp, vp, vp, vp])
     proto("fsq_segmentation_states", ci, [vp, vp, vp])
+    proto("fsq_segmentation_states_view", ci, [vp, pp, pp])
     proto("fsq_segmentation_traceback_count", u32, [vp])
     proto("fsq_segmentation_traceback", ci, [vp, vp, vp, vp, vp])
     proto("fsq_segmentation_dp_table", ci, [vp, vp, vp, vp, vp])
@@ -236,6 +237,15 @@ class Segmentation:
         a = np.zeros((self.count, self.m), np.uint32)
         d = np.zeros((self.count, self.m), np.uint32)
         self.ctx.check(self.ctx.lib.fsq_segmentation_states(self.h, _p(a), _p(d)))
+        return a, d
+
+    def reduced_pbwt_samples_view(self):
+        """Zero-copy views of the handle's pinned host buffers (valid until free())."""
+        pa, pd = C.c_void_p(), C.c_void_p()
+        self.ctx.check(self.ctx.lib.fsq_segmentation_states_view(self.h, C.byref(pa), C.byref(pd)))
+        shape = (self.count, self.m)
+        a = np.ctypeslib.as_array(C.cast(pa, C.POINTER(C.c_uint32)), shape)
+        d = np.ctypeslib.as_array(C.cast(pd, C.POINTER(C.c_uint32)), shape)
         return a, d
 
     def traceback(self):

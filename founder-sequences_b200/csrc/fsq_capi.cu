@@ -53,7 +53,7 @@ struct fsq_segmentation
 	std::vector <uint64_t> lb, rb;            // reduced
 	std::vector <uint32_t> size;
 	uint32_t *d_a{}, *d_d{};                  // reduced states on the device, count x m
-	std::vector <uint32_t> h_a, h_d;
+	uint32_t *h_a{}, *h_d{};                  // pinned host copies, made on first request
 	std::vector <uint64_t> tb_lb, tb_rb;      // traceback before reduction
 	std::vector <uint32_t> tb_max, tb_size;
 	std::vector <uint32_t> dp_lb, dp_max, dp_size;   // keep_dp
@@ -576,7 +576,7 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	CK(tb_max.alloc(dp_size * 4)); CK(tb_lb.alloc(dp_size * 4)); CK(tb_size.alloc(dp_size * 4));
 	CK(lev.alloc((size_t) n_levels * n_blk * 4)); CK(overflow.alloc(4));
 	CK(cnt.alloc(n * 4)); CK(h0.alloc(n * 4));
-	uint32_t cap = (uint32_t) std::min <int64_t>(m, std::max <int64_t>(1, ctx->opt("cap", 63)));
+	uint32_t cap = (uint32_t) std::min <int64_t>(m, std::max <int64_t>(1, ctx->opt("cap", 127)));
 	while (true)
 	{
 		CK(toplist.alloc((size_t) n * (cap + 1) * sizeof(uint2)));
@@ -620,6 +620,7 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 		if (0 == ovf) break;
 		if (cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list at column %u with cap = m", ovf - 1);
 		cap = (uint32_t) std::min <uint64_t>(m, (uint64_t) cap * 4);
+		ctx->opts["cap"] = cap;          // later calls on this context start from the bound that worked
 		ctx->stats["cap_retries"] += 1;
 	}
 	ctx->stats["cap"] = cap;
@@ -708,7 +709,7 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 
 	// ---- the reduced samples: device copy for the follow-on kernels, host copy for the joiners ----
 	{
-		phase pg(ctx, "gather_d2h");
+		phase pg(ctx, "gather");
 		uint32_t const cntS = (uint32_t) chosen.size();
 		dbuf d_idx;
 		CK(d_idx.alloc((size_t) cntS * 4));
@@ -719,10 +720,6 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 		gather_states_kernel <<<grid, 256, 0, ctx->stream>>>(st_a.as <uint32_t>(), st_d.as <uint32_t>(), d_idx.as <uint32_t>(), m, seg->d_a, seg->d_d);
 		CK(cudaGetLastError());
 		ctx->stats["kernel_launches"] += 1;
-		seg->h_a.resize((size_t) cntS * m);
-		seg->h_d.resize((size_t) cntS * m);
-		CK(cudaMemcpyAsync(seg->h_a.data(), seg->d_a, (size_t) cntS * m * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(seg->h_d.data(), seg->d_d, (size_t) cntS * m * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		pg.stop();
 		CK(cudaStreamSynchronize(ctx->stream));
 	}
@@ -737,6 +734,8 @@ void fsq_segmentation_free(fsq_segmentation *seg)
 	if (seg->ctx) cudaSetDevice(seg->ctx->device);
 	cudaFree(seg->d_a);
 	cudaFree(seg->d_d);
+	cudaFreeHost(seg->h_a);
+	cudaFreeHost(seg->h_d);
 	delete seg;
 }
 
@@ -752,11 +751,42 @@ int fsq_segmentation_bounds(const fsq_segmentation *seg, uint64_t *lb, uint64_t 
 	return FSQ_OK;
 }
 
-int fsq_segmentation_states(const fsq_segmentation *seg, uint32_t *a, uint32_t *d)
+static int fetch_states(fsq_segmentation *seg)
 {
+	fsq_ctx *ctx = seg->ctx;
+	if (seg->h_a) return FSQ_OK;
+	size_t const bytes = seg->lb.size() * (size_t) seg->m * 4;
+	CK(cudaSetDevice(ctx->device));
+	phase pd(ctx, "states_d2h");
+	CK(cudaMallocHost(&seg->h_a, bytes));
+	CK(cudaMallocHost(&seg->h_d, bytes));
+	CK(cudaMemcpyAsync(seg->h_a, seg->d_a, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(seg->h_d, seg->d_d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	pd.stop();
+	CK(cudaStreamSynchronize(ctx->stream));
+	return FSQ_OK;
+}
+
+int fsq_segmentation_states(const fsq_segmentation *cseg, uint32_t *a, uint32_t *d)
+{
+	fsq_segmentation *seg = const_cast <fsq_segmentation *>(cseg);
 	if (!seg || !a || !d) return FSQ_ERR_ARG;
-	std::copy(seg->h_a.begin(), seg->h_a.end(), a);
-	std::copy(seg->h_d.begin(), seg->h_d.end(), d);
+	int const rc = fetch_states(seg);
+	if (rc) return rc;
+	size_t const bytes = seg->lb.size() * (size_t) seg->m * 4;
+	memcpy(a, seg->h_a, bytes);
+	memcpy(d, seg->h_d, bytes);
+	return FSQ_OK;
+}
+
+int fsq_segmentation_states_view(const fsq_segmentation *cseg, const uint32_t **a, const uint32_t **d)
+{
+	fsq_segmentation *seg = const_cast <fsq_segmentation *>(cseg);
+	if (!seg || !a || !d) return FSQ_ERR_ARG;
+	int const rc = fetch_states(seg);
+	if (rc) return rc;
+	*a = seg->h_a;
+	*d = seg->h_d;
 	return FSQ_OK;
 }
 

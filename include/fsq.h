@@ -98,6 +98,9 @@ uint32_t fsq_segmentation_max_segment_size(const fsq_segmentation *seg);
 int fsq_segmentation_bounds(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *size);
 /* reduced_pbwt_samples[i].input_permutation() / input_divergence(); count × m each */
 int fsq_segmentation_states(const fsq_segmentation *seg, uint32_t *a, uint32_t *d);
+/* The same without the extra copy: pointers into pinned host memory owned by the handle (valid until it is freed).
+ * The device->host copy happens on the first call of either function. */
+int fsq_segmentation_states_view(const fsq_segmentation *seg, const uint32_t **a, const uint32_t **d);
 
 /* Test taps.  The traceback before reduction (segmentation_lp_context.cc:191-224): count, then lb/rb/max/size. */
 uint32_t fsq_segmentation_traceback_count(const fsq_segmentation *seg);
