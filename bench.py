@@ -245,7 +245,8 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
         phases[k] = ctx.stat("ms_" + k) / args.steps
     launches = ctx.stat("kernel_launches")
     cap = ctx.stat("cap")
-    geom = {"block_columns": int(ctx.stat("block_columns")), "blocks": int(ctx.stat("blocks")), "warps_per_block": int(ctx.stat("warps")), "cap": int(cap), "cap_retries": int(ctx.stat("cap_retries"))}
+    geom = {"block_columns": int(ctx.stat("block_columns")), "blocks": int(ctx.stat("blocks")), "warps_per_block": int(ctx.stat("warps")), "cap": int(cap), "cap_retries": int(ctx.stat("cap_retries")),
+            "chunk": int(ctx.stat("chunk")), "dp_chains": int(ctx.stat("dp_chunks")), "dp_rounds_per_step": ctx.stat("dp_rounds") / args.steps}
 
     # ---- end to end: host rows -> C ABI -> host results ----
     e2e = None

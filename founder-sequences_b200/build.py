@@ -14,7 +14,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libfsq_b200.so")
-SOURCES = ["fsq_capi.cu", "fsq_pbwt.cu", "fsq_dp.cu", "fsq_pack.cu"]
+SOURCES = ["fsq_capi.cu", "fsq_pbwt.cu", "fsq_dp.cu", "fsq_pack.cu", "fsq_bscan_e9.cu", "fsq_bscan_e17.cu", "fsq_bscan_e33.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
@@ -38,7 +38,7 @@ def _run(cmd):
 
 def build_library(force=False, verbose=False):
     os.makedirs(LIBDIR, exist_ok=True)
-    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh", ".inc"))]
     headers.append(os.path.join(ROOT, "include", "fsq.h"))
     objs, jobs = [], []
     for src in SOURCES:
@@ -48,7 +48,7 @@ def build_library(force=False, verbose=False):
         if force or _newer(o, [s] + headers):
             cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", s, "-o", o]
             jobs.append(cmd)
-    with ThreadPoolExecutor(max_workers=4) as ex:
+    with ThreadPoolExecutor(max_workers=8) as ex:
         for out in ex.map(_run, jobs):
             if verbose and out:
                 print(out)

@@ -41,6 +41,7 @@ struct fsq_msa
 	uint8_t *cols{};
 	uint64_t col_stride{};
 	uint32_t m{}, nsym{};
+	uint32_t sym_mask{};       // bit c set: comp value c occurs in some row
 	uint64_t n{}, col0{};
 };
 
@@ -124,11 +125,15 @@ void flush_phases(fsq_ctx *ctx)
 struct geometry
 {
 	uint32_t n_tiles, n_warps, tpw, C, cg, B;
+	// blocked column step (fsq_bstep.cuh): E elements per thread, T threads, symbols sym0 .. sym0 + ns - 1
+	bool blocked;
+	uint32_t E, T, ns, sym0;
 };
 
 geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 {
 	geometry g;
+	memset(&g, 0, sizeof g);
 	uint32_t const m = msa->m;
 	g.n_tiles = (m + 31) / 32;
 	int64_t w = ctx->opt("warps", 0);
@@ -141,12 +146,40 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 	g.tpw = (g.n_tiles + g.n_warps - 1) / g.n_warps;
 	while (g.tpw > 32 && g.n_warps < 32) { g.n_warps *= 2; g.tpw = (g.n_tiles + g.n_warps - 1) / g.n_warps; }
 
+	// The blocked step walks E consecutive positions per thread; it needs the symbols that occur to span at most 8 values.
+	uint32_t const mask = msa->sym_mask ? msa->sym_mask : ((1u << msa->nsym) - 1u);
+	uint32_t lo = 0, hi = 31;
+	while (!((mask >> lo) & 1u)) ++lo;
+	while (!((mask >> hi) & 1u)) --hi;
+	g.sym0 = lo;
+	g.ns = hi - lo + 1;
+	int64_t const kern = ctx->opt("kernel", 0);        // 0 auto, 1 striped, 2 blocked
+	g.blocked = (1 != kern) && g.ns <= 8 && m <= 448u * 33u;
+	uint32_t threads = g.n_warps * 32, regs = 64;
+	if (g.blocked)
+	{
+		int64_t e = ctx->opt("chunk", 0);
+		if (9 != e && 17 != e && 33 != e)
+			e = m <= 32 * 9 ? 9 : (m <= 32 * 17 ? 17 : 33);
+		uint32_t const tmax = 9 == e ? 1024 : (17 == e ? 512 : 448);
+		if ((uint64_t) tmax * e < m) e = 33;
+		g.E = (uint32_t) e;
+		g.T = ((m + g.E - 1) / g.E + 31) / 32 * 32;
+		threads = g.T;
+		regs = 9 == g.E ? 64 : 128;
+	}
+
 	g.cg = (uint32_t) std::max <uint64_t>(1, 2048 / msa->col_stride);
 	int64_t C = ctx->opt("block_columns", 0);
 	if (C <= 0)
 	{
 		// enough blocks to fill every SM a few times over, but long enough to amortise the two extra passes' fixed costs
-		uint64_t const resident = (uint64_t) ctx->prop.multiProcessorCount * std::max <uint32_t>(1, std::min <uint32_t>(32, 2048 / (g.n_warps * 32)));
+		uint64_t per_sm = std::min <uint64_t>(32, 2048 / threads);
+		per_sm = std::min <uint64_t>(per_sm, 65536 / ((uint64_t) threads * regs));
+		size_t const smem = 2 * (size_t) g.cg * msa->col_stride + 4 * (size_t) threads * (g.blocked ? g.E + 2 * g.ns : 1) + 2 * (size_t) m + 1024;
+		per_sm = std::min <uint64_t>(per_sm, (227 * 1024) / smem);
+		per_sm = std::max <uint64_t>(per_sm, 1);
+		uint64_t const resident = (uint64_t) ctx->prop.multiProcessorCount * per_sm;
 		C = (int64_t) ((msa->n + resident - 1) / resident);
 		C = std::max <int64_t>(C, 64);
 		C = std::min <int64_t>(C, 4096);
@@ -159,6 +192,18 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 	return g;
 }
 
+// One launch of the column-block scan in the geometry's flavour.
+cudaError_t launch_scan(block_args const &A, uint32_t n_blocks, geometry const &g, bool hist, cudaStream_t st)
+{
+	if (!g.blocked) return launch_block(A, n_blocks, g.n_warps, g.tpw, hist, st);
+	switch (g.E)
+	{
+		case 9: return launch_bblock_e9(A, n_blocks, g.T, g.ns, hist, st);
+		case 17: return launch_bblock_e17(A, n_blocks, g.T, g.ns, hist, st);
+		default: return launch_bblock_e33(A, n_blocks, g.T, g.ns, hist, st);
+	}
+}
+
 void fill_common(block_args &A, fsq_msa const *msa, geometry const &g)
 {
 	memset(&A, 0, sizeof A);
@@ -169,6 +214,7 @@ void fill_common(block_args &A, fsq_msa const *msa, geometry const &g)
 	A.m = msa->m;
 	A.n_tiles = g.n_tiles;
 	A.nsym = msa->nsym;
+	A.sym0 = g.sym0;
 	A.C = g.C;
 	A.cg = g.cg;
 }
@@ -195,7 +241,7 @@ __global__ void gather_states_kernel(uint32_t const *src_a, uint32_t const *src_
 struct scan_state
 {
 	geometry g;
-	dbuf sum_a, sum_d, st_a, st_d, code, oldvals, R, items;
+	dbuf sum_a, sum_d, rel_a, rel_d, st_a, st_d, code, oldvals, R, items, item_begin;
 };
 
 // Pass A (local scans), stitch, rank compression.  After this, st_[ad] hold the exact PBWT state at every block start.
@@ -220,35 +266,111 @@ int prepare_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
 		A.mode = MODE_LOCAL;
 		A.sum_a = S.sum_a.as <uint32_t>();
 		A.sum_d = S.sum_d.as <uint32_t>();
-		CK(launch_block(A, g.B - 1, g.n_warps, g.tpw, false, ctx->stream));
+		CK(launch_scan(A, g.B - 1, g, false, ctx->stream));
 		pa.stop();
 		ctx->stats["kernel_launches"] += 1;
 
+		// Stitch in three levels, because composing summaries is associative:
+		//   1. every group of G consecutive blocks composes its block summaries left to right (groups in parallel),
+		//      giving the state at each of its block starts relative to the group start;
+		//   2. one CTA chains the group summaries into the true states at the group starts;
+		//   3. every remaining block start = (true state at its group start) o (its group-relative state), all in parallel.
 		phase ps(ctx, "stitch");
-		std::vector <stitch_item> items(g.B - 1);
-		for (uint32_t b = 0; b + 1 < g.B; ++b)
+		uint32_t const B = g.B;
+		uint32_t G = (uint32_t) ctx->opt("stitch_group", 0);
+		if (0 == G) G = (uint32_t) std::ceil(std::sqrt((double) B));
+		G = std::max <uint32_t>(1, std::min(G, B));
+		uint32_t const Q = (B + G - 1) / G;
+		CK(S.rel_a.alloc(((size_t) B + 1) * m * 4)); CK(S.rel_d.alloc(((size_t) B + 1) * m * 4));
+		uint32_t *sum_a = S.sum_a.as <uint32_t>(), *sum_d = S.sum_d.as <uint32_t>();
+		uint32_t *rel_a = S.rel_a.as <uint32_t>(), *rel_d = S.rel_d.as <uint32_t>();
+		uint32_t *st_a = S.st_a.as <uint32_t>(), *st_d = S.st_d.as <uint32_t>();
+		auto start_of = [&](uint32_t b) { return (uint32_t) (msa->col0 + (uint64_t) b * g.C); };
+		// state at the start of block b relative to the start of its group (b not the first of the group); the one after
+		// the first block is that block's own summary
+		auto rel_ptr = [&](uint32_t b, uint32_t *&a, uint32_t *&d) {
+			uint32_t const b0 = (b - 1) / G * G;       // group of block b - 1: b may be one past the group's last block
+			if (b == b0 + 1) { a = sum_a + (size_t) b0 * m; d = sum_d + (size_t) b0 * m; }
+			else { a = rel_a + (size_t) b * m; d = rel_d + (size_t) b * m; }
+		};
+		std::vector <stitch_item> items;
+		std::vector <uint32_t> begin[3];
+		for (uint32_t q = 0; q < Q; ++q)
 		{
-			stitch_item &it = items[b];
-			memset(&it, 0, sizeof it);
-			it.in_a = S.st_a.as <uint32_t>() + (size_t) b * m;
-			it.in_d = S.st_d.as <uint32_t>() + (size_t) b * m;
-			it.pi = S.sum_a.as <uint32_t>() + (size_t) b * m;
-			it.delta = S.sum_d.as <uint32_t>() + (size_t) b * m;
-			it.out_a = S.st_a.as <uint32_t>() + (size_t) (b + 1) * m;
-			it.out_d = S.st_d.as <uint32_t>() + (size_t) (b + 1) * m;
-			it.s_mark = (uint32_t) (msa->col0 + (uint64_t) b * g.C);
+			uint32_t const b0 = q * G, b1 = std::min(B, b0 + G);
+			size_t const before = items.size();
+			for (uint32_t b = b0 + 1; b < b1 && b + 2 <= B; ++b)      // the last block has no summary: nothing follows it
+			{
+				// summary of [start(b0), start(b + 1)) = summary of [start(b0), start(b)) o summary of block b
+				stitch_item it;
+				memset(&it, 0, sizeof it);
+				uint32_t *ia, *id;
+				rel_ptr(b, ia, id);
+				it.in_a = ia; it.in_d = id;
+				it.pi = sum_a + (size_t) b * m; it.delta = sum_d + (size_t) b * m;
+				it.out_a = rel_a + (size_t) (b + 1) * m; it.out_d = rel_d + (size_t) (b + 1) * m;
+				it.s_mark = start_of(b);
+				items.push_back(it);
+			}
+			if (items.size() > before) begin[0].push_back((uint32_t) before);
 		}
+		begin[0].push_back((uint32_t) items.size());
+		size_t const n1 = items.size();
+		begin[1].push_back((uint32_t) n1);
+		for (uint32_t q = 0; q + 1 < Q; ++q)
+		{
+			uint32_t const b0 = q * G, b1 = b0 + G;
+			stitch_item it;
+			memset(&it, 0, sizeof it);
+			uint32_t *la, *ld;
+			rel_ptr(b1, la, ld);
+			it.in_a = st_a + (size_t) b0 * m; it.in_d = st_d + (size_t) b0 * m;
+			it.pi = la; it.delta = ld;
+			it.out_a = st_a + (size_t) b1 * m; it.out_d = st_d + (size_t) b1 * m;
+			it.s_mark = start_of(b0);
+			items.push_back(it);
+		}
+		begin[1].push_back((uint32_t) items.size());
+		for (uint32_t q = 0; q < Q; ++q)
+		{
+			uint32_t const b0 = q * G, b1 = std::min(B, b0 + G);
+			for (uint32_t b = b0 + 1; b < b1; ++b)
+			{
+				stitch_item it;
+				memset(&it, 0, sizeof it);
+				uint32_t *la, *ld;
+				rel_ptr(b, la, ld);
+				it.in_a = st_a + (size_t) b0 * m; it.in_d = st_d + (size_t) b0 * m;
+				it.pi = la; it.delta = ld;
+				it.out_a = st_a + (size_t) b * m; it.out_d = st_d + (size_t) b * m;
+				it.s_mark = start_of(b0);
+				begin[2].push_back((uint32_t) items.size());
+				items.push_back(it);
+			}
+		}
+		begin[2].push_back((uint32_t) items.size());
+		std::vector <uint32_t> begin_all;
+		size_t off[3];
+		for (int ph = 0; ph < 3; ++ph) { off[ph] = begin_all.size(); begin_all.insert(begin_all.end(), begin[ph].begin(), begin[ph].end()); }
 		CK(S.items.alloc(items.size() * sizeof(stitch_item)));
+		CK(S.item_begin.alloc(begin_all.size() * 4));
 		CK(cudaMemcpyAsync(S.items.p, items.data(), items.size() * sizeof(stitch_item), cudaMemcpyHostToDevice, ctx->stream));
-		CK(cudaStreamSynchronize(ctx->stream));     // items is a stack vector
-		stitch_args SA;
-		SA.items = S.items.as <stitch_item>();
-		SA.n_steps = g.B - 1;
-		SA.m = m;
-		SA.n_tiles = g.n_tiles;
-		CK(launch_stitch(SA, ctx->stream));
+		CK(cudaMemcpyAsync(S.item_begin.p, begin_all.data(), begin_all.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));     // items and begin_all are stack vectors
+		for (int ph = 0; ph < 3; ++ph)
+		{
+			uint32_t const n_ctas = (uint32_t) begin[ph].size() - 1;
+			if (0 == n_ctas || begin[ph].front() == begin[ph].back()) continue;
+			stitch_args SA;
+			SA.items = S.items.as <stitch_item>();
+			SA.item_begin = S.item_begin.as <uint32_t>() + off[ph];
+			SA.n_ctas = n_ctas;
+			SA.m = m;
+			SA.n_tiles = g.n_tiles;
+			CK(launch_stitch(SA, ctx->stream));
+			ctx->stats["kernel_launches"] += 1;
+		}
 		ps.stop();
-		ctx->stats["kernel_launches"] += 1;
 	}
 	{
 		phase pp(ctx, "prep");
@@ -296,7 +418,7 @@ int dump_states(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S, std::vector <ui
 	A.dump_begin = d_begin.as <uint32_t>();
 	A.dump_a = dump_a;
 	A.dump_d = dump_d;
-	CK(launch_block(A, (uint32_t) ids.size(), g.n_warps, g.tpw, false, ctx->stream));
+	CK(launch_scan(A, (uint32_t) ids.size(), g, false, ctx->stream));
 	pc.stop();
 	ctx->stats["kernel_launches"] += 1;
 	CK(cudaStreamSynchronize(ctx->stream));   // the three staging buffers die here
@@ -380,7 +502,7 @@ const char *fsq_last_error(const fsq_ctx *ctx) { return ctx ? ctx->error.c_str()
 int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
 {
 	if (!ctx || !key) return fail(ctx, FSQ_ERR_ARG, "null argument");
-	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", nullptr};
+	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", nullptr};
 	for (char const **k = known; *k; ++k)
 		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }
 	return fail(ctx, FSQ_ERR_ARG, "unknown option '%s'", key);
@@ -419,16 +541,19 @@ int fsq_msa_from_device_rows(fsq_ctx *ctx, const uint8_t *d_rows, uint64_t row_s
 	if (rc) return rc;
 	fsq_msa *msa = nullptr;
 	if ((rc = new_msa(ctx, m, n, 0, nsym, &msa))) return rc;
-	dbuf d_comp;
+	dbuf d_comp, d_mask;
 	cudaError_t e = d_comp.alloc(256);
+	if (cudaSuccess == e) e = d_mask.alloc(4);
+	if (cudaSuccess == e) e = cudaMemsetAsync(d_mask.p, 0, 4, ctx->stream);
 	if (cudaSuccess == e) e = cudaMemcpyAsync(d_comp.p, comp, 256, cudaMemcpyHostToDevice, ctx->stream);
 	if (cudaSuccess == e)
 	{
 		phase pk(ctx, "pack");
-		e = launch_pack(d_rows, row_stride, m, n, d_comp.as <uint8_t>(), msa->cols, msa->col_stride, 0, ctx->stream);
+		e = launch_pack(d_rows, row_stride, m, n, d_comp.as <uint8_t>(), msa->cols, msa->col_stride, 0, d_mask.as <uint32_t>(), ctx->stream);
 		pk.stop();
 		ctx->stats["kernel_launches"] += 1;
 	}
+	if (cudaSuccess == e) e = cudaMemcpyAsync(&msa->sym_mask, d_mask.p, 4, cudaMemcpyDeviceToHost, ctx->stream);
 	if (cudaSuccess == e) e = cudaStreamSynchronize(ctx->stream);
 	if (cudaSuccess != e) { fsq_msa_free(msa); return fail(ctx, FSQ_ERR_CUDA, "pack: %s", cudaGetErrorString(e)); }
 	*out = msa;
@@ -462,9 +587,11 @@ int fsq_msa_from_rows(fsq_ctx *ctx, const uint8_t *const *rows, uint32_t m, uint
 	// Rows go up in column chunks through a device staging matrix (row-major, m x chunk), then get packed.
 	uint64_t const chunk = std::max <uint64_t>(32, std::min <uint64_t>(n, ((256ull << 20) / m) & ~31ull));
 	uint64_t const row_stride = (chunk + 15) & ~15ull;
-	dbuf stage, d_comp;
+	dbuf stage, d_comp, d_mask;
 	cudaError_t e = stage.alloc((size_t) m * row_stride);
 	if (cudaSuccess == e) e = d_comp.alloc(256);
+	if (cudaSuccess == e) e = d_mask.alloc(4);
+	if (cudaSuccess == e) e = cudaMemsetAsync(d_mask.p, 0, 4, ctx->stream);
 	if (cudaSuccess == e) e = cudaMemcpyAsync(d_comp.p, comp, 256, cudaMemcpyHostToDevice, ctx->stream);
 	phase pk(ctx, "h2d_pack");
 	for (uint64_t c0 = 0; c0 < n && cudaSuccess == e; c0 += chunk)
@@ -479,10 +606,11 @@ int fsq_msa_from_rows(fsq_ctx *ctx, const uint8_t *const *rows, uint32_t m, uint
 		else
 			for (uint32_t r = 0; r < m && cudaSuccess == e; ++r)
 				e = cudaMemcpyAsync(stage.as <uint8_t>() + (size_t) r * row_stride, rows[r] + c0, nc, cudaMemcpyHostToDevice, ctx->stream);
-		if (cudaSuccess == e) e = launch_pack(stage.as <uint8_t>(), row_stride, m, nc, d_comp.as <uint8_t>(), msa->cols, msa->col_stride, c0, ctx->stream);
+		if (cudaSuccess == e) e = launch_pack(stage.as <uint8_t>(), row_stride, m, nc, d_comp.as <uint8_t>(), msa->cols, msa->col_stride, c0, d_mask.as <uint32_t>(), ctx->stream);
 		ctx->stats["kernel_launches"] += 1;
 	}
 	pk.stop();
+	if (cudaSuccess == e) e = cudaMemcpyAsync(&msa->sym_mask, d_mask.p, 4, cudaMemcpyDeviceToHost, ctx->stream);
 	if (cudaSuccess == e) e = cudaStreamSynchronize(ctx->stream);
 	if (cudaSuccess != e) { fsq_msa_free(msa); return fail(ctx, FSQ_ERR_CUDA, "upload/pack: %s", cudaGetErrorString(e)); }
 	*out = msa;
@@ -500,6 +628,7 @@ int fsq_msa_synth(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint64_t 
 	if (cudaSuccess == e) e = cudaStreamSynchronize(ctx->stream);
 	if (cudaSuccess != e) { fsq_msa_free(msa); return fail(ctx, FSQ_ERR_CUDA, "synth: %s", cudaGetErrorString(e)); }
 	ctx->stats["kernel_launches"] += 1;
+	msa->sym_mask = gaps ? 0x3eu : 0x1eu;      // comps 1..5 ('-', A, C, G, T) or 1..4
 	*out = msa;
 	return FSQ_OK;
 }
@@ -569,21 +698,39 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 
 	// ---- pass B + DP; the top-list bound grows until the DP proves the result exact ----
 	uint64_t const dp_size = n - L + 1;
+	uint32_t const n_entries = (uint32_t) (n - 2 * L + 1);
 	uint32_t const n_blk = (uint32_t) (dp_size / 64 + 1);
 	uint32_t n_levels = 1;
 	while ((1ull << n_levels) <= n_blk) ++n_levels;
-	dbuf tb_max, tb_lb, tb_size, lev, overflow, cnt, h0, toplist;
-	CK(tb_max.alloc(dp_size * 4)); CK(tb_lb.alloc(dp_size * 4)); CK(tb_size.alloc(dp_size * 4));
-	CK(lev.alloc((size_t) n_levels * n_blk * 4)); CK(overflow.alloc(4));
+	dbuf tb_max, tb_lb, tb_size, mk, lev, flags, chunk_level, cnt, h0, toplist;
+	CK(tb_max.alloc(dp_size * 4)); CK(tb_lb.alloc(dp_size * 4)); CK(tb_size.alloc(dp_size * 4)); CK(mk.alloc(dp_size * 8));
+	CK(lev.alloc((size_t) n_levels * n_blk * 4)); CK(flags.alloc(16));
 	CK(cnt.alloc(n * 4)); CK(h0.alloc(n * 4));
+	// chains: enough to fill the device a few times over, each a whole number of 64-entry rmq blocks
+	uint32_t chunk, n_chunks;
+	{
+		int64_t want = ctx->opt("dp_chunks", 0);
+		if (want <= 0) want = 4 * (int64_t) ctx->prop.multiProcessorCount;
+		uint64_t c = (n_entries + (uint64_t) want - 1) / (uint64_t) want;
+		c = std::max <uint64_t>(c, std::max <uint64_t>(256, 8 * L));
+		if (1 == want) c = n_entries;
+		c = (c + 63) / 64 * 64;
+		chunk = (uint32_t) std::min <uint64_t>(c, 0xffffffc0ull);
+		n_chunks = (n_entries + chunk - 1) / chunk;
+	}
+	CK(chunk_level.alloc((size_t) n_chunks * 8));
 	uint32_t cap = (uint32_t) std::min <int64_t>(m, std::max <int64_t>(1, ctx->opt("cap", 127)));
 	while (true)
 	{
 		CK(toplist.alloc((size_t) n * (cap + 1) * sizeof(uint2)));
+		// entries the per-column DP writes start from 0 (the first round's stand-in for "nothing known"); the ones the
+		// reference never writes keep its defaults; masks and rmq cells start from values that index inside the table
 		CK(cudaMemsetAsync(tb_max.p, 0xff, dp_size * 4, ctx->stream));
+		CK(cudaMemsetAsync(tb_max.p, 0, (size_t) n_entries * 4, ctx->stream));
 		CK(cudaMemsetAsync(tb_size.p, 0xff, dp_size * 4, ctx->stream));
 		CK(cudaMemsetAsync(tb_lb.p, 0, dp_size * 4, ctx->stream));
-		CK(cudaMemsetAsync(overflow.p, 0, 4, ctx->stream));
+		CK(cudaMemsetAsync(mk.p, 0xff, dp_size * 8, ctx->stream));
+		CK(cudaMemsetAsync(lev.p, 0, (size_t) n_levels * n_blk * 4, ctx->stream));
 		{
 			phase pb(ctx, "pass_b");
 			block_args A;
@@ -597,10 +744,11 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 			A.cap = cap;
 			A.cnt = cnt.as <uint32_t>();
 			A.h0 = h0.as <uint32_t>();
-			CK(launch_block(A, g.B, g.n_warps, g.tpw, true, ctx->stream));
+			CK(launch_scan(A, g.B, g, true, ctx->stream));
 			pb.stop();
 			ctx->stats["kernel_launches"] += 1;
 		}
+		uint32_t ovf = 0;
 		{
 			phase pd(ctx, "dp");
 			dp_args D;
@@ -608,15 +756,51 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 			D.m = m; D.n = n; D.L = L;
 			D.toplist = toplist.as <uint2>(); D.cap = cap; D.cnt = cnt.as <uint32_t>(); D.h0 = h0.as <uint32_t>();
 			D.tb_max = tb_max.as <uint32_t>(); D.tb_lb = tb_lb.as <uint32_t>(); D.tb_size = tb_size.as <uint32_t>();
+			D.mk = mk.as <uint64_t>();
 			D.lev = lev.as <uint32_t>(); D.n_blk = n_blk; D.n_levels = n_levels;
-			D.overflow = overflow.as <uint32_t>();
-			CK(launch_dp(D, ctx->stream));
-			pd.stop();
+			D.n_entries = n_entries; D.chunk = chunk; D.n_chunks = n_chunks;
+			D.chunk_level = chunk_level.as <uint32_t>();
+			D.flags = flags.as <uint32_t>();
+			uint32_t h_flags[2] = {0, 0};
+			int64_t const max_rounds = std::max <int64_t>(2, ctx->opt("dp_max_rounds", 16));
+			int64_t const guess_rounds = ctx->opt("dp_guess_rounds", 8);      // after these the table is left to settle by itself
+			uint32_t rounds = 0;
+			CK(cudaMemsetAsync(flags.p, 0, 16, ctx->stream));
+			while (true)
+			{
+				CK(cudaMemsetAsync(flags.p, 0, 8, ctx->stream));
+				CK(launch_dp_chains(D, ctx->stream));
+				ctx->stats["kernel_launches"] += 1;
+				++rounds;
+				if (1 == D.n_chunks) break;             // a single chain is the reference's own order: exact as it stands
+				if (rounds > 1)
+				{
+					CK(cudaMemcpyAsync(h_flags, flags.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+					CK(cudaStreamSynchronize(ctx->stream));
+					if (0 == h_flags[0]) break;         // nothing changed: every entry was computed from the table it is part of
+				}
+				if (rounds >= max_rounds)
+				{
+					// the guesses keep failing: one chain over everything, exact in a single round
+					D.chunk = (n_entries + 63) / 64 * 64;
+					D.n_chunks = 1;
+					ctx->stats["dp_fallbacks"] += 1;
+				}
+				else if (rounds <= guess_rounds)
+				{
+					CK(launch_dp_guess(D, ctx->stream));
+					ctx->stats["kernel_launches"] += 4 + n_levels;
+				}
+			}
+			CK(launch_dp_final(D, ctx->stream));
 			ctx->stats["kernel_launches"] += 1;
+			ctx->stats["dp_rounds"] += rounds;
+			ctx->stats["dp_chunks"] = n_chunks;
+			pd.stop();
+			CK(cudaMemcpyAsync(h_flags, flags.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+			CK(cudaStreamSynchronize(ctx->stream));
+			ovf = h_flags[1];
 		}
-		uint32_t ovf = 0;
-		CK(cudaMemcpyAsync(&ovf, overflow.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaStreamSynchronize(ctx->stream));
 		if (0 == ovf) break;
 		if (cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list at column %u with cap = m", ovf - 1);
 		cap = (uint32_t) std::min <uint64_t>(m, (uint64_t) cap * 4);
@@ -626,7 +810,8 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	ctx->stats["cap"] = cap;
 	ctx->stats["block_columns"] = g.C;
 	ctx->stats["blocks"] = g.B;
-	ctx->stats["warps"] = g.n_warps;
+	ctx->stats["warps"] = g.blocked ? g.T / 32 : g.n_warps;
+	ctx->stats["chunk"] = g.blocked ? g.E : 0;
 
 	// ---- traceback (reference: segmentation_lp_context.cc:191-224) ----
 	fsq_segmentation *seg = new (std::nothrow) fsq_segmentation;

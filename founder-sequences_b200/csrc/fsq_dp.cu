@@ -9,40 +9,72 @@ namespace fsq {
 // lev[0][b]  = leftmost argmin of entries [64 b, 64 b + 64)
 // lev[p][i]  = (M[lev[0][i + 2^p - 1]] < M[lev[p-1][i]]) ? lev[0][i + 2^p - 1] : lev[p-1][i]
 //              -- rmq.hh:76-77 reads the same cell twice, so level p covers blocks {i, i+1, i+3, ..., i+2^p-1} only.
+// The reference's linear scans inside a 64-block (naive_min, rmq.hh:86-118) are answered in O(1) from a per-entry
+// mask: bit j of mk[t] is set iff entry 64 b + j (j <= t mod 64, b = t / 64) is <= every later entry up to t; the
+// lowest set bit at or above a position is then the leftmost minimum of [position, t].
 
-__device__ __forceinline__ uint32_t naive_min(uint32_t const *M, uint32_t first, uint32_t last)
+__device__ __forceinline__ uint32_t inblock_min(uint64_t const *mk, uint32_t first, uint32_t last)
 {
-	uint32_t best = first, bv = M[first];
-	for (uint32_t i = first + 1; i < last; ++i)
-	{
-		uint32_t const v = M[i];
-		if (v < bv) { bv = v; best = i; }
-	}
-	return best;
+	unsigned long long const msk = mk[last] & (~0ull << (first & 63u));
+	return (last & ~63u) + (uint32_t) __ffsll((long long) msk) - 1u;
 }
 
-__device__ __forceinline__ uint32_t rmq_query(uint32_t const *M, uint32_t const *lev, uint32_t n_blk, uint32_t beg, uint32_t end)
+__device__ __forceinline__ uint32_t rmq_query(uint32_t const *M, uint64_t const *mk, uint32_t const *lev, uint32_t n_blk, uint32_t beg, uint32_t end)
 {
 	uint32_t const bb = beg / 64 + 1;
 	uint32_t const eb = end / 64;
+	uint32_t const last = end - 1;
 	if (bb >= eb)
-		return naive_min(M, beg, end);
+	{
+		// naive_min(beg, end): at most two consecutive blocks
+		if ((beg >> 6) == (last >> 6))
+			return inblock_min(mk, beg, last);
+		uint32_t const left = inblock_min(mk, beg, beg | 63u);
+		uint32_t const right = inblock_min(mk, last & ~63u, last);
+		return (M[right] < M[left]) ? right : left;
+	}
 	uint32_t const p = 31u - __clz(eb - bb);
 	uint32_t const s1 = lev[(size_t) p * n_blk + bb];
 	uint32_t const s2 = lev[(size_t) p * n_blk + eb - (1u << p)];
 	uint32_t smp = (M[s2] < M[s1]) ? s2 : s1;
-	uint32_t const left = naive_min(M, beg, bb * 64);
+	uint32_t const left = inblock_min(mk, beg, beg | 63u);
 	smp = (M[left] < M[smp]) ? left : smp;
 	if (end == eb * 64)
 		return smp;
-	uint32_t const right = naive_min(M, eb * 64, end);
+	uint32_t const right = inblock_min(mk, eb * 64, last);
 	return (M[right] < M[smp]) ? right : smp;
+}
+
+// mk[t] from the table; one warp.  Returns the mask in every lane.
+__device__ __forceinline__ unsigned long long make_mask(uint32_t const *M, uint32_t t)
+{
+	uint32_t const lane = lane_id();
+	uint32_t const blk = t & ~63u, tt = t & 63u;
+	uint32_t const v0 = lane <= tt ? M[blk + lane] : 0xffffffffu;
+	uint32_t const v1 = lane + 32 <= tt ? M[blk + 32 + lane] : 0xffffffffu;
+	uint32_t s0 = v0, s1 = v1;          // inclusive suffix minima inside each half (shfl_down returns the own value past lane 31)
+#pragma unroll
+	for (int o = 1; o < 32; o <<= 1)
+	{
+		s0 = min(s0, __shfl_down_sync(FSQ_FULL, s0, o));
+		s1 = min(s1, __shfl_down_sync(FSQ_FULL, s1, o));
+	}
+	uint32_t const hi_all = __shfl_sync(FSQ_FULL, s1, 0);
+	uint32_t e0 = __shfl_down_sync(FSQ_FULL, s0, 1);
+	uint32_t e1 = __shfl_down_sync(FSQ_FULL, s1, 1);
+	e0 = (31 == lane) ? hi_all : min(e0, hi_all);
+	e1 = (31 == lane) ? 0xffffffffu : e1;
+	uint32_t const b0 = __ballot_sync(FSQ_FULL, lane <= tt && v0 <= e0);
+	uint32_t const b1 = __ballot_sync(FSQ_FULL, lane + 32 <= tt && v1 <= e1);
+	return (unsigned long long) b0 | ((unsigned long long) b1 << 32);
 }
 
 // One column of calculate_segmentation_lp_dp_arg (reference: founder-sequences/segmentation_lp_context.cc:393-481),
 // evaluated by one warp over the column's top list.  Only ranges whose segment size S is <= cap are listed; any
 // other range has a candidate value > cap, so the result is exact whenever it is <= cap (or the list is complete).
-__device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, uint64_t const t_out)
+// The list is in descending order of the divergence value, i.e. ascending S, and a candidate is worth at least its
+// S: once S exceeds the best value so far nothing later can win or tie.
+__device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, uint64_t const t_out, uint32_t &reach)
 {
 	uint32_t const lane = lane_id();
 	uint32_t const L = (uint32_t) A.L;
@@ -54,8 +86,11 @@ __device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, ui
 
 	unsigned long long best = ~0ull;
 	uint32_t best_idx = 0, best_S = 0;
+	uint32_t far = (uint32_t) t_out;      // the lowest table entry a candidate looked at
 	for (uint32_t t0 = 1; t0 < E; t0 += 32)
 	{
+		if ((uint32_t) (best >> 32) < list[t0].y)
+			break;
 		uint32_t const t = t0 + lane;
 		unsigned long long key = ~0ull;
 		uint32_t idx = 0, S = 0;
@@ -70,7 +105,8 @@ __device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, ui
 				uint32_t const hi = min(up, hi_clip);
 				if (lo < hi)
 				{
-					idx = rmq_query(A.tb_max, A.lev, A.n_blk, lo - L, hi - L);
+					far = min(far, lo - L);
+					idx = rmq_query(A.tb_max, A.mk, A.lev, A.n_blk, lo - L, hi - L);
 					uint32_t const val = max(A.tb_max[idx], S);
 					key = ((unsigned long long) val << 32) | (0xffffffffu - t);   // ties: the lowest range (largest t) wins
 				}
@@ -91,6 +127,8 @@ __device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, ui
 			best_S = __shfl_sync(FSQ_FULL, S, owner);
 		}
 	}
+	far = __reduce_min_sync(FSQ_FULL, far);
+	reach = max(reach, (uint32_t) t_out - far);
 	if (0 == lane)
 	{
 		uint32_t const h0 = A.h0[k];
@@ -99,74 +137,184 @@ __device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, ui
 		uint32_t lb = 0, mx = whole, sz = whole;
 		if (~0ull != best && best_val < whole) { lb = best_idx + L; mx = best_val; sz = best_S; }
 		if (!complete && mx > A.cap)
-			atomicMax(A.overflow, (uint32_t) (k + 1));
-		A.tb_max[t_out] = mx;
+			atomicMax(&A.flags[1], (uint32_t) (k + 1));
+		if (A.tb_max[t_out] != mx) { A.tb_max[t_out] = mx; A.flags[0] = 1; }
 		A.tb_lb[t_out] = lb;
 		A.tb_size[t_out] = sz;
 	}
 }
 
-// First pass staging (reference: segmentation_lp_context.cc:26-188).  Column k reads only table entries
-// <= k + 1 - 2L, so L consecutive columns are independent: one wavefront = up to 32 columns, one warp each.
-__global__ void __launch_bounds__(1024) dp_kernel(dp_args const A)
+// First pass staging (reference: segmentation_lp_context.cc:26-188).  Entry t (column t + L - 1) reads only
+// entries <= t - L, so L consecutive entries are independent of one another: a wavefront.  The n / L wavefronts
+// form a serial chain; to run it in parallel the table is cut into chunks and every chunk's chain is run at the same
+// time against the table as it stands -- its own entries as it computes them, earlier chunks' entries as a previous
+// round left them.  A round that changes no stored value has computed every entry from a table it agrees with,
+// which by induction over the entries is the reference's table; until then rounds repeat (the first chunk is exact
+// after one round, so at most n_chunks rounds are needed; the guess after the first round makes it two or three).
+// Everything stored is written by exactly one chain: entries, masks and level-0 cells by the chunk's owner, a cell
+// lev[p][i] by the owner of block i + 2^p - 1, whose completion defines it (rmq.hh:61-84).
+__global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 {
 	uint32_t const warp = threadIdx.x >> 5;
+	uint32_t const n_warps = blockDim.x >> 5;
 	uint32_t const lane = lane_id();
-	uint64_t const n = A.n, L = A.L;
-	uint64_t const k_first = L - 1, k_last = n - L - 1;
-	uint32_t const WF = (uint32_t) (L < 32 ? L : 32);
+	uint32_t const L = (uint32_t) A.L;
+	uint32_t const W = L < 64 ? L : 64;
+	uint32_t const t_begin = blockIdx.x * A.chunk;
+	uint32_t const t_end = min(A.n_entries, t_begin + A.chunk);
+	uint32_t reach = 0;
 
-	for (uint64_t k0 = k_first; k0 <= k_last; k0 += WF)
+	for (uint32_t t0 = t_begin; t0 < t_end; t0 += W)
 	{
-		uint64_t const k = k0 + warp;
-		if (warp < WF && k <= k_last)
-			dp_column(A, k, k + 1 - L);
+		uint32_t const t1 = min(t_end, t0 + W);
+		for (uint32_t t = t0 + warp; t < t1; t += n_warps)
+			dp_column(A, (uint64_t) t + L - 1, t, reach);
 		__syncthreads();
 
-		// rmq.update for every entry written in this wavefront (rmq.hh:61-84)
-		uint64_t const t_lo = k0 + 1 - L;
-		uint64_t const k_hi = (k0 + WF - 1 < k_last) ? k0 + WF - 1 : k_last;
-		uint64_t const t_hi = k_hi + 1 - L;
+		// masks of the new entries; then rmq.update for the block that completed, if one did (W <= 64: at most one)
+		for (uint32_t t = t0 + warp; t < t1; t += n_warps)
 		{
-			// a block b completes when entry 64 b + 63 is written; at most one per wavefront (WF <= 32)
-			uint64_t const b64 = (t_hi + 1) / 64;           // number of complete blocks now
-			if (b64 > 0 && 64 * b64 - 1 >= t_lo)
-			{
-				uint32_t const b = (uint32_t) (b64 - 1);
-				if (0 == warp)
-				{
-					uint32_t const i0 = 64 * b + lane, i1 = i0 + 32;
-					uint32_t const v0 = A.tb_max[i0], v1 = A.tb_max[i1];
-					unsigned long long key = (v1 < v0) ? (((unsigned long long) v1 << 32) | i1) : (((unsigned long long) v0 << 32) | i0);
-#pragma unroll
-					for (int o = 16; o > 0; o >>= 1)
-					{
-						unsigned long long const other = __shfl_xor_sync(FSQ_FULL, key, o);
-						key = other < key ? other : key;
-					}
-					uint32_t const smp0 = (uint32_t) key;            // leftmost minimal entry of the block
-					uint32_t const val0 = (uint32_t) (key >> 32);
-					if (0 == lane) A.lev[b] = smp0;
-					uint32_t const p = lane;
-					if (p >= 1 && p < A.n_levels && (1ull << p) <= (uint64_t) b + 1)
-					{
-						uint32_t const i = b + 1 - (1u << p);
-						uint32_t const prev = A.lev[(size_t) (p - 1) * A.n_blk + i];
-						A.lev[(size_t) p * A.n_blk + i] = (val0 < A.tb_max[prev]) ? smp0 : prev;
-					}
-				}
-			}
+			unsigned long long const msk = make_mask(A.tb_max, t);
+			if (0 == lane && A.mk[t] != msk) { A.mk[t] = msk; A.flags[0] = 1; }
 		}
 		__syncthreads();
+		if (0 == warp && (t1 >> 6) != (t0 >> 6))
+		{
+			uint32_t const b = (t1 >> 6) - 1;
+			uint32_t const smp0 = 64 * b + (uint32_t) __ffsll((long long) A.mk[64 * b + 63]) - 1u;      // leftmost minimal entry of the block
+			uint32_t const val0 = A.tb_max[smp0];
+			uint32_t const p = lane;
+			if (0 == p)
+			{
+				if (A.lev[b] != smp0) { A.lev[b] = smp0; A.flags[0] = 1; }
+			}
+			else if (p < A.n_levels && (1ull << p) <= (uint64_t) b + 1)
+			{
+				uint32_t const i = b + 1 - (1u << p);
+				uint32_t const prev = A.lev[(size_t) (p - 1) * A.n_blk + i];
+				uint32_t const res = (val0 < A.tb_max[prev]) ? smp0 : prev;
+				uint32_t *cell = &A.lev[(size_t) p * A.n_blk + i];
+				if (*cell != res) { *cell = res; A.flags[0] = 1; }
+			}
+		}
+		// the next wavefront's queries may read what was just written
+		__syncthreads();
 	}
-	// segmentation_lp_context.cc:165-185: the final column, from the final histogram
-	if (0 == warp)
-		dp_column(A, n - 1, n - L);
+	if (0 == lane && reach) atomicMax(&A.flags[2], reach);
 }
 
-cudaError_t launch_dp(dp_args const &A, cudaStream_t st)
+cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st)
 {
-	dp_kernel <<<1, 1024, 0, st>>>(A);
+	// one warp per column of a wavefront, in as few equal passes as 16 warps allow
+	uint32_t const W = (uint32_t) (A.L < 64 ? A.L : 64);
+	uint32_t const passes = (W + 15) / 16;
+	uint32_t const n_warps = (W + passes - 1) / passes;
+	dp_chain_kernel <<<A.n_chunks, n_warps * 32, 0, st>>>(A);
+	return cudaGetLastError();
+}
+
+// segmentation_lp_context.cc:165-185: the final column, from the final histogram
+__global__ void dp_final_kernel(dp_args const A)
+{
+	uint32_t reach = 0;
+	dp_column(A, A.n - 1, A.n - A.L, reach);
+}
+
+cudaError_t launch_dp_final(dp_args const &A, cudaStream_t st)
+{
+	dp_final_kernel <<<1, 32, 0, st>>>(A);
+	return cudaGetLastError();
+}
+
+// ---- the guess between rounds -------------------------------------------------------------------------------------------
+// A chain that starts from a wrong idea of the entries before its chunk only repairs its own chunk, so a correction
+// would travel one chunk per round.  What travels is a level: an entry is max(an earlier entry within reach, a segment
+// size) >= the smallest entry within reach, so the minimum over a window as long as the reach never decreases along the
+// table and bounds every later entry from below.  After a round, every entry is therefore raised to the window minimum
+// at the end of the chunk before it (computed from values that are themselves at most the true ones).  Any guess is
+// allowed -- only a round that changes nothing ends the iteration -- a good one saves rounds.
+__global__ void __launch_bounds__(128) dp_chunk_level_kernel(dp_args const A)
+{
+	__shared__ uint32_t wmin[4];
+	uint32_t const c = blockIdx.x;
+	uint32_t const end = min(A.n_entries, (c + 1) * A.chunk);
+	uint32_t const D = 2 * A.flags[2] + 64;          // twice the farthest look-back seen so far
+	uint32_t const begin = end > D ? end - D : 0;
+	uint32_t v = 0xffffffffu;
+	for (uint32_t t = begin + threadIdx.x; t < end; t += blockDim.x) v = min(v, A.tb_max[t]);
+	v = __reduce_min_sync(FSQ_FULL, v);
+	if (0 == lane_id()) wmin[threadIdx.x >> 5] = v;
+	__syncthreads();
+	if (0 == threadIdx.x) A.chunk_level[A.n_chunks + c] = min(min(wmin[0], wmin[1]), min(wmin[2], wmin[3]));
+}
+
+// chunk_level[c] = max over c' < c of the window minimum at the end of chunk c'
+__global__ void __launch_bounds__(1024) dp_level_kernel(dp_args const A)
+{
+	__shared__ uint32_t carry;
+	__shared__ uint32_t wmax[32];
+	uint32_t const lane = lane_id(), warp = threadIdx.x >> 5;
+	if (0 == threadIdx.x) carry = 0;
+	__syncthreads();
+	for (uint32_t c0 = 0; c0 < A.n_chunks; c0 += blockDim.x)
+	{
+		uint32_t const c = c0 + threadIdx.x;
+		uint32_t const v = c < A.n_chunks ? A.chunk_level[A.n_chunks + c] : 0u;
+		uint32_t s = v;                                    // inclusive running maximum inside the warp
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1)
+			s = max(s, __shfl_up_sync(FSQ_FULL, s, o));      // shfl_up returns the own value below lane o
+		if (31 == lane) wmax[warp] = s;
+		__syncthreads();
+		uint32_t before = carry;
+		for (uint32_t w = 0; w < warp; ++w) before = max(before, wmax[w]);
+		uint32_t const incl = max(before, s);
+		uint32_t const prev = __shfl_up_sync(FSQ_FULL, incl, 1);
+		if (c < A.n_chunks) A.chunk_level[c] = (0 == lane) ? before : prev;      // exclusive
+		__syncthreads();
+		if (blockDim.x - 1 == threadIdx.x) carry = incl;
+		__syncthreads();
+	}
+}
+
+__global__ void dp_raise_kernel(dp_args const A)
+{
+	uint32_t const t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= A.n_entries) return;
+	uint32_t const lvl = A.chunk_level[t / A.chunk];
+	if (A.tb_max[t] < lvl) A.tb_max[t] = lvl;
+}
+
+__global__ void dp_masks_kernel(dp_args const A)
+{
+	uint32_t const t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (t >= A.n_entries) return;
+	unsigned long long const msk = make_mask(A.tb_max, t);
+	if (0 == lane_id()) A.mk[t] = msk;
+}
+
+// Level p of the rmq tables for every cell whose defining block is complete.
+__global__ void dp_levels_kernel(dp_args const A, uint32_t p)
+{
+	uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t const n_complete = A.n_entries / 64;
+	uint64_t const b = (uint64_t) i + (1ull << p) - 1;       // the block whose completion defines lev[p][i]
+	if (b >= n_complete) return;
+	uint32_t const smp0 = 64 * (uint32_t) b + (uint32_t) __ffsll((long long) A.mk[64 * b + 63]) - 1u;
+	if (0 == p) { A.lev[i] = smp0; return; }
+	uint32_t const prev = A.lev[(size_t) (p - 1) * A.n_blk + i];
+	A.lev[(size_t) p * A.n_blk + i] = (A.tb_max[smp0] < A.tb_max[prev]) ? smp0 : prev;
+}
+
+cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st)
+{
+	dp_chunk_level_kernel <<<A.n_chunks, 128, 0, st>>>(A);
+	dp_level_kernel <<<1, 1024, 0, st>>>(A);
+	dp_raise_kernel <<<(A.n_entries + 255) / 256, 256, 0, st>>>(A);
+	dp_masks_kernel <<<(A.n_entries + 7) / 8, 256, 0, st>>>(A);
+	uint32_t const n_complete = A.n_entries / 64;
+	for (uint32_t p = 0; p < A.n_levels && (1ull << p) <= n_complete; ++p)
+		dp_levels_kernel <<<(n_complete + 255) / 256, 256, 0, st>>>(A, p);
 	return cudaGetLastError();
 }
 

@@ -20,6 +20,7 @@ struct block_args
 	uint64_t n_local;          // columns held
 	uint64_t col0;             // global index of local column 0
 	uint32_t m, n_tiles, nsym;
+	uint32_t sym0;             // smallest symbol value that occurs (1 when NUL is absent); blocked kernels use nsym - sym0 symbols
 	uint32_t C;                // columns per block
 	uint32_t cg;               // columns per TMA stage
 	uint32_t first_block;
@@ -49,6 +50,24 @@ struct block_args
 
 size_t block_smem_bytes(block_args const &A, uint32_t n_warps, bool hist);
 cudaError_t launch_block(block_args const &A, uint32_t n_blocks, uint32_t n_warps, uint32_t tpw, bool hist, cudaStream_t st);
+// Blocked column step (fsq_bstep.cuh): T threads, E elements per thread, T E >= m.
+inline size_t bblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uint32_t NS, bool hist)
+{
+	auto r16 = [](size_t b) { return (b + 15) & ~size_t(15); };
+	uint32_t const n_warps = T >> 5;
+	size_t t = 0;
+	t += r16(2 * (size_t) A.cg * A.col_stride);
+	t += r16(2 * sizeof(uint64_t));
+	t += r16(sizeof(uint32_t) * (size_t) T * E);
+	t += r16(sizeof(uint32_t) * (size_t) T * NS) * 2;
+	t += r16(sizeof(uint32_t) * n_warps * NS) * 2;
+	t += r16(sizeof(uint32_t) * n_warps);
+	if (hist) t += r16(sizeof(uint32_t) * ((A.m + A.C + 2) / 2 + 1));
+	return t;
+}
+cudaError_t launch_bblock_e9(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
+cudaError_t launch_bblock_e17(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
+cudaError_t launch_bblock_e33(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
 cudaError_t launch_prep(uint32_t const *st_d, uint32_t m, uint16_t *code, uint32_t *oldvals, uint32_t *R, uint32_t first_block, uint32_t n_blocks, cudaStream_t st);
 
 struct stitch_item
@@ -64,8 +83,9 @@ struct stitch_item
 
 struct stitch_args
 {
-	stitch_item const *items;      // device array, executed in order by one CTA
-	uint32_t n_steps;
+	stitch_item const *items;      // device array; CTA g executes items [item_begin[g], item_begin[g + 1]) in order
+	uint32_t const *item_begin;    // device array [n_ctas + 1]
+	uint32_t n_ctas;
 	uint32_t m, n_tiles;
 };
 
@@ -79,13 +99,21 @@ struct dp_args
 	uint64_t n;                 // columns (global == local for one GPU)
 	uint64_t L;
 	uint2 const *toplist; uint32_t cap; uint32_t const *cnt; uint32_t const *h0;
-	uint32_t *tb_max, *tb_lb, *tb_size;   // [n - L + 1]
+	uint32_t *tb_max, *tb_lb, *tb_size;   // [n - L + 1]; entry t describes right bound t + L
+	uint64_t *mk;               // [n - L + 1] in-block minima masks (see fsq_dp.cu)
 	uint32_t *lev;              // [n_levels][n_blk] rmq tables
 	uint32_t n_blk, n_levels;
-	uint32_t *overflow;         // set to 1 + column when the top list was too short to be exact
+	uint32_t n_entries;         // entries 0 .. n - 2L (the ones the per-column DP writes)
+	uint32_t chunk;             // entries per chain (multiple of 64); chain c owns entries [c chunk, (c + 1) chunk)
+	uint32_t n_chunks;
+	uint32_t *chunk_level;      // [2 n_chunks] scratch for the guess
+	uint32_t *flags;            // [0] some stored value changed  [1] 1 + column whose top list was too short to be exact
+	                            // [2] the farthest any column looked back in the table (entries), over all rounds
 };
 
-cudaError_t launch_dp(dp_args const &A, cudaStream_t st);
+cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st);       // every chain once, against the table as it stands
+cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st);        // between rounds: level the table, rebuild masks and rmq tables
+cudaError_t launch_dp_final(dp_args const &A, cudaStream_t st);        // the last column (entry n - L)
 
 // next[j] / size for the greedy reduction; see fsq_dp.cu
 struct reduce_args
@@ -103,7 +131,7 @@ cudaError_t launch_segment_sets(uint32_t const *a, uint32_t const *d, uint32_t m
 cudaError_t launch_pair_weights(uint32_t const *cls_l, uint32_t const *cls_r, uint32_t m, uint32_t runs_r, int32_t *W, cudaStream_t st);
 
 // ---- pack / synth ----------------------------------------------------------------------------------------------
-cudaError_t launch_pack(uint8_t const *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint8_t const *d_comp, uint8_t *cols, uint64_t col_stride, uint64_t col_first, cudaStream_t st);
+cudaError_t launch_pack(uint8_t const *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint8_t const *d_comp, uint8_t *cols, uint64_t col_stride, uint64_t col_first, uint32_t *sym_mask, cudaStream_t st);
 cudaError_t launch_synth_packed(uint8_t *cols, uint64_t col_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps, cudaStream_t st);
 cudaError_t launch_synth_rows(uint8_t *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps, cudaStream_t st);
 

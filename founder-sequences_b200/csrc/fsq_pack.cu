@@ -12,7 +12,7 @@ constexpr int PACK_COLS = 32;
 
 __global__ void __launch_bounds__(PACK_ROWS) pack_kernel(
 	uint8_t const *rows, uint64_t row_stride, uint32_t m, uint64_t n, uint8_t const *comp,
-	uint8_t *cols, uint64_t col_stride, uint64_t col_first
+	uint8_t *cols, uint64_t col_stride, uint64_t col_first, uint32_t *sym_mask
 )
 {
 	__shared__ uint8_t tile[PACK_COLS][PACK_ROWS + 4];
@@ -25,6 +25,7 @@ __global__ void __launch_bounds__(PACK_ROWS) pack_kernel(
 	uint32_t const r0 = blockIdx.y * PACK_ROWS;
 	uint32_t const r = r0 + tid;
 	uint32_t const nc = (uint32_t) (n - c0 < PACK_COLS ? n - c0 : PACK_COLS);
+	uint32_t present = 0;      // comp values seen by this thread
 	if (r < m)
 	{
 		uint8_t const *src = rows + (uint64_t) r * row_stride + c0;
@@ -36,12 +37,20 @@ __global__ void __launch_bounds__(PACK_ROWS) pack_kernel(
 			for (int q = 0; q < 8; ++q)
 #pragma unroll
 				for (int bb = 0; bb < 4; ++bb)
-					tile[q * 4 + bb][tid] = scomp[(w[q] >> (8 * bb)) & 0xffu];
+				{
+					uint8_t const cv = scomp[(w[q] >> (8 * bb)) & 0xffu];
+					tile[q * 4 + bb][tid] = cv;
+					present |= 1u << (cv & 31u);
+				}
 		}
 		else
 		{
 			for (uint32_t c = 0; c < nc; ++c)
-				tile[c][tid] = scomp[src[c]];
+			{
+				uint8_t const cv = scomp[src[c]];
+				tile[c][tid] = cv;
+				present |= 1u << (cv & 31u);
+			}
 		}
 	}
 	else
@@ -49,6 +58,8 @@ __global__ void __launch_bounds__(PACK_ROWS) pack_kernel(
 		for (uint32_t c = 0; c < PACK_COLS; ++c)
 			tile[c][tid] = 0;
 	}
+	present = __reduce_or_sync(FSQ_FULL, present);
+	if (0 == (tid & 31u) && present) atomicOr(sym_mask, present);
 	__syncthreads();
 
 	// 32 columns x 32 words; thread -> (column = tid / 8 + 0, 8, 16, 24; word = tid % 8 * 4 .. + 3)?  Keep it simple:
@@ -69,12 +80,12 @@ __global__ void __launch_bounds__(PACK_ROWS) pack_kernel(
 	}
 }
 
-cudaError_t launch_pack(uint8_t const *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint8_t const *d_comp, uint8_t *cols, uint64_t col_stride, uint64_t col_first, cudaStream_t st)
+cudaError_t launch_pack(uint8_t const *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint8_t const *d_comp, uint8_t *cols, uint64_t col_stride, uint64_t col_first, uint32_t *sym_mask, cudaStream_t st)
 {
 	// grid.y covers every word of a column, including the padding words beyond m (written as zero).
 	uint32_t const words_per_col = (uint32_t) (col_stride / 4);
 	dim3 const grid((unsigned) ((n + PACK_COLS - 1) / PACK_COLS), (words_per_col * 8 + PACK_ROWS - 1) / PACK_ROWS);
-	pack_kernel <<<grid, PACK_ROWS, 0, st>>>(d_rows, row_stride, m, n, d_comp, cols, col_stride, col_first);
+	pack_kernel <<<grid, PACK_ROWS, 0, st>>>(d_rows, row_stride, m, n, d_comp, cols, col_stride, col_first, sym_mask);
 	return cudaGetLastError();
 }
 

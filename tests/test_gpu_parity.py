@@ -12,11 +12,13 @@ def as_rows(lst):
     return np.frombuffer(b"".join(lst), np.uint8).reshape(len(lst), -1).copy()
 
 
-def check_states(ctx, oracle, rows, block_columns=None, warps=None, columns=None):
+def check_states(ctx, oracle, rows, block_columns=None, warps=None, columns=None, kernel=0, chunk=0):
     m, n = rows.shape
     if block_columns:
         ctx.set_option("block_columns", block_columns)
     ctx.set_option("warps", warps or 0)
+    ctx.set_option("kernel", kernel)      # 0 auto, 1 striped step, 2 blocked step
+    ctx.set_option("chunk", chunk)        # elements per thread of the blocked step (9, 17, 33; 0 auto)
     if columns is None:
         columns = np.arange(1, n + 1)
     with oracle.open(rows) as o:
@@ -44,7 +46,27 @@ def test_kat_states(ctx, oracle):
 ])
 def test_states_every_column(ctx, oracle, synth, m, n, C, W):
     rows = synth.synth_rows(m, n, seed=m + n, founders=max(2, m // 12), gaps=(m % 2 == 0), recomb_block=37, mu=0.02, gap=0.02)
-    check_states(ctx, oracle, rows, C, W)
+    check_states(ctx, oracle, rows, C, W, kernel=1)
+
+
+@pytest.mark.parametrize("m,n,C,E", [
+    (5, 40, 7, 0), (33, 100, 16, 9), (64, 300, 64, 0), (64, 300, 13, 17), (100, 257, 50, 33), (288, 90, 30, 9), (289, 90, 30, 0),
+    (257, 200, 33, 0), (545, 100, 25, 0), (1000, 150, 40, 0), (1000, 150, 40, 9), (1000, 120, 64, 17), (1056, 80, 20, 33),
+    (1057, 80, 20, 33), (2500, 90, 32, 0), (5000, 70, 35, 0),
+])
+def test_states_every_column_blocked(ctx, oracle, synth, m, n, C, E):
+    """The blocked column step (E consecutive positions per thread) in every chunk length and CTA shape."""
+    rows = synth.synth_rows(m, n, seed=m + n, founders=max(2, m // 12), gaps=(m % 2 == 0), recomb_block=37, mu=0.02, gap=0.02)
+    check_states(ctx, oracle, rows, C, kernel=2, chunk=E)
+
+
+def test_states_blocked_nul_and_wide_alphabets(ctx, oracle):
+    """NUL bytes in the rows (comp 0 is then a real symbol), 8 symbols, and more than 8 (falls back to the striped step)."""
+    rng = np.random.default_rng(11)
+    for alphabet in (b"\0AC", b"ACGTNRYK", b"ACGTNRYKMSW"):
+        rows = rng.choice(np.frombuffer(alphabet, np.uint8), size=(150, 60))
+        rows[:, 20:40] = rows[0, 20:40]
+        check_states(ctx, oracle, rows, 11)
 
 
 def test_states_identical_rows_and_columns(ctx, oracle):
@@ -160,6 +182,29 @@ def test_segmentation_invariant_under_block_size(ctx, oracle, synth):
         with ctx.msa_from_rows(rows) as msa, ctx.segment(msa, 12) as seg:
             results.append((seg.max_segment_size,) + tuple(x.tobytes() for x in seg.reduced_traceback()) + tuple(x.tobytes() for x in seg.reduced_pbwt_samples()))
     assert all(r == results[0] for r in results)
+
+
+@pytest.mark.parametrize("G", [1, 2, 3, 7, 1000])
+def test_states_invariant_under_stitch_grouping(ctx, oracle, synth, G):
+    """The three-level stitch (groups of G blocks) composes summaries associatively: any grouping gives the same states."""
+    rows = synth.synth_rows(130, 500, seed=77, founders=9, gaps=True, recomb_block=41, mu=0.01)
+    ctx.set_option("stitch_group", G)
+    check_states(ctx, oracle, rows, 12, columns=np.arange(1, 501, 7))
+
+
+@pytest.mark.parametrize("chunks,max_rounds", [(1, 12), (3, 12), (0, 12), (1000, 12), (1000, 2)])
+def test_segmentation_invariant_under_dp_chaining(ctx, oracle, synth, chunks, max_rounds):
+    """The DP table is cut into chains that run at once and repeat until a round changes nothing; one chain, many chains
+    and the give-up-and-run-one-chain path must all produce the reference's table."""
+    rows = synth.synth_rows(120, 9000, seed=5, founders=10, gaps=True, recomb_block=300, mu=0.004)
+    ctx.set_option("dp_chunks", chunks)
+    ctx.set_option("dp_max_rounds", max_rounds)
+    ctx.reset_stats()
+    compare_segmentation(ctx, oracle, rows, 6, block_columns=700, sets=False)
+    if chunks == 1:
+        assert ctx.stat("dp_rounds") == 1
+    if chunks == 1000:
+        assert ctx.stat("dp_chunks") > 8
 
 
 def test_not_reducible_and_short(ctx, fsq, oracle):
