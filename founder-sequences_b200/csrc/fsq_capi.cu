@@ -33,6 +33,45 @@ struct fsq_ctx
 	std::vector <std::pair <std::string, std::pair <cudaEvent_t, cudaEvent_t>>> pending;   // phase timers
 
 	int64_t opt(char const *k, int64_t dflt) const { auto it = opts.find(k); return opts.end() == it ? dflt : it->second; }
+
+	// Workspace cache: device and pinned-host blocks released by one call are reused by the next instead of going
+	// through cudaMalloc / cudaFree (which synchronise the device).  Everything runs on the context's one stream, so a
+	// block handed out again is only touched after the work that used it before.
+	struct block { void *p; size_t bytes; };
+	std::vector <block> dev_cache, host_cache;
+
+	cudaError_t take(bool host, size_t bytes, void **out, size_t *got)
+	{
+		std::vector <block> &cache = host ? host_cache : dev_cache;
+		bytes = (std::max <size_t>(bytes, 16) + 255) & ~size_t(255);
+		size_t best = cache.size();
+		for (size_t i = 0; i < cache.size(); ++i)
+			if (cache[i].bytes >= bytes && cache[i].bytes <= bytes + bytes / 2 && (best == cache.size() || cache[i].bytes < cache[best].bytes))
+				best = i;
+		if (best != cache.size())
+		{
+			*out = cache[best].p; *got = cache[best].bytes;
+			cache[best] = cache.back(); cache.pop_back();
+			return cudaSuccess;
+		}
+		cudaError_t e = host ? cudaMallocHost(out, bytes) : cudaMalloc(out, bytes);
+		if (cudaErrorMemoryAllocation == e)
+		{
+			cudaGetLastError();
+			trim(host);
+			e = host ? cudaMallocHost(out, bytes) : cudaMalloc(out, bytes);
+		}
+		*got = bytes;
+		return e;
+	}
+	void give(bool host, void *p, size_t bytes) { if (p) (host ? host_cache : dev_cache).push_back({p, bytes}); }
+	void trim(bool host)
+	{
+		std::vector <block> &cache = host ? host_cache : dev_cache;
+		if (!cache.empty()) cudaStreamSynchronize(stream);
+		for (auto &b : cache) { if (host) cudaFreeHost(b.p); else cudaFree(b.p); }
+		cache.clear();
+	}
 };
 
 struct fsq_msa
@@ -55,6 +94,7 @@ struct fsq_segmentation
 	std::vector <uint32_t> size;
 	uint32_t *d_a{}, *d_d{};                  // reduced states on the device, count x m
 	uint32_t *h_a{}, *h_d{};                  // pinned host copies, made on first request
+	size_t d_bytes[2]{}, h_bytes[2]{};        // sizes of those blocks in the context's workspace cache
 	std::vector <uint64_t> tb_lb, tb_rb;      // traceback before reduction
 	std::vector <uint32_t> tb_max, tb_size;
 	std::vector <uint32_t> dp_lb, dp_max, dp_size;   // keep_dp
@@ -83,14 +123,24 @@ int fail(fsq_ctx *ctx, int code, char const *fmt, ...)
 
 #define CK(call) do { cudaError_t e_ = (call); if (cudaSuccess != e_) return fail(ctx, FSQ_ERR_CUDA, "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while (0)
 
-// RAII device buffer
-struct dbuf
+// RAII workspace buffers (device / pinned host) out of the context's cache
+template <bool HOST>
+struct wbuf
 {
 	void *p{nullptr};
-	~dbuf() { if (p) cudaFree(p); }
-	cudaError_t alloc(size_t bytes) { if (p) { cudaFree(p); p = nullptr; } return cudaMalloc(&p, bytes ? bytes : 16); }
+	size_t bytes{0};
+	fsq_ctx *owner{nullptr};
+	wbuf() = default;
+	wbuf(wbuf const &) = delete;
+	wbuf &operator=(wbuf const &) = delete;
+	~wbuf() { release(); }
+	void release() { if (p) owner->give(HOST, p, bytes); p = nullptr; }
+	cudaError_t alloc(fsq_ctx *ctx, size_t want) { release(); owner = ctx; return ctx->take(HOST, want, &p, &bytes); }
+	void *detach() { void *q = p; p = nullptr; return q; }
 	template <typename T> T *as() const { return static_cast <T *>(p); }
 };
+typedef wbuf <false> dbuf;
+typedef wbuf <true> hbuf;
 
 struct phase
 {
@@ -251,9 +301,9 @@ int prepare_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
 	geometry const &g = S.g;
 	uint32_t const m = msa->m;
 	size_t const bm = (size_t) g.B * m;
-	CK(S.sum_a.alloc(bm * 4)); CK(S.sum_d.alloc(bm * 4));
-	CK(S.st_a.alloc(bm * 4)); CK(S.st_d.alloc(bm * 4));
-	CK(S.code.alloc(bm * 2)); CK(S.oldvals.alloc(bm * 4)); CK(S.R.alloc((size_t) g.B * 4));
+	CK(S.sum_a.alloc(ctx, bm * 4)); CK(S.sum_d.alloc(ctx, bm * 4));
+	CK(S.st_a.alloc(ctx, bm * 4)); CK(S.st_d.alloc(ctx, bm * 4));
+	CK(S.code.alloc(ctx, bm * 2)); CK(S.oldvals.alloc(ctx, bm * 4)); CK(S.R.alloc(ctx, (size_t) g.B * 4));
 
 	iota_kernel <<<(m + 255) / 256, 256, 0, ctx->stream>>>(S.st_a.as <uint32_t>(), S.st_d.as <uint32_t>(), m, (uint32_t) msa->col0);
 	CK(cudaGetLastError());
@@ -281,7 +331,7 @@ int prepare_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
 		if (0 == G) G = (uint32_t) std::ceil(std::sqrt((double) B));
 		G = std::max <uint32_t>(1, std::min(G, B));
 		uint32_t const Q = (B + G - 1) / G;
-		CK(S.rel_a.alloc(((size_t) B + 1) * m * 4)); CK(S.rel_d.alloc(((size_t) B + 1) * m * 4));
+		CK(S.rel_a.alloc(ctx, ((size_t) B + 1) * m * 4)); CK(S.rel_d.alloc(ctx, ((size_t) B + 1) * m * 4));
 		uint32_t *sum_a = S.sum_a.as <uint32_t>(), *sum_d = S.sum_d.as <uint32_t>();
 		uint32_t *rel_a = S.rel_a.as <uint32_t>(), *rel_d = S.rel_d.as <uint32_t>();
 		uint32_t *st_a = S.st_a.as <uint32_t>(), *st_d = S.st_d.as <uint32_t>();
@@ -352,8 +402,8 @@ int prepare_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
 		std::vector <uint32_t> begin_all;
 		size_t off[3];
 		for (int ph = 0; ph < 3; ++ph) { off[ph] = begin_all.size(); begin_all.insert(begin_all.end(), begin[ph].begin(), begin[ph].end()); }
-		CK(S.items.alloc(items.size() * sizeof(stitch_item)));
-		CK(S.item_begin.alloc(begin_all.size() * 4));
+		CK(S.items.alloc(ctx, items.size() * sizeof(stitch_item)));
+		CK(S.item_begin.alloc(ctx, begin_all.size() * 4));
 		CK(cudaMemcpyAsync(S.items.p, items.data(), items.size() * sizeof(stitch_item), cudaMemcpyHostToDevice, ctx->stream));
 		CK(cudaMemcpyAsync(S.item_begin.p, begin_all.data(), begin_all.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
 		CK(cudaStreamSynchronize(ctx->stream));     // items and begin_all are stack vectors
@@ -401,7 +451,7 @@ int dump_states(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S, std::vector <ui
 	}
 	if (ids.empty()) return FSQ_OK;
 	dbuf d_cols, d_begin, d_ids;
-	CK(d_cols.alloc(columns.size() * 8)); CK(d_begin.alloc(begin.size() * 4)); CK(d_ids.alloc(ids.size() * 4));
+	CK(d_cols.alloc(ctx, columns.size() * 8)); CK(d_begin.alloc(ctx, begin.size() * 4)); CK(d_ids.alloc(ctx, ids.size() * 4));
 	CK(cudaMemcpyAsync(d_cols.p, columns.data(), columns.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
 	CK(cudaMemcpyAsync(d_begin.p, begin.data(), begin.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
 	CK(cudaMemcpyAsync(d_ids.p, ids.data(), ids.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -443,7 +493,13 @@ int new_msa(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint32_t nsym, 
 	msa->ctx = ctx; msa->m = m; msa->n = n; msa->col0 = col0; msa->nsym = nsym;
 	msa->col_stride = (((uint64_t) m + 1) / 2 + 15) & ~15ull;
 	unsigned long long const bytes = msa->col_stride * n;
-	cudaError_t const e = cudaMalloc(&msa->cols, bytes);
+	cudaError_t e = cudaMalloc(&msa->cols, bytes);
+	if (cudaErrorMemoryAllocation == e)
+	{
+		cudaGetLastError();
+		ctx->trim(false);        // give the workspace cache back and try once more
+		e = cudaMalloc(&msa->cols, bytes);
+	}
 	if (cudaSuccess != e)
 	{
 		delete msa;
@@ -493,6 +549,8 @@ void fsq_destroy(fsq_ctx *ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	flush_phases(ctx);
+	ctx->trim(false);
+	ctx->trim(true);
 	cudaStreamDestroy(ctx->stream);
 	delete ctx;
 }
@@ -542,8 +600,8 @@ int fsq_msa_from_device_rows(fsq_ctx *ctx, const uint8_t *d_rows, uint64_t row_s
 	fsq_msa *msa = nullptr;
 	if ((rc = new_msa(ctx, m, n, 0, nsym, &msa))) return rc;
 	dbuf d_comp, d_mask;
-	cudaError_t e = d_comp.alloc(256);
-	if (cudaSuccess == e) e = d_mask.alloc(4);
+	cudaError_t e = d_comp.alloc(ctx, 256);
+	if (cudaSuccess == e) e = d_mask.alloc(ctx, 4);
 	if (cudaSuccess == e) e = cudaMemsetAsync(d_mask.p, 0, 4, ctx->stream);
 	if (cudaSuccess == e) e = cudaMemcpyAsync(d_comp.p, comp, 256, cudaMemcpyHostToDevice, ctx->stream);
 	if (cudaSuccess == e)
@@ -588,9 +646,9 @@ int fsq_msa_from_rows(fsq_ctx *ctx, const uint8_t *const *rows, uint32_t m, uint
 	uint64_t const chunk = std::max <uint64_t>(32, std::min <uint64_t>(n, ((256ull << 20) / m) & ~31ull));
 	uint64_t const row_stride = (chunk + 15) & ~15ull;
 	dbuf stage, d_comp, d_mask;
-	cudaError_t e = stage.alloc((size_t) m * row_stride);
-	if (cudaSuccess == e) e = d_comp.alloc(256);
-	if (cudaSuccess == e) e = d_mask.alloc(4);
+	cudaError_t e = stage.alloc(ctx, (size_t) m * row_stride);
+	if (cudaSuccess == e) e = d_comp.alloc(ctx, 256);
+	if (cudaSuccess == e) e = d_mask.alloc(ctx, 4);
 	if (cudaSuccess == e) e = cudaMemsetAsync(d_mask.p, 0, 4, ctx->stream);
 	if (cudaSuccess == e) e = cudaMemcpyAsync(d_comp.p, comp, 256, cudaMemcpyHostToDevice, ctx->stream);
 	phase pk(ctx, "h2d_pack");
@@ -670,7 +728,7 @@ int fsq_pbwt_states(fsq_ctx *ctx, const fsq_msa *msa, const uint64_t *columns, u
 	if ((rc = prepare_scan(ctx, msa, S))) return rc;
 	dbuf da, dd;
 	size_t const bytes = (size_t) count * msa->m * 4;
-	CK(da.alloc(bytes)); CK(dd.alloc(bytes));
+	CK(da.alloc(ctx, bytes)); CK(dd.alloc(ctx, bytes));
 	if ((rc = dump_states(ctx, msa, S, cols, da.as <uint32_t>(), dd.as <uint32_t>()))) return rc;
 	CK(cudaMemcpyAsync(a, da.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaMemcpyAsync(d, dd.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
@@ -703,9 +761,9 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	uint32_t n_levels = 1;
 	while ((1ull << n_levels) <= n_blk) ++n_levels;
 	dbuf tb_max, tb_lb, tb_size, mk, lev, flags, chunk_level, cnt, h0, toplist;
-	CK(tb_max.alloc(dp_size * 4)); CK(tb_lb.alloc(dp_size * 4)); CK(tb_size.alloc(dp_size * 4)); CK(mk.alloc(dp_size * 8));
-	CK(lev.alloc((size_t) n_levels * n_blk * 4)); CK(flags.alloc(16));
-	CK(cnt.alloc(n * 4)); CK(h0.alloc(n * 4));
+	CK(tb_max.alloc(ctx, dp_size * 4)); CK(tb_lb.alloc(ctx, dp_size * 4)); CK(tb_size.alloc(ctx, dp_size * 4)); CK(mk.alloc(ctx, dp_size * 8));
+	CK(lev.alloc(ctx, (size_t) n_levels * n_blk * 4)); CK(flags.alloc(ctx, 16));
+	CK(cnt.alloc(ctx, n * 4)); CK(h0.alloc(ctx, n * 4));
 	// chains: enough to fill the device a few times over, each a whole number of 64-entry rmq blocks
 	uint32_t chunk, n_chunks;
 	{
@@ -718,11 +776,11 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 		chunk = (uint32_t) std::min <uint64_t>(c, 0xffffffc0ull);
 		n_chunks = (n_entries + chunk - 1) / chunk;
 	}
-	CK(chunk_level.alloc((size_t) n_chunks * 8));
+	CK(chunk_level.alloc(ctx, (size_t) n_chunks * 8));
 	uint32_t cap = (uint32_t) std::min <int64_t>(m, std::max <int64_t>(1, ctx->opt("cap", 127)));
 	while (true)
 	{
-		CK(toplist.alloc((size_t) n * (cap + 1) * sizeof(uint2)));
+		CK(toplist.alloc(ctx, (size_t) n * (cap + 1) * sizeof(uint2)));
 		// entries the per-column DP writes start from 0 (the first round's stand-in for "nothing known"); the ones the
 		// reference never writes keep its defaults; masks and rmq cells start from values that index inside the table
 		CK(cudaMemsetAsync(tb_max.p, 0xff, dp_size * 4, ctx->stream));
@@ -818,32 +876,48 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	if (!seg) return fail(ctx, FSQ_ERR_NOMEM, "out of host memory");
 	struct guard { fsq_segmentation *&s; bool ok{false}; ~guard() { if (!ok) { fsq_segmentation_free(s); s = nullptr; } } } gd{seg};
 	seg->ctx = ctx; seg->m = m; seg->n = n; seg->L = L;
+	dbuf tr_lb, tr_rb, tr_max, tr_size;          // the traceback on the device, text order
+	uint32_t T = 0;
 	{
 		phase pt(ctx, "traceback");
-		std::vector <uint32_t> h_lb(dp_size), h_max(dp_size), h_size(dp_size);
-		CK(cudaMemcpyAsync(h_lb.data(), tb_lb.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(h_max.data(), tb_max.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(h_size.data(), tb_size.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		trace_args TA;
+		memset(&TA, 0, sizeof TA);
+		TA.tb_lb = tb_lb.as <uint32_t>(); TA.tb_max = tb_max.as <uint32_t>(); TA.tb_size = tb_size.as <uint32_t>();
+		TA.L = (uint32_t) L; TA.dp_size = (uint32_t) dp_size;
+		TA.levels = 1;
+		while ((1ull << TA.levels) <= dp_size / L + 1) ++TA.levels;
+		dbuf jump, count;
+		CK(jump.alloc(ctx, (size_t) TA.levels * dp_size * 4)); CK(count.alloc(ctx, 4));
+		TA.jump = jump.as <uint32_t>(); TA.count = count.as <uint32_t>();
+		CK(launch_trace_tables(TA, ctx->stream));
+		ctx->stats["kernel_launches"] += TA.levels + 1;
+		CK(cudaMemcpyAsync(&T, count.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaStreamSynchronize(ctx->stream));
-		uint64_t idx = dp_size - 1;
-		while (true)
-		{
-			seg->tb_lb.push_back(h_lb[idx]);
-			seg->tb_rb.push_back(idx + L);
-			seg->tb_max.push_back(h_max[idx]);
-			seg->tb_size.push_back(h_size[idx]);
-			if (0 == h_lb[idx]) break;
-			idx = h_lb[idx] - L;
-		}
-		std::reverse(seg->tb_lb.begin(), seg->tb_lb.end());
-		std::reverse(seg->tb_rb.begin(), seg->tb_rb.end());
-		std::reverse(seg->tb_max.begin(), seg->tb_max.end());
-		std::reverse(seg->tb_size.begin(), seg->tb_size.end());
-		seg->K = seg->tb_max.back();
+		CK(tr_lb.alloc(ctx, (size_t) T * 4)); CK(tr_rb.alloc(ctx, (size_t) T * 8)); CK(tr_max.alloc(ctx, (size_t) T * 4)); CK(tr_size.alloc(ctx, (size_t) T * 4));
+		TA.out_lb = tr_lb.as <uint32_t>(); TA.out_rb = tr_rb.as <uint64_t>(); TA.out_max = tr_max.as <uint32_t>(); TA.out_size = tr_size.as <uint32_t>();
+		CK(launch_trace_gather(TA, T, ctx->stream));
+		ctx->stats["kernel_launches"] += 1;
+		hbuf stage;
+		CK(stage.alloc(ctx, (size_t) T * 20));
+		uint64_t *h_rb = stage.as <uint64_t>();
+		uint32_t *h_lb = (uint32_t *) (h_rb + T), *h_max = h_lb + T, *h_size = h_max + T;
+		CK(cudaMemcpyAsync(h_rb, tr_rb.p, (size_t) T * 8, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_lb, tr_lb.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_max, tr_max.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_size, tr_size.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		if (ctx->opt("keep_dp", 0))
 		{
-			seg->dp_lb.swap(h_lb); seg->dp_max.swap(h_max); seg->dp_size.swap(h_size);
+			seg->dp_lb.resize(dp_size); seg->dp_max.resize(dp_size); seg->dp_size.resize(dp_size);
+			CK(cudaMemcpyAsync(seg->dp_lb.data(), tb_lb.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			CK(cudaMemcpyAsync(seg->dp_max.data(), tb_max.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+			CK(cudaMemcpyAsync(seg->dp_size.data(), tb_size.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		}
+		CK(cudaStreamSynchronize(ctx->stream));
+		seg->tb_rb.assign(h_rb, h_rb + T);
+		seg->tb_lb.assign(h_lb, h_lb + T);
+		seg->tb_max.assign(h_max, h_max + T);
+		seg->tb_size.assign(h_size, h_size + T);
+		seg->K = seg->tb_max.back();
 		pt.stop();
 	}
 	if (!(seg->K < m))
@@ -855,28 +929,29 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	}
 
 	// ---- pass C: states at the traceback right bounds (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35) ----
-	uint32_t const T = (uint32_t) seg->tb_rb.size();
 	dbuf st_a, st_d;
-	CK(st_a.alloc((size_t) T * m * 4)); CK(st_d.alloc((size_t) T * m * 4));
+	CK(st_a.alloc(ctx, (size_t) T * m * 4)); CK(st_d.alloc(ctx, (size_t) T * m * 4));
 	if ((rc = dump_states(ctx, msa, S, seg->tb_rb, st_a.as <uint32_t>(), st_d.as <uint32_t>()))) return rc;
 
 	// ---- greedy reduction (segmentation_lp_context.cc:335-390) ----
-	std::vector <uint32_t> chosen;
+	hbuf chosen_buf;
+	CK(chosen_buf.alloc(ctx, (size_t) T * 4));
+	uint32_t *chosen = chosen_buf.as <uint32_t>();
+	uint32_t cntS = 0;
 	{
 		phase pr(ctx, "reduce");
-		dbuf d_rb, d_sz, d_next, d_nsize;
-		CK(d_rb.alloc((size_t) T * 8)); CK(d_sz.alloc((size_t) T * 4)); CK(d_next.alloc((size_t) T * 4)); CK(d_nsize.alloc((size_t) T * 4));
-		CK(cudaMemcpyAsync(d_rb.p, seg->tb_rb.data(), (size_t) T * 8, cudaMemcpyHostToDevice, ctx->stream));
-		CK(cudaMemcpyAsync(d_sz.p, seg->tb_size.data(), (size_t) T * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dbuf d_next, d_nsize;
+		hbuf h_next;
+		CK(d_next.alloc(ctx, (size_t) T * 4)); CK(d_nsize.alloc(ctx, (size_t) T * 4)); CK(h_next.alloc(ctx, (size_t) T * 8));
 		reduce_args Rg;
 		Rg.m = m; Rg.T = T; Rg.K = seg->K;
-		Rg.tb_rb = d_rb.as <uint64_t>(); Rg.tb_size = d_sz.as <uint32_t>(); Rg.st_d = st_d.as <uint32_t>();
+		Rg.tb_rb = tr_rb.as <uint64_t>(); Rg.tb_size = tr_size.as <uint32_t>(); Rg.st_d = st_d.as <uint32_t>();
 		Rg.next = d_next.as <uint32_t>(); Rg.next_size = d_nsize.as <uint32_t>();
 		CK(launch_reduce(Rg, ctx->stream));
 		ctx->stats["kernel_launches"] += 1;
-		std::vector <uint32_t> nxt(T), nsz(T);
-		CK(cudaMemcpyAsync(nxt.data(), d_next.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(nsz.data(), d_nsize.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		uint32_t *nxt = h_next.as <uint32_t>(), *nsz = nxt + T;
+		CK(cudaMemcpyAsync(nxt, d_next.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(nsz, d_nsize.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaStreamSynchronize(ctx->stream));
 		uint64_t cur_lb = 0;
 		for (uint32_t u = 0; u < T; )
@@ -885,7 +960,7 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 			seg->lb.push_back(cur_lb);
 			seg->rb.push_back(seg->tb_rb[last]);
 			seg->size.push_back(nsz[u]);
-			chosen.push_back(last);
+			chosen[cntS++] = last;
 			cur_lb = seg->tb_rb[last];
 			u = last + 1;
 		}
@@ -895,18 +970,18 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	// ---- the reduced samples: device copy for the follow-on kernels, host copy for the joiners ----
 	{
 		phase pg(ctx, "gather");
-		uint32_t const cntS = (uint32_t) chosen.size();
-		dbuf d_idx;
-		CK(d_idx.alloc((size_t) cntS * 4));
-		CK(cudaMemcpyAsync(d_idx.p, chosen.data(), (size_t) cntS * 4, cudaMemcpyHostToDevice, ctx->stream));
-		CK(cudaMalloc(&seg->d_a, (size_t) cntS * m * 4));
-		CK(cudaMalloc(&seg->d_d, (size_t) cntS * m * 4));
+		dbuf d_idx, da, dd;
+		CK(d_idx.alloc(ctx, (size_t) cntS * 4));
+		CK(cudaMemcpyAsync(d_idx.p, chosen, (size_t) cntS * 4, cudaMemcpyHostToDevice, ctx->stream));
+		CK(da.alloc(ctx, (size_t) cntS * m * 4)); CK(dd.alloc(ctx, (size_t) cntS * m * 4));
 		dim3 const grid((m + 255) / 256, cntS);
-		gather_states_kernel <<<grid, 256, 0, ctx->stream>>>(st_a.as <uint32_t>(), st_d.as <uint32_t>(), d_idx.as <uint32_t>(), m, seg->d_a, seg->d_d);
+		gather_states_kernel <<<grid, 256, 0, ctx->stream>>>(st_a.as <uint32_t>(), st_d.as <uint32_t>(), d_idx.as <uint32_t>(), m, da.as <uint32_t>(), dd.as <uint32_t>());
 		CK(cudaGetLastError());
 		ctx->stats["kernel_launches"] += 1;
 		pg.stop();
 		CK(cudaStreamSynchronize(ctx->stream));
+		seg->d_bytes[0] = da.bytes; seg->d_bytes[1] = dd.bytes;
+		seg->d_a = (uint32_t *) da.detach(); seg->d_d = (uint32_t *) dd.detach();
 	}
 	gd.ok = true;
 	*out = seg;
@@ -916,11 +991,12 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 void fsq_segmentation_free(fsq_segmentation *seg)
 {
 	if (!seg) return;
-	if (seg->ctx) cudaSetDevice(seg->ctx->device);
-	cudaFree(seg->d_a);
-	cudaFree(seg->d_d);
-	cudaFreeHost(seg->h_a);
-	cudaFreeHost(seg->h_d);
+	// the buffers go back to the context's workspace cache (the context must outlive its segmentations)
+	fsq_ctx *ctx = seg->ctx;
+	ctx->give(false, seg->d_a, seg->d_bytes[0]);
+	ctx->give(false, seg->d_d, seg->d_bytes[1]);
+	ctx->give(true, seg->h_a, seg->h_bytes[0]);
+	ctx->give(true, seg->h_d, seg->h_bytes[1]);
 	delete seg;
 }
 
@@ -943,8 +1019,12 @@ static int fetch_states(fsq_segmentation *seg)
 	size_t const bytes = seg->lb.size() * (size_t) seg->m * 4;
 	CK(cudaSetDevice(ctx->device));
 	phase pd(ctx, "states_d2h");
-	CK(cudaMallocHost(&seg->h_a, bytes));
-	CK(cudaMallocHost(&seg->h_d, bytes));
+	{
+		hbuf ha, hd;
+		CK(ha.alloc(ctx, bytes)); CK(hd.alloc(ctx, bytes));
+		seg->h_bytes[0] = ha.bytes; seg->h_bytes[1] = hd.bytes;
+		seg->h_a = (uint32_t *) ha.detach(); seg->h_d = (uint32_t *) hd.detach();
+	}
 	CK(cudaMemcpyAsync(seg->h_a, seg->d_a, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaMemcpyAsync(seg->h_d, seg->d_d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 	pd.stop();
@@ -1007,7 +1087,7 @@ int fsq_segmentation_dp_table(const fsq_segmentation *seg, uint64_t *lb, uint64_
 
 static int sets_on_device(fsq_ctx *ctx, uint32_t const *d_a, uint32_t const *d_d, uint32_t m, uint64_t lb, dbuf &off, dbuf &ids, dbuf &cls, dbuf &nruns)
 {
-	CK(off.alloc(((size_t) m + 1) * 4)); CK(ids.alloc((size_t) m * 4)); CK(cls.alloc((size_t) m * 4)); CK(nruns.alloc(4));
+	CK(off.alloc(ctx, ((size_t) m + 1) * 4)); CK(ids.alloc(ctx, (size_t) m * 4)); CK(cls.alloc(ctx, (size_t) m * 4)); CK(nruns.alloc(ctx, 4));
 	CK(launch_segment_sets(d_a, d_d, m, lb, off.as <uint32_t>(), ids.as <uint32_t>(), cls.as <uint32_t>(), nruns.as <uint32_t>(), ctx->stream));
 	ctx->stats["kernel_launches"] += 1;
 	return FSQ_OK;
@@ -1023,7 +1103,7 @@ int fsq_distinct_rows(fsq_ctx *ctx, const fsq_msa *msa, uint32_t *row_of_run, ui
 	scan_state S;
 	if ((rc = prepare_scan(ctx, msa, S))) return rc;
 	dbuf da, dd, off, ids, cls, nruns;
-	CK(da.alloc((size_t) m * 4)); CK(dd.alloc((size_t) m * 4));
+	CK(da.alloc(ctx, (size_t) m * 4)); CK(dd.alloc(ctx, (size_t) m * 4));
 	std::vector <uint64_t> cols(1, msa->n);
 	if ((rc = dump_states(ctx, msa, S, cols, da.as <uint32_t>(), dd.as <uint32_t>()))) return rc;
 	if ((rc = sets_on_device(ctx, da.as <uint32_t>(), dd.as <uint32_t>(), m, 0, off, ids, cls, nruns))) return rc;
@@ -1079,7 +1159,7 @@ int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, int3
 	CK(cudaMemcpyAsync(&rr, n_r.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaStreamSynchronize(ctx->stream));
 	size_t const bytes = (size_t) rl * rr * 4;
-	CK(dW.alloc(bytes));
+	CK(dW.alloc(ctx, bytes));
 	CK(cudaMemsetAsync(dW.p, 0, bytes, ctx->stream));
 	CK(launch_pair_weights(cls_l.as <uint32_t>(), cls_r.as <uint32_t>(), m, rr, dW.as <int32_t>(), ctx->stream));
 	ctx->stats["kernel_launches"] += 1;

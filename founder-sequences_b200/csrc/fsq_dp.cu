@@ -319,6 +319,68 @@ cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st)
 }
 
 
+// ---- traceback (reference: segmentation_lp_context.cc:191-224) --------------------------------------------------------------
+constexpr uint32_t TRACE_END = 0xffffffffu;
+
+__global__ void trace_init_kernel(trace_args const A)
+{
+	uint32_t const t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= A.dp_size) return;
+	uint32_t const lb = A.tb_lb[t];
+	A.jump[t] = lb ? lb - A.L : TRACE_END;
+}
+
+__global__ void trace_double_kernel(trace_args const A, uint32_t k)
+{
+	uint32_t const t = blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= A.dp_size) return;
+	uint32_t const *prev = A.jump + (size_t) (k - 1) * A.dp_size;
+	uint32_t const j = prev[t];
+	A.jump[(size_t) k * A.dp_size + t] = (TRACE_END == j) ? TRACE_END : prev[j];
+}
+
+__global__ void trace_count_kernel(trace_args const A)
+{
+	uint32_t cur = A.dp_size - 1, hops = 0;
+	for (int k = (int) A.levels - 1; k >= 0; --k)
+	{
+		uint32_t const j = A.jump[(size_t) k * A.dp_size + cur];
+		if (TRACE_END != j) { cur = j; hops += 1u << k; }
+	}
+	*A.count = hops + 1;
+}
+
+__global__ void trace_gather_kernel(trace_args const A, uint32_t count)
+{
+	uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;      // hops back from the last entry
+	if (s >= count) return;
+	uint32_t cur = A.dp_size - 1;
+	for (uint32_t k = 0; k < A.levels; ++k)
+		if ((s >> k) & 1u) cur = A.jump[(size_t) k * A.dp_size + cur];
+	uint32_t const o = count - 1 - s;
+	A.out_lb[o] = A.tb_lb[cur];
+	A.out_rb[o] = (uint64_t) cur + A.L;
+	A.out_max[o] = A.tb_max[cur];
+	A.out_size[o] = A.tb_size[cur];
+}
+
+cudaError_t launch_trace_tables(trace_args const &A, cudaStream_t st)
+{
+	uint32_t const grid = (A.dp_size + 255) / 256;
+	trace_init_kernel <<<grid, 256, 0, st>>>(A);
+	for (uint32_t k = 1; k < A.levels; ++k)
+		trace_double_kernel <<<grid, 256, 0, st>>>(A, k);
+	trace_count_kernel <<<1, 1, 0, st>>>(A);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_trace_gather(trace_args const &A, uint32_t count, cudaStream_t st)
+{
+	trace_gather_kernel <<<(count + 255) / 256, 256, 0, st>>>(A, count);
+	return cudaGetLastError();
+}
+
+
 // ---- greedy reduction (reference: segmentation_lp_context.cc:335-390; pbwt.hh:206-216) ------------------------------
 // #{d_rb > lb} is the number of distinct rows over [lb, rb), which cannot decrease as rb grows, so the run that the
 // reference's sequential loop would merge from a given start is a function of the start alone: one warp per start u

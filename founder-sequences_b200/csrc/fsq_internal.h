@@ -115,6 +115,20 @@ cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st);       // every 
 cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st);        // between rounds: level the table, rebuild masks and rmq tables
 cudaError_t launch_dp_final(dp_args const &A, cudaStream_t st);        // the last column (entry n - L)
 
+// Traceback (reference: segmentation_lp_context.cc:191-224) by pointer doubling: jump[k][t] = the entry 2^k hops
+// before t on the path t -> lb[t] - L.  The walk from the last entry is then T independent binary descents.
+struct trace_args
+{
+	uint32_t const *tb_lb, *tb_max, *tb_size;
+	uint32_t L, dp_size, levels;
+	uint32_t *jump;              // [levels][dp_size]
+	uint32_t *count;             // [1] entries on the path
+	uint32_t *out_lb, *out_max, *out_size;   // [count] in text order
+	uint64_t *out_rb;
+};
+cudaError_t launch_trace_tables(trace_args const &A, cudaStream_t st);     // jump tables + count
+cudaError_t launch_trace_gather(trace_args const &A, uint32_t count, cudaStream_t st);
+
 // next[j] / size for the greedy reduction; see fsq_dp.cu
 struct reduce_args
 {
