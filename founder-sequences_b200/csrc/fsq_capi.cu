@@ -177,6 +177,7 @@ struct geometry
 	uint32_t n_tiles, n_warps, tpw, C, cg, B;
 	// blocked column step (fsq_bstep.cuh): E elements per thread, T threads, symbols sym0 .. sym0 + ns - 1
 	bool blocked;
+	bool chunked;          // fsq_cstep.cuh (the default where it applies); otherwise blocked = fsq_bstep.cuh, else striped
 	uint32_t E, T, ns, sym0;
 };
 
@@ -203,10 +204,23 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 	while (!((mask >> hi) & 1u)) --hi;
 	g.sym0 = lo;
 	g.ns = hi - lo + 1;
-	int64_t const kern = ctx->opt("kernel", 0);        // 0 auto, 1 striped, 2 blocked
-	g.blocked = (1 != kern) && g.ns <= 8 && m <= 448u * 33u;
+	int64_t const kern = ctx->opt("kernel", 0);        // 0 auto, 1 striped, 2 blocked, 3 chunked
+	g.chunked = (0 == kern || 3 == kern) && g.ns <= 8 && m <= 384u * 33u;
+	g.blocked = !g.chunked && (1 != kern) && g.ns <= 8 && m <= 448u * 33u;
 	uint32_t threads = g.n_warps * 32, regs = 64;
-	if (g.blocked)
+	if (g.chunked)
+	{
+		int64_t e = ctx->opt("chunk", 0);
+		if (9 != e && 17 != e && 33 != e)
+			e = m <= 32 * 9 ? 9 : (m <= 32 * 17 ? 17 : 33);
+		uint32_t const tmax = 9 == e ? 1024 : 512;
+		if ((uint64_t) tmax * e < m) e = 33;
+		g.E = (uint32_t) e;
+		g.T = ((m + g.E - 1) / g.E + 31) / 32 * 32;
+		threads = g.T;
+		regs = 9 == g.E ? 64 : 128;
+	}
+	else if (g.blocked)
 	{
 		int64_t e = ctx->opt("chunk", 0);
 		if (9 != e && 17 != e && 33 != e)
@@ -219,14 +233,24 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 		regs = 9 == g.E ? 64 : 128;
 	}
 
-	g.cg = (uint32_t) std::max <uint64_t>(1, 2048 / msa->col_stride);
+	g.cg = (uint32_t) std::max <uint64_t>(1, (g.chunked ? 1024 : 2048) / msa->col_stride);
 	int64_t C = ctx->opt("block_columns", 0);
 	if (C <= 0)
 	{
-		// enough blocks to fill every SM a few times over, but long enough to amortise the two extra passes' fixed costs
+		// enough blocks to fill every SM once (the same blocks serve passes A and B, so the pass with the larger
+		// footprint decides), but long enough to amortise the two extra passes' fixed costs
 		uint64_t per_sm = std::min <uint64_t>(32, 2048 / threads);
 		per_sm = std::min <uint64_t>(per_sm, 65536 / ((uint64_t) threads * regs));
-		size_t const smem = 2 * (size_t) g.cg * msa->col_stride + 4 * (size_t) threads * (g.blocked ? g.E + 2 * g.ns : 1) + 2 * (size_t) m + 1024;
+		size_t smem = 2 * (size_t) g.cg * msa->col_stride + 4 * (size_t) threads * (g.blocked ? g.E + 2 * g.ns : 1) + 2 * (size_t) m + 1024;
+		if (g.chunked)
+		{
+			block_args P;
+			memset(&P, 0, sizeof P);
+			P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m;
+			P.C = (uint32_t) std::min <uint64_t>(4096, std::max <uint64_t>(64, msa->n / (ctx->prop.multiProcessorCount * 8)));
+			smem = cblock_smem_bytes(P, g.T, g.E, g.ns, true) + 1024;
+			per_sm = std::min <uint64_t>(per_sm, 65536 / ((uint64_t) threads * (9 == g.E ? 64 : (17 == g.E ? 128 : 168))));
+		}
 		per_sm = std::min <uint64_t>(per_sm, (227 * 1024) / smem);
 		per_sm = std::max <uint64_t>(per_sm, 1);
 		uint64_t const resident = (uint64_t) ctx->prop.multiProcessorCount * per_sm;
@@ -245,6 +269,15 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 // One launch of the column-block scan in the geometry's flavour.
 cudaError_t launch_scan(block_args const &A, uint32_t n_blocks, geometry const &g, bool hist, cudaStream_t st)
 {
+	if (g.chunked)
+	{
+		switch (g.E)
+		{
+			case 9: return launch_cblock_e9(A, n_blocks, g.T, g.ns, hist, st);
+			case 17: return launch_cblock_e17(A, n_blocks, g.T, g.ns, hist, st);
+			default: return launch_cblock_e33(A, n_blocks, g.T, g.ns, hist, st);
+		}
+	}
 	if (!g.blocked) return launch_block(A, n_blocks, g.n_warps, g.tpw, hist, st);
 	switch (g.E)
 	{
@@ -285,6 +318,26 @@ __global__ void gather_states_kernel(uint32_t const *src_a, uint32_t const *src_
 		dst_a[to] = src_a[from];
 		dst_d[to] = src_d[from];
 	}
+}
+
+// States kept by pass B (packed row | code << 16, one row of `stride` words per column) -> (a, d) at the given right
+// bounds: the state before column rb is the one stored after column rb - 1; its codes are relative to that column's block.
+__global__ void gather_stored_states_kernel(
+	uint32_t const *states, uint64_t stride, uint64_t const *rbs, uint32_t m, uint32_t C, uint64_t col0,
+	uint32_t const *oldvals, uint32_t const *R, uint32_t *dst_a, uint32_t *dst_d
+)
+{
+	uint32_t const t = blockIdx.y;
+	uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= m) return;
+	uint64_t const k = rbs[t] - 1;                 // local column whose output state this is
+	uint32_t const b = (uint32_t) (k / C);
+	uint32_t const r = R[b];
+	uint32_t const w = states[k * stride + i];
+	uint32_t const code = w >> 16;
+	uint32_t const v = code >= r ? (uint32_t) (col0 + (uint64_t) b * C + 1 + (code - r)) : oldvals[(size_t) b * m + code];
+	dst_a[(size_t) t * m + i] = w & 0xffffu;
+	dst_d[(size_t) t * m + i] = v;
 }
 
 // Everything the scans share: local summaries, true block start states, their rank compression.
@@ -560,7 +613,7 @@ const char *fsq_last_error(const fsq_ctx *ctx) { return ctx ? ctx->error.c_str()
 int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
 {
 	if (!ctx || !key) return fail(ctx, FSQ_ERR_ARG, "null argument");
-	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", nullptr};
+	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", nullptr};
 	for (char const **k = known; *k; ++k)
 		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }
 	return fail(ctx, FSQ_ERR_ARG, "unknown option '%s'", key);
@@ -778,6 +831,26 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	}
 	CK(chunk_level.alloc(ctx, (size_t) n_chunks * 8));
 	uint32_t cap = (uint32_t) std::min <int64_t>(m, std::max <int64_t>(1, ctx->opt("cap", 127)));
+	// Pass B keeps the state of every column when 4 m n bytes fit comfortably (option store_states: -1 auto, 0 never,
+	// 1 always); the states at the traceback positions are then a gather instead of a third scan.
+	dbuf states;
+	uint64_t const state_stride = ((uint64_t) m + 3) & ~3ull;
+	{
+		int64_t const want = ctx->opt("store_states", -1);
+		size_t free_b = 0, total_b = 0;
+		bool keep = false;
+		if (g.chunked && 0 != want)
+		{
+			CK(cudaMemGetInfo(&free_b, &total_b));
+			size_t cached = 0;
+			for (auto const &blk : ctx->dev_cache) cached += blk.bytes;
+			size_t const need = (size_t) (state_stride * 4 * n);
+			size_t const other = (size_t) n * (cap + 1) * 8 + (size_t) n * 64 + ((size_t) 1 << 30);
+			keep = (1 == want) || need + other < free_b + cached;
+			if (keep && cudaSuccess != states.alloc(ctx, need)) { cudaGetLastError(); keep = false; }
+		}
+		ctx->stats["store_states"] = keep ? 1 : 0;
+	}
 	while (true)
 	{
 		CK(toplist.alloc(ctx, (size_t) n * (cap + 1) * sizeof(uint2)));
@@ -802,6 +875,8 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 			A.cap = cap;
 			A.cnt = cnt.as <uint32_t>();
 			A.h0 = h0.as <uint32_t>();
+			A.states = states.as <uint32_t>();
+			A.state_stride = state_stride;
 			CK(launch_scan(A, g.B, g, true, ctx->stream));
 			pb.stop();
 			ctx->stats["kernel_launches"] += 1;
@@ -868,8 +943,9 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	ctx->stats["cap"] = cap;
 	ctx->stats["block_columns"] = g.C;
 	ctx->stats["blocks"] = g.B;
-	ctx->stats["warps"] = g.blocked ? g.T / 32 : g.n_warps;
-	ctx->stats["chunk"] = g.blocked ? g.E : 0;
+	ctx->stats["warps"] = (g.blocked || g.chunked) ? g.T / 32 : g.n_warps;
+	ctx->stats["chunk"] = (g.blocked || g.chunked) ? g.E : 0;
+	ctx->stats["kernel"] = g.chunked ? 3 : (g.blocked ? 2 : 1);
 
 	// ---- traceback (reference: segmentation_lp_context.cc:191-224) ----
 	fsq_segmentation *seg = new (std::nothrow) fsq_segmentation;
@@ -931,7 +1007,18 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	// ---- pass C: states at the traceback right bounds (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35) ----
 	dbuf st_a, st_d;
 	CK(st_a.alloc(ctx, (size_t) T * m * 4)); CK(st_d.alloc(ctx, (size_t) T * m * 4));
-	if ((rc = dump_states(ctx, msa, S, seg->tb_rb, st_a.as <uint32_t>(), st_d.as <uint32_t>()))) return rc;
+	if (states.p)
+	{
+		phase pc(ctx, "pass_c");
+		dim3 const grid((m + 255) / 256, T);
+		gather_stored_states_kernel <<<grid, 256, 0, ctx->stream>>>(states.as <uint32_t>(), state_stride, tr_rb.as <uint64_t>(), m, g.C, msa->col0,
+			S.oldvals.as <uint32_t>(), S.R.as <uint32_t>(), st_a.as <uint32_t>(), st_d.as <uint32_t>());
+		CK(cudaGetLastError());
+		pc.stop();
+		ctx->stats["kernel_launches"] += 1;
+		states.release();
+	}
+	else if ((rc = dump_states(ctx, msa, S, seg->tb_rb, st_a.as <uint32_t>(), st_d.as <uint32_t>()))) return rc;
 
 	// ---- greedy reduction (segmentation_lp_context.cc:335-390) ----
 	hbuf chosen_buf;

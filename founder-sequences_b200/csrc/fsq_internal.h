@@ -41,6 +41,9 @@ struct block_args
 	uint32_t *cnt;             // entries | complete << 31
 	uint32_t *h0;              // #{d == 0}
 
+	uint32_t *states;          // [n_local][state_stride] packed state after every column (optional; chunked kernel only)
+	uint64_t state_stride;     // words
+
 	// MODE_DUMP
 	uint32_t const *blk_ids;
 	uint64_t const *dump_cols; // ascending local right bounds
@@ -68,6 +71,25 @@ inline size_t bblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uin
 cudaError_t launch_bblock_e9(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
 cudaError_t launch_bblock_e17(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
 cudaError_t launch_bblock_e33(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
+// Chunked column step (fsq_cstep.cuh): T threads, E elements per thread, T E >= m; 32-bit histogram counters.
+inline size_t cblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uint32_t NS, bool hist)
+{
+	auto r16 = [](size_t b) { return (b + 15) & ~size_t(15); };
+	uint32_t const n_warps = T >> 5;
+	size_t const words = (size_t) T * E;
+	size_t t = 0;
+	t += r16(2 * (size_t) A.cg * A.col_stride);
+	t += r16(2 * sizeof(uint64_t));
+	t += r16((size_t) A.cg * ((words + 15) & ~size_t(15)));
+	t += r16(sizeof(uint32_t) * words);
+	t += r16(sizeof(uint32_t) * (size_t) T * (NS | 1));
+	t += r16(sizeof(uint32_t) * n_warps * 2 * NS);
+	if (hist) t += r16(sizeof(uint32_t) * ((size_t) A.m + A.C + 8)) + r16(sizeof(uint32_t) * (size_t) A.m);
+	return t;
+}
+cudaError_t launch_cblock_e9(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
+cudaError_t launch_cblock_e17(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
+cudaError_t launch_cblock_e33(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
 cudaError_t launch_prep(uint32_t const *st_d, uint32_t m, uint16_t *code, uint32_t *oldvals, uint32_t *R, uint32_t first_block, uint32_t n_blocks, cudaStream_t st);
 
 struct stitch_item

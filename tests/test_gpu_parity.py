@@ -60,6 +60,17 @@ def test_states_every_column_blocked(ctx, oracle, synth, m, n, C, E):
     check_states(ctx, oracle, rows, C, kernel=2, chunk=E)
 
 
+@pytest.mark.parametrize("m,n,C,E", [
+    (5, 40, 7, 0), (33, 100, 16, 9), (64, 300, 64, 0), (64, 300, 13, 17), (100, 257, 50, 33), (288, 90, 30, 9), (289, 90, 30, 0),
+    (257, 200, 33, 0), (545, 100, 25, 0), (1000, 150, 40, 0), (1000, 150, 40, 9), (1000, 120, 64, 17), (1056, 80, 20, 33),
+    (1057, 80, 20, 33), (2500, 90, 32, 0), (5000, 70, 35, 0),
+])
+def test_states_every_column_chunked(ctx, oracle, synth, m, n, C, E):
+    """The chunked column step (fsq_cstep.cuh: float one-hot arithmetic, padded rows) in every chunk length and CTA shape."""
+    rows = synth.synth_rows(m, n, seed=m + n, founders=max(2, m // 12), gaps=(m % 2 == 0), recomb_block=37, mu=0.02, gap=0.02)
+    check_states(ctx, oracle, rows, C, kernel=3, chunk=E)
+
+
 def test_states_blocked_nul_and_wide_alphabets(ctx, oracle):
     """NUL bytes in the rows (comp 0 is then a real symbol), 8 symbols, and more than 8 (falls back to the striped step)."""
     rng = np.random.default_rng(11)
@@ -156,6 +167,21 @@ def test_segmentation_matches_oracle(ctx, oracle, synth, m, n, L, C, founders):
     rows = synth.synth_rows(m, n, seed=m + L, founders=founders, gaps=(founders % 2 == 0))
     res = compare_segmentation(ctx, oracle, rows, L, C or None)
     assert res is not None
+
+
+@pytest.mark.parametrize("store,kernel", [(0, 0), (1, 0), (-1, 2), (-1, 1)])
+@pytest.mark.parametrize("m,n,L,C", [(200, 3000, 20, 100), (1000, 1500, 20, 128), (1101, 900, 8, 77)])
+def test_segmentation_stored_states_and_rescan(ctx, oracle, synth, store, kernel, m, n, L, C):
+    """States at the traceback positions: out of the states pass B keeps (TMA bulk store) or by the re-scan (pass C); and
+    the older step kernels (striped, blocked) through the same pipeline."""
+    rows = synth.synth_rows(m, n, seed=m + L + 1, founders=9, gaps=True)
+    ctx.set_option("store_states", store)
+    ctx.set_option("kernel", kernel)
+    ctx.reset_stats()
+    res = compare_segmentation(ctx, oracle, rows, L, C, sets=False)
+    assert res is not None
+    if kernel == 0:
+        assert ctx.stat("store_states") == (1 if store else 0)
 
 
 def test_segmentation_edge_lengths(ctx, oracle, synth):
