@@ -31,6 +31,7 @@ struct fsq_ctx
 	std::map <std::string, int64_t> opts;
 	std::map <std::string, double> stats;
 	std::vector <std::pair <std::string, std::pair <cudaEvent_t, cudaEvent_t>>> pending;   // phase timers
+	cudaEvent_t call_start{nullptr};       // recorded at the entry of fsq_segment: phases report their offset from it ("at_<phase>")
 
 	int64_t opt(char const *k, int64_t dflt) const { auto it = opts.find(k); return opts.end() == it ? dflt : it->second; }
 
@@ -165,6 +166,12 @@ void flush_phases(fsq_ctx *ctx)
 		cudaEventSynchronize(p.second.second);
 		cudaEventElapsedTime(&ms, p.second.first, p.second.second);
 		ctx->stats["ms_" + p.first] += ms;
+		if (ctx->call_start)
+		{
+			float at = 0;
+			if (cudaSuccess == cudaEventElapsedTime(&at, ctx->call_start, p.second.first)) ctx->stats["at_" + p.first] = at;
+			if (cudaSuccess == cudaEventElapsedTime(&at, ctx->call_start, p.second.second)) ctx->stats["end_" + p.first] = at;
+		}
 		cudaEventDestroy(p.second.first);
 		cudaEventDestroy(p.second.second);
 	}
@@ -344,144 +351,196 @@ __global__ void gather_stored_states_kernel(
 struct scan_state
 {
 	geometry g;
-	dbuf sum_a, sum_d, rel_a, rel_d, st_a, st_d, code, oldvals, R, items, item_begin;
+	dbuf sum_a, sum_d;          // [B][m]: block summaries (pass A); after the up-sweep, summaries of aligned spans
+	dbuf st_a, st_d;            // [B + 1][m]: state at every block start (slot B: at the end of the last block)
+	dbuf code, oldvals, R, items, item_begin;
+	hbuf h_items, h_begin;
+	bool relative{false};      // st_* are still relative to the identity state at the first local column
 };
 
-// Pass A (local scans), stitch, rank compression.  After this, st_[ad] hold the exact PBWT state at every block start.
-int prepare_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
+// Levels of stitch items (one CTA per item, one launch per level), uploaded in one go.
+struct stitch_plan
+{
+	std::vector <stitch_item> items;
+	std::vector <size_t> level_begin{0};
+	void end_level() { level_begin.push_back(items.size()); }
+};
+
+int run_stitch_plan(fsq_ctx *ctx, scan_state &S, stitch_plan const &plan, uint32_t m, std::vector <std::vector <std::pair <uint32_t *, uint32_t const *>>> const &copies)
+{
+	size_t const n = plan.items.size();
+	if (n)
+	{
+		// pinned staging lives in the scan state: it is released only after the caller's final synchronisation
+		CK(S.h_items.alloc(ctx, n * sizeof(stitch_item))); CK(S.h_begin.alloc(ctx, (n + 1) * 4));
+		memcpy(S.h_items.p, plan.items.data(), n * sizeof(stitch_item));
+		for (size_t i = 0; i <= n; ++i) S.h_begin.as <uint32_t>()[i] = (uint32_t) i;
+		CK(S.items.alloc(ctx, n * sizeof(stitch_item))); CK(S.item_begin.alloc(ctx, (n + 1) * 4));
+		CK(cudaMemcpyAsync(S.items.p, S.h_items.p, n * sizeof(stitch_item), cudaMemcpyHostToDevice, ctx->stream));
+		CK(cudaMemcpyAsync(S.item_begin.p, S.h_begin.p, (n + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+	}
+	for (size_t l = 0; l + 1 < plan.level_begin.size(); ++l)
+	{
+		if (l < copies.size())
+			for (auto const &c : copies[l])
+				CK(cudaMemcpyAsync(c.first, c.second, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+		size_t const first = plan.level_begin[l], count = plan.level_begin[l + 1] - first;
+		if (0 == count) continue;
+		stitch_args SA;
+		SA.items = S.items.as <stitch_item>();
+		SA.item_begin = S.item_begin.as <uint32_t>() + first;
+		SA.n_ctas = (uint32_t) count;
+		SA.m = m;
+		SA.n_tiles = S.g.n_tiles;
+		CK(launch_stitch(SA, ctx->stream));
+		ctx->stats["kernel_launches"] += 1;
+	}
+	return FSQ_OK;
+}
+
+// Pass A (local scans) and the prefix composition of the block summaries (composing summaries is
+// associative): an up-sweep turns the block summaries into summaries of aligned power-of-two spans in place, a down-sweep
+// turns those into the state at every block start *relative to the identity state at the first local column* -- which
+// for an alignment that starts at column 0 is the true state.  2 log2(B) levels of independent stitches.
+int local_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
 {
 	S.g = choose_geometry(ctx, msa);
 	geometry const &g = S.g;
 	uint32_t const m = msa->m;
-	size_t const bm = (size_t) g.B * m;
+	uint32_t const B = g.B;
+	size_t const bm = (size_t) B * m;
 	CK(S.sum_a.alloc(ctx, bm * 4)); CK(S.sum_d.alloc(ctx, bm * 4));
-	CK(S.st_a.alloc(ctx, bm * 4)); CK(S.st_d.alloc(ctx, bm * 4));
-	CK(S.code.alloc(ctx, bm * 2)); CK(S.oldvals.alloc(ctx, bm * 4)); CK(S.R.alloc(ctx, (size_t) g.B * 4));
+	CK(S.st_a.alloc(ctx, (bm + m) * 4)); CK(S.st_d.alloc(ctx, (bm + m) * 4));
+	CK(S.code.alloc(ctx, bm * 2)); CK(S.oldvals.alloc(ctx, bm * 4)); CK(S.R.alloc(ctx, (size_t) B * 4));
+	uint32_t *sum_a = S.sum_a.as <uint32_t>(), *sum_d = S.sum_d.as <uint32_t>();
+	uint32_t *st_a = S.st_a.as <uint32_t>(), *st_d = S.st_d.as <uint32_t>();
 
-	iota_kernel <<<(m + 255) / 256, 256, 0, ctx->stream>>>(S.st_a.as <uint32_t>(), S.st_d.as <uint32_t>(), m, (uint32_t) msa->col0);
+	iota_kernel <<<(m + 255) / 256, 256, 0, ctx->stream>>>(st_a, st_d, m, (uint32_t) msa->col0);
 	CK(cudaGetLastError());
+	S.relative = 0 != msa->col0;
 
-	if (g.B > 1)
 	{
 		phase pa(ctx, "pass_a");
 		block_args A;
 		fill_common(A, msa, g);
 		A.mode = MODE_LOCAL;
-		A.sum_a = S.sum_a.as <uint32_t>();
-		A.sum_d = S.sum_d.as <uint32_t>();
-		CK(launch_scan(A, g.B - 1, g, false, ctx->stream));
+		A.sum_a = sum_a;
+		A.sum_d = sum_d;
+		CK(launch_scan(A, B, g, false, ctx->stream));
 		pa.stop();
 		ctx->stats["kernel_launches"] += 1;
+	}
 
-		// Stitch in three levels, because composing summaries is associative:
-		//   1. every group of G consecutive blocks composes its block summaries left to right (groups in parallel),
-		//      giving the state at each of its block starts relative to the group start;
-		//   2. one CTA chains the group summaries into the true states at the group starts;
-		//   3. every remaining block start = (true state at its group start) o (its group-relative state), all in parallel.
-		phase ps(ctx, "stitch");
-		uint32_t const B = g.B;
-		uint32_t G = (uint32_t) ctx->opt("stitch_group", 0);
-		if (0 == G) G = (uint32_t) std::ceil(std::sqrt((double) B));
-		G = std::max <uint32_t>(1, std::min(G, B));
-		uint32_t const Q = (B + G - 1) / G;
-		CK(S.rel_a.alloc(ctx, ((size_t) B + 1) * m * 4)); CK(S.rel_d.alloc(ctx, ((size_t) B + 1) * m * 4));
-		uint32_t *sum_a = S.sum_a.as <uint32_t>(), *sum_d = S.sum_d.as <uint32_t>();
-		uint32_t *rel_a = S.rel_a.as <uint32_t>(), *rel_d = S.rel_d.as <uint32_t>();
-		uint32_t *st_a = S.st_a.as <uint32_t>(), *st_d = S.st_d.as <uint32_t>();
-		auto start_of = [&](uint32_t b) { return (uint32_t) (msa->col0 + (uint64_t) b * g.C); };
-		// state at the start of block b relative to the start of its group (b not the first of the group); the one after
-		// the first block is that block's own summary
-		auto rel_ptr = [&](uint32_t b, uint32_t *&a, uint32_t *&d) {
-			uint32_t const b0 = (b - 1) / G * G;       // group of block b - 1: b may be one past the group's last block
-			if (b == b0 + 1) { a = sum_a + (size_t) b0 * m; d = sum_d + (size_t) b0 * m; }
-			else { a = rel_a + (size_t) b * m; d = rel_d + (size_t) b * m; }
-		};
-		std::vector <stitch_item> items;
-		std::vector <uint32_t> begin[3];
-		for (uint32_t q = 0; q < Q; ++q)
+	phase ps(ctx, "stitch");
+	auto start_of = [&](uint64_t b) { return (uint32_t) (msa->col0 + b * g.C); };
+	auto U = [&](uint64_t i, uint32_t *&a, uint32_t *&d) { a = sum_a + i * m; d = sum_d + i * m; };
+	auto P = [&](uint64_t i, uint32_t *&a, uint32_t *&d) { a = st_a + (i + 1) * m; d = st_d + (i + 1) * m; };      // state at the end of block i
+	uint32_t levels = 0;
+	while ((1ull << (levels + 1)) <= B) ++levels;          // 2^levels <= B
+	stitch_plan plan;
+	std::vector <std::vector <std::pair <uint32_t *, uint32_t const *>>> copies;
+	// up-sweep: U[i] <- U[i - 2^l] o U[i] for every i with (i + 1) a multiple of 2^(l + 1)
+	for (uint32_t l = 0; l < levels; ++l)
+	{
+		uint64_t const half = 1ull << l, span = half << 1;
+		for (uint64_t i = span - 1; i < B; i += span)
 		{
-			uint32_t const b0 = q * G, b1 = std::min(B, b0 + G);
-			size_t const before = items.size();
-			for (uint32_t b = b0 + 1; b < b1 && b + 2 <= B; ++b)      // the last block has no summary: nothing follows it
-			{
-				// summary of [start(b0), start(b + 1)) = summary of [start(b0), start(b)) o summary of block b
-				stitch_item it;
-				memset(&it, 0, sizeof it);
-				uint32_t *ia, *id;
-				rel_ptr(b, ia, id);
-				it.in_a = ia; it.in_d = id;
-				it.pi = sum_a + (size_t) b * m; it.delta = sum_d + (size_t) b * m;
-				it.out_a = rel_a + (size_t) (b + 1) * m; it.out_d = rel_d + (size_t) (b + 1) * m;
-				it.s_mark = start_of(b);
-				items.push_back(it);
-			}
-			if (items.size() > before) begin[0].push_back((uint32_t) before);
-		}
-		begin[0].push_back((uint32_t) items.size());
-		size_t const n1 = items.size();
-		begin[1].push_back((uint32_t) n1);
-		for (uint32_t q = 0; q + 1 < Q; ++q)
-		{
-			uint32_t const b0 = q * G, b1 = b0 + G;
 			stitch_item it;
 			memset(&it, 0, sizeof it);
-			uint32_t *la, *ld;
-			rel_ptr(b1, la, ld);
-			it.in_a = st_a + (size_t) b0 * m; it.in_d = st_d + (size_t) b0 * m;
-			it.pi = la; it.delta = ld;
-			it.out_a = st_a + (size_t) b1 * m; it.out_d = st_d + (size_t) b1 * m;
-			it.s_mark = start_of(b0);
-			items.push_back(it);
+			uint32_t *la, *ld, *ra, *rd;
+			U(i - half, la, ld); U(i, ra, rd);
+			it.in_a = la; it.in_d = ld;
+			it.pi = ra; it.delta = rd;
+			it.out_a = ra; it.out_d = rd;                   // in place: the kernel holds the item in shared memory before it writes
+			it.s_mark = start_of(i + 1 - half);
+			plan.items.push_back(it);
 		}
-		begin[1].push_back((uint32_t) items.size());
-		for (uint32_t q = 0; q < Q; ++q)
+		plan.end_level();
+		copies.emplace_back();
+	}
+	// down-sweep: with 2^l the lowest set bit of i + 1, P[i] = U[i] when i + 1 == 2^l, else P[i - 2^l] o U[i]
+	for (int l = (int) levels; l >= 0; --l)
+	{
+		uint64_t const half = 1ull << l, span = half << 1;
+		copies.emplace_back();
+		for (uint64_t i = half - 1; i < B; i += span)
 		{
-			uint32_t const b0 = q * G, b1 = std::min(B, b0 + G);
-			for (uint32_t b = b0 + 1; b < b1; ++b)
+			uint32_t *ua, *ud, *pa_, *pd_;
+			U(i, ua, ud); P(i, pa_, pd_);
+			if (i + 1 == half)
 			{
-				stitch_item it;
-				memset(&it, 0, sizeof it);
-				uint32_t *la, *ld;
-				rel_ptr(b, la, ld);
-				it.in_a = st_a + (size_t) b0 * m; it.in_d = st_d + (size_t) b0 * m;
-				it.pi = la; it.delta = ld;
-				it.out_a = st_a + (size_t) b * m; it.out_d = st_d + (size_t) b * m;
-				it.s_mark = start_of(b0);
-				begin[2].push_back((uint32_t) items.size());
-				items.push_back(it);
+				copies.back().push_back({pa_, ua});
+				copies.back().push_back({pd_, ud});
+				continue;
 			}
+			stitch_item it;
+			memset(&it, 0, sizeof it);
+			uint32_t *qa, *qd;
+			P(i - half, qa, qd);
+			it.in_a = qa; it.in_d = qd;
+			it.pi = ua; it.delta = ud;
+			it.out_a = pa_; it.out_d = pd_;
+			it.s_mark = start_of(i + 1 - half);
+			plan.items.push_back(it);
 		}
-		begin[2].push_back((uint32_t) items.size());
-		std::vector <uint32_t> begin_all;
-		size_t off[3];
-		for (int ph = 0; ph < 3; ++ph) { off[ph] = begin_all.size(); begin_all.insert(begin_all.end(), begin[ph].begin(), begin[ph].end()); }
-		CK(S.items.alloc(ctx, items.size() * sizeof(stitch_item)));
-		CK(S.item_begin.alloc(ctx, begin_all.size() * 4));
-		CK(cudaMemcpyAsync(S.items.p, items.data(), items.size() * sizeof(stitch_item), cudaMemcpyHostToDevice, ctx->stream));
-		CK(cudaMemcpyAsync(S.item_begin.p, begin_all.data(), begin_all.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
-		CK(cudaStreamSynchronize(ctx->stream));     // items and begin_all are stack vectors
-		for (int ph = 0; ph < 3; ++ph)
-		{
-			uint32_t const n_ctas = (uint32_t) begin[ph].size() - 1;
-			if (0 == n_ctas || begin[ph].front() == begin[ph].back()) continue;
-			stitch_args SA;
-			SA.items = S.items.as <stitch_item>();
-			SA.item_begin = S.item_begin.as <uint32_t>() + off[ph];
-			SA.n_ctas = n_ctas;
-			SA.m = m;
-			SA.n_tiles = g.n_tiles;
-			CK(launch_stitch(SA, ctx->stream));
-			ctx->stats["kernel_launches"] += 1;
-		}
-		ps.stop();
+		plan.end_level();
 	}
 	{
-		phase pp(ctx, "prep");
-		CK(launch_prep(S.st_d.as <uint32_t>(), m, S.code.as <uint16_t>(), S.oldvals.as <uint32_t>(), S.R.as <uint32_t>(), 0, g.B, ctx->stream));
-		pp.stop();
-		ctx->stats["kernel_launches"] += 1;
+		int const rc = run_stitch_plan(ctx, S, plan, m, copies);
+		if (rc) return rc;
 	}
+	ps.stop();
 	return FSQ_OK;
+}
+
+// Column-sharded operation: the states of local_scan() are relative to the identity state at the first local column;
+// given the true state there (d_a, d_d on the device), every block start becomes (true state) o (relative state).
+int apply_start_state(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S, uint32_t const *d_a, uint32_t const *d_d)
+{
+	geometry const &g = S.g;
+	uint32_t const m = msa->m;
+	uint32_t *st_a = S.st_a.as <uint32_t>(), *st_d = S.st_d.as <uint32_t>();
+	phase ps(ctx, "stitch");
+	stitch_plan plan;
+	for (uint64_t b = 1; b <= g.B; ++b)
+	{
+		stitch_item it;
+		memset(&it, 0, sizeof it);
+		it.in_a = d_a; it.in_d = d_d;
+		it.pi = st_a + b * m; it.delta = st_d + b * m;
+		it.out_a = st_a + b * m; it.out_d = st_d + b * m;
+		it.s_mark = (uint32_t) msa->col0;
+		plan.items.push_back(it);
+	}
+	plan.end_level();
+	CK(cudaStreamSynchronize(ctx->stream));      // the staging buffers of the scan state are about to be rewritten
+	int const rc = run_stitch_plan(ctx, S, plan, m, {});
+	if (rc) return rc;
+	CK(cudaMemcpyAsync(st_a, d_a, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+	CK(cudaMemcpyAsync(st_d, d_d, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+	ps.stop();
+	S.relative = false;
+	return FSQ_OK;
+}
+
+// Rank compression of the (true) block start divergences.
+int compress_starts(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
+{
+	phase pp(ctx, "prep");
+	CK(launch_prep(S.st_d.as <uint32_t>(), msa->m, S.code.as <uint16_t>(), S.oldvals.as <uint32_t>(), S.R.as <uint32_t>(), 0, S.g.B, ctx->stream));
+	pp.stop();
+	ctx->stats["kernel_launches"] += 1;
+	return FSQ_OK;
+}
+
+// Pass A, stitch, rank compression for an alignment that starts at column 0.  After this, st_[ad] hold the exact PBWT
+// state at every block start.
+int prepare_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
+{
+	int rc = local_scan(ctx, msa, S);
+	if (rc) return rc;
+	if (S.relative) return fail(ctx, FSQ_ERR_ARG, "this entry point needs an alignment that starts at column 0 (column shards go through fsq_shard_*)");
+	return compress_starts(ctx, msa, S);
 }
 
 // Pass C: (a_c, d_c) at the given ascending local columns c (1 <= c <= n) into dump_a / dump_d (count x m).
@@ -802,6 +861,9 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	uint32_t const m = msa->m;
 	if (n < 2 * L) return fail(ctx, FSQ_ERR_SHORT, "n = %llu < 2L = %llu: short path", (unsigned long long) n, (unsigned long long) (2 * L));
 	CK(cudaSetDevice(ctx->device));
+	flush_phases(ctx);
+	if (!ctx->call_start) CK(cudaEventCreate(&ctx->call_start));
+	CK(cudaEventRecord(ctx->call_start, ctx->stream));
 
 	scan_state S;
 	if ((rc = prepare_scan(ctx, msa, S))) return rc;
