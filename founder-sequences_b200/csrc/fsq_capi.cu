@@ -587,6 +587,360 @@ int dump_states(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S, std::vector <ui
 	return FSQ_OK;
 }
 
+} // namespace
+
+// One run of the long path over the columns one rank holds (all of them on a single GPU), cut into the stages between
+// which column-sharded ranks exchange data.  fsq_segment() runs the stages back to back; fsq_shard_*() exposes them.
+struct fsq_shard
+{
+	fsq_ctx *ctx{};
+	fsq_msa const *msa{};
+	uint32_t m{};
+	uint64_t n{};               // columns of the whole alignment
+	uint64_t L{};
+	uint64_t c0{}, c1{};        // this rank's columns [c0, c1)
+	scan_state S;
+	bool started{false};        // block start states are true and compressed
+
+	// DP: the table is global (every rank holds all of it), the top lists are local
+	uint64_t dp_size{};
+	uint32_t n_entries{}, n_blk{}, n_levels{}, t_first{}, t_last{};
+	uint32_t chunk{}, n_chunks{}, cap{}, rounds{};
+	bool single_chain{false};
+	dbuf tb_max, tb_lb, tb_size, mk, lev, flags, chunk_level, cnt, h0, toplist, states;
+	uint64_t state_stride{};
+
+	// traceback (replicated) and reduction
+	uint32_t T{}, K{};
+	dbuf tr_lb, tr_rb, tr_max, tr_size, lists, d_next, d_nsize;
+	std::vector <uint64_t> tb_lb_h, tb_rb_h;
+	std::vector <uint32_t> tb_max_h, tb_size_h;
+	uint32_t pos_first{}, pos_last{};          // traceback positions whose right bound this rank holds the state of
+	std::vector <uint64_t> red_lb, red_rb;
+	std::vector <uint32_t> red_size, red_pos;  // reduced segments; red_pos: index into the traceback
+	uint32_t seg_first{}, seg_last{};          // reduced segments whose state this rank holds
+	dbuf red_a, red_d;                         // [seg_last - seg_first][m]
+
+	dp_args dp() const
+	{
+		dp_args D;
+		memset(&D, 0, sizeof D);
+		D.m = m; D.n = n; D.L = L; D.col_base = c0; D.t_first = t_first; D.t_last = t_last;
+		D.toplist = toplist.as <uint2>(); D.cap = cap; D.cnt = cnt.as <uint32_t>(); D.h0 = h0.as <uint32_t>();
+		D.tb_max = tb_max.as <uint32_t>(); D.tb_lb = tb_lb.as <uint32_t>(); D.tb_size = tb_size.as <uint32_t>();
+		D.mk = mk.as <uint64_t>();
+		D.lev = lev.as <uint32_t>(); D.n_blk = n_blk; D.n_levels = n_levels;
+		D.n_entries = n_entries;
+		D.chunk = single_chain ? (n_entries + 63) / 64 * 64 : chunk;
+		D.n_chunks = single_chain ? 1 : n_chunks;
+		D.chunk_level = chunk_level.as <uint32_t>();
+		D.flags = flags.as <uint32_t>();
+		return D;
+	}
+};
+
+namespace {
+
+int shard_init(fsq_shard *P, fsq_ctx *ctx, fsq_msa const *msa, uint64_t n_total, uint64_t L)
+{
+	P->ctx = ctx; P->msa = msa; P->m = msa->m; P->n = n_total; P->L = L;
+	P->c0 = msa->col0; P->c1 = msa->col0 + msa->n;
+	uint64_t const n = n_total;
+	P->dp_size = n - L + 1;
+	P->n_entries = (uint32_t) (n - 2 * L + 1);
+	P->n_blk = (uint32_t) (P->dp_size / 64 + 1);
+	P->n_levels = 1;
+	while ((1ull << P->n_levels) <= P->n_blk) ++P->n_levels;
+	// entry t is computed at column t + L - 1
+	uint64_t const lo = P->c0 + 1 > L ? P->c0 + 1 - L : 0, hi = P->c1 + 1 > L ? P->c1 + 1 - L : 0;
+	P->t_first = (uint32_t) std::min <uint64_t>(lo, P->n_entries);
+	P->t_last = (uint32_t) std::min <uint64_t>(hi, P->n_entries);
+	// chains: enough to fill the device a few times over, each a whole number of 64-entry rmq blocks, on a global grid
+	{
+		int64_t want = ctx->opt("dp_chunks", 0);
+		if (want <= 0) want = 4 * (int64_t) ctx->prop.multiProcessorCount;
+		uint64_t const own = std::max <uint64_t>(1, P->t_last - P->t_first);
+		uint64_t c = (own + (uint64_t) want - 1) / (uint64_t) want;
+		c = std::max <uint64_t>(c, std::max <uint64_t>(256, 8 * L));
+		if (1 == want) c = P->n_entries;
+		c = (c + 63) / 64 * 64;
+		P->chunk = (uint32_t) std::min <uint64_t>(c, 0xffffffc0ull);
+		P->n_chunks = (P->n_entries + P->chunk - 1) / P->chunk;
+	}
+	P->cap = (uint32_t) std::min <int64_t>(P->m, std::max <int64_t>(1, ctx->opt("cap", 127)));
+	P->state_stride = ((uint64_t) P->m + 3) & ~3ull;
+	return FSQ_OK;
+}
+
+// Pass B over this rank's columns with the current top-list bound; resets the DP table.
+int shard_scan(fsq_shard *P)
+{
+	fsq_ctx *ctx = P->ctx;
+	fsq_msa const *msa = P->msa;
+	geometry const &g = P->S.g;
+	uint32_t const m = P->m;
+	uint64_t const nl = msa->n;
+	if (!P->tb_max.p)
+	{
+		CK(P->tb_max.alloc(ctx, P->dp_size * 4)); CK(P->tb_lb.alloc(ctx, P->dp_size * 4)); CK(P->tb_size.alloc(ctx, P->dp_size * 4));
+		CK(P->mk.alloc(ctx, P->dp_size * 8)); CK(P->lev.alloc(ctx, (size_t) P->n_levels * P->n_blk * 4)); CK(P->flags.alloc(ctx, 16));
+		CK(P->cnt.alloc(ctx, nl * 4)); CK(P->h0.alloc(ctx, nl * 4));
+		CK(P->chunk_level.alloc(ctx, (size_t) P->n_chunks * 8));
+		// Pass B keeps the state of every column when 4 m n bytes fit comfortably (option store_states: -1 auto, 0 never,
+		// 1 always); the states at the segment boundaries are then a gather instead of a third scan.
+		int64_t const want = ctx->opt("store_states", -1);
+		bool keep = false;
+		if (g.chunked && 0 != want)
+		{
+			size_t free_b = 0, total_b = 0;
+			CK(cudaMemGetInfo(&free_b, &total_b));
+			size_t cached = 0;
+			for (auto const &blk : ctx->dev_cache) cached += blk.bytes;
+			size_t const need = (size_t) (P->state_stride * 4 * nl);
+			size_t const other = (size_t) nl * (P->cap + 1) * 8 + (size_t) nl * 64 + ((size_t) 1 << 30);
+			keep = (1 == want) || need + other < free_b + cached;
+			if (keep && cudaSuccess != P->states.alloc(ctx, need)) { cudaGetLastError(); keep = false; }
+		}
+		ctx->stats["store_states"] = keep ? 1 : 0;
+	}
+	CK(P->toplist.alloc(ctx, (size_t) nl * (P->cap + 1) * sizeof(uint2)));
+	// entries the per-column DP writes start from 0 (the first round's stand-in for "nothing known"); the ones the
+	// reference never writes keep its defaults; masks and rmq cells start from values that index inside the table
+	CK(cudaMemsetAsync(P->tb_max.p, 0xff, P->dp_size * 4, ctx->stream));
+	CK(cudaMemsetAsync(P->tb_max.p, 0, (size_t) P->n_entries * 4, ctx->stream));
+	CK(cudaMemsetAsync(P->tb_size.p, 0xff, P->dp_size * 4, ctx->stream));
+	CK(cudaMemsetAsync(P->tb_lb.p, 0, P->dp_size * 4, ctx->stream));
+	CK(cudaMemsetAsync(P->mk.p, 0xff, P->dp_size * 8, ctx->stream));
+	CK(cudaMemsetAsync(P->lev.p, 0, (size_t) P->n_levels * P->n_blk * 4, ctx->stream));
+	CK(cudaMemsetAsync(P->flags.p, 0, 16, ctx->stream));
+	P->rounds = 0;
+	P->single_chain = false;
+	{
+		phase pb(ctx, "pass_b");
+		block_args A;
+		fill_common(A, msa, g);
+		A.mode = MODE_EXACT;
+		A.st_a = P->S.st_a.as <uint32_t>();
+		A.code = P->S.code.as <uint16_t>();
+		A.oldvals = P->S.oldvals.as <uint32_t>();
+		A.R = P->S.R.as <uint32_t>();
+		A.toplist = P->toplist.as <uint2>();
+		A.cap = P->cap;
+		A.cnt = P->cnt.as <uint32_t>();
+		A.h0 = P->h0.as <uint32_t>();
+		A.states = P->states.as <uint32_t>();
+		A.state_stride = P->state_stride;
+		CK(launch_scan(A, g.B, g, true, ctx->stream));
+		pb.stop();
+		ctx->stats["kernel_launches"] += 1;
+	}
+	return FSQ_OK;
+}
+
+// One DP round: every own chain once against the table as it stands.  changed: some stored value changed;
+// reach: the farthest any column has looked back so far (entries).
+int shard_dp_round(fsq_shard *P, uint32_t *changed, uint32_t *reach)
+{
+	fsq_ctx *ctx = P->ctx;
+	phase pd(ctx, "dp");
+	dp_args const D = P->dp();
+	CK(cudaMemsetAsync(P->flags.p, 0, 4, ctx->stream));
+	CK(launch_dp_chains(D, ctx->stream));
+	ctx->stats["kernel_launches"] += 1;
+	++P->rounds;
+	uint32_t h_flags[4] = {0, 0, 0, 0};
+	CK(cudaMemcpyAsync(h_flags, P->flags.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+	pd.stop();
+	CK(cudaStreamSynchronize(ctx->stream));
+	*changed = h_flags[0];
+	*reach = h_flags[2];
+	return FSQ_OK;
+}
+
+// Between rounds: with guess, level the table (fsq_dp.cu) using the given look-back; rebuild masks and rmq tables.
+int shard_dp_sync(fsq_shard *P, int guess, uint32_t reach)
+{
+	fsq_ctx *ctx = P->ctx;
+	phase pd(ctx, "dp");
+	dp_args const D = P->dp();
+	if (guess)
+	{
+		CK(cudaMemcpyAsync(P->flags.as <uint32_t>() + 2, &reach, 4, cudaMemcpyHostToDevice, ctx->stream));
+		CK(launch_dp_guess(D, ctx->stream));
+		ctx->stats["kernel_launches"] += 4 + P->n_levels;
+	}
+	else
+	{
+		CK(launch_dp_rebuild(D, ctx->stream));
+		ctx->stats["kernel_launches"] += 1 + P->n_levels;
+	}
+	pd.stop();
+	CK(cudaStreamSynchronize(ctx->stream));      // reach is a stack variable of the caller's frame
+	return FSQ_OK;
+}
+
+// The last entry (segmentation_lp_context.cc:165-185), on the rank that holds the last column; and this rank's
+// "top list too short" flag (1 + column, 0 = none).
+int shard_dp_final(fsq_shard *P, uint32_t *overflow)
+{
+	fsq_ctx *ctx = P->ctx;
+	phase pd(ctx, "dp");
+	if (P->c1 == P->n)
+	{
+		CK(launch_dp_final(P->dp(), ctx->stream));
+		ctx->stats["kernel_launches"] += 1;
+	}
+	uint32_t h_flags[2] = {0, 0};
+	CK(cudaMemcpyAsync(h_flags, P->flags.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+	pd.stop();
+	CK(cudaStreamSynchronize(ctx->stream));
+	*overflow = h_flags[1];
+	ctx->stats["dp_rounds"] += P->rounds;
+	ctx->stats["dp_chunks"] = P->n_chunks;
+	return FSQ_OK;
+}
+
+// Traceback over the (complete, global) table -- segmentation_lp_context.cc:191-224 -- on the device by pointer doubling;
+// every rank does the same.  Leaves the traceback on the device (text order) and on the host.
+int shard_traceback(fsq_shard *P)
+{
+	fsq_ctx *ctx = P->ctx;
+	phase pt(ctx, "traceback");
+	trace_args TA;
+	memset(&TA, 0, sizeof TA);
+	TA.tb_lb = P->tb_lb.as <uint32_t>(); TA.tb_max = P->tb_max.as <uint32_t>(); TA.tb_size = P->tb_size.as <uint32_t>();
+	TA.L = (uint32_t) P->L; TA.dp_size = (uint32_t) P->dp_size;
+	TA.levels = 1;
+	while ((1ull << TA.levels) <= P->dp_size / P->L + 1) ++TA.levels;
+	dbuf jump, count;
+	CK(jump.alloc(ctx, (size_t) TA.levels * P->dp_size * 4)); CK(count.alloc(ctx, 4));
+	TA.jump = jump.as <uint32_t>(); TA.count = count.as <uint32_t>();
+	CK(launch_trace_tables(TA, ctx->stream));
+	ctx->stats["kernel_launches"] += TA.levels + 1;
+	uint32_t T = 0;
+	CK(cudaMemcpyAsync(&T, count.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	P->T = T;
+	CK(P->tr_lb.alloc(ctx, (size_t) T * 4)); CK(P->tr_rb.alloc(ctx, (size_t) T * 8)); CK(P->tr_max.alloc(ctx, (size_t) T * 4)); CK(P->tr_size.alloc(ctx, (size_t) T * 4));
+	TA.out_lb = P->tr_lb.as <uint32_t>(); TA.out_rb = P->tr_rb.as <uint64_t>(); TA.out_max = P->tr_max.as <uint32_t>(); TA.out_size = P->tr_size.as <uint32_t>();
+	CK(launch_trace_gather(TA, T, ctx->stream));
+	ctx->stats["kernel_launches"] += 1;
+	hbuf stage;
+	CK(stage.alloc(ctx, (size_t) T * 20));
+	uint64_t *h_rb = stage.as <uint64_t>();
+	uint32_t *h_lb = (uint32_t *) (h_rb + T), *h_max = h_lb + T, *h_size = h_max + T;
+	CK(cudaMemcpyAsync(h_rb, P->tr_rb.p, (size_t) T * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(h_lb, P->tr_lb.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(h_max, P->tr_max.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(h_size, P->tr_size.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	pt.stop();
+	CK(cudaStreamSynchronize(ctx->stream));
+	P->tb_rb_h.assign(h_rb, h_rb + T);
+	P->tb_lb_h.assign(h_lb, h_lb + T);
+	P->tb_max_h.assign(h_max, h_max + T);
+	P->tb_size_h.assign(h_size, h_size + T);
+	P->K = P->tb_max_h.back();
+	// the traceback positions this rank holds the state of: right bounds in (c0, c1]
+	P->pos_first = (uint32_t) (std::upper_bound(P->tb_rb_h.begin(), P->tb_rb_h.end(), P->c0) - P->tb_rb_h.begin());
+	P->pos_last = (uint32_t) (std::upper_bound(P->tb_rb_h.begin(), P->tb_rb_h.end(), P->c1) - P->tb_rb_h.begin());
+	return FSQ_OK;
+}
+
+// The rows of the reduction's count lists for the traceback positions this rank owns (the others arrive by exchange).
+int shard_reduce_lists(fsq_shard *P)
+{
+	fsq_ctx *ctx = P->ctx;
+	uint32_t const width = P->K + 1;
+	CK(P->lists.alloc(ctx, (size_t) P->T * width * sizeof(uint2)));
+	phase pr(ctx, "reduce");
+	reduce_args R;
+	memset(&R, 0, sizeof R);
+	R.T = P->T; R.K = P->K; R.width = width;
+	R.tb_rb = P->tr_rb.as <uint64_t>(); R.tb_size = P->tr_size.as <uint32_t>();
+	R.lists = P->lists.as <uint2>();
+	R.toplist = P->toplist.as <uint2>(); R.cap = P->cap; R.cnt = P->cnt.as <uint32_t>(); R.col_base = P->c0;
+	R.pos_first = P->pos_first; R.pos_last = P->pos_last;
+	CK(launch_reduce_lists(R, ctx->stream));
+	ctx->stats["kernel_launches"] += 1;
+	pr.stop();
+	return FSQ_OK;
+}
+
+// Greedy reduction (segmentation_lp_context.cc:335-390) from the complete lists; every rank does the same.
+int shard_reduce(fsq_shard *P)
+{
+	fsq_ctx *ctx = P->ctx;
+	uint32_t const T = P->T;
+	phase pr(ctx, "reduce");
+	hbuf h_next;
+	CK(P->d_next.alloc(ctx, (size_t) T * 4)); CK(P->d_nsize.alloc(ctx, (size_t) T * 4)); CK(h_next.alloc(ctx, (size_t) T * 8));
+	reduce_args R;
+	memset(&R, 0, sizeof R);
+	R.T = T; R.K = P->K; R.width = P->K + 1;
+	R.tb_rb = P->tr_rb.as <uint64_t>(); R.tb_size = P->tr_size.as <uint32_t>();
+	R.lists = P->lists.as <uint2>();
+	R.next = P->d_next.as <uint32_t>(); R.next_size = P->d_nsize.as <uint32_t>();
+	CK(launch_reduce(R, ctx->stream));
+	ctx->stats["kernel_launches"] += 1;
+	uint32_t *nxt = h_next.as <uint32_t>(), *nsz = nxt + T;
+	CK(cudaMemcpyAsync(nxt, P->d_next.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(nsz, P->d_nsize.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	pr.stop();
+	CK(cudaStreamSynchronize(ctx->stream));
+	P->red_lb.clear(); P->red_rb.clear(); P->red_size.clear(); P->red_pos.clear();
+	uint64_t cur_lb = 0;
+	for (uint32_t u = 0; u < T; )
+	{
+		uint32_t const last = nxt[u];
+		P->red_lb.push_back(cur_lb);
+		P->red_rb.push_back(P->tb_rb_h[last]);
+		P->red_size.push_back(nsz[u]);
+		P->red_pos.push_back(last);
+		cur_lb = P->tb_rb_h[last];
+		u = last + 1;
+	}
+	// the reduced segments whose end state this rank holds
+	P->seg_first = (uint32_t) (std::upper_bound(P->red_rb.begin(), P->red_rb.end(), P->c0) - P->red_rb.begin());
+	P->seg_last = (uint32_t) (std::upper_bound(P->red_rb.begin(), P->red_rb.end(), P->c1) - P->red_rb.begin());
+	return FSQ_OK;
+}
+
+// (a, d) at the right bounds of this rank's reduced segments (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35):
+// a gather out of the states pass B kept, else a re-scan of the blocks that hold them (pass C).
+int shard_reduced_states(fsq_shard *P)
+{
+	fsq_ctx *ctx = P->ctx;
+	uint32_t const m = P->m;
+	uint32_t const cnt = P->seg_last - P->seg_first;
+	CK(P->red_a.alloc(ctx, (size_t) std::max <uint32_t>(cnt, 1) * m * 4)); CK(P->red_d.alloc(ctx, (size_t) std::max <uint32_t>(cnt, 1) * m * 4));
+	if (0 == cnt) return FSQ_OK;
+	if (P->states.p)
+	{
+		hbuf h_rb;
+		dbuf d_rb;
+		CK(h_rb.alloc(ctx, (size_t) cnt * 8)); CK(d_rb.alloc(ctx, (size_t) cnt * 8));
+		for (uint32_t i = 0; i < cnt; ++i) h_rb.as <uint64_t>()[i] = P->red_rb[P->seg_first + i] - P->c0;      // local right bounds
+		CK(cudaMemcpyAsync(d_rb.p, h_rb.p, (size_t) cnt * 8, cudaMemcpyHostToDevice, ctx->stream));
+		phase pc(ctx, "pass_c");
+		dim3 const grid((m + 255) / 256, cnt);
+		gather_stored_states_kernel <<<grid, 256, 0, ctx->stream>>>(P->states.as <uint32_t>(), P->state_stride, d_rb.as <uint64_t>(), m, P->S.g.C, P->c0,
+			P->S.oldvals.as <uint32_t>(), P->S.R.as <uint32_t>(), P->red_a.as <uint32_t>(), P->red_d.as <uint32_t>());
+		CK(cudaGetLastError());
+		pc.stop();
+		ctx->stats["kernel_launches"] += 1;
+		CK(cudaStreamSynchronize(ctx->stream));
+		P->states.release();
+	}
+	else
+	{
+		std::vector <uint64_t> cols(cnt);
+		for (uint32_t i = 0; i < cnt; ++i) cols[i] = P->red_rb[P->seg_first + i] - P->c0;
+		int const rc = dump_states(ctx, P->msa, P->S, cols, P->red_a.as <uint32_t>(), P->red_d.as <uint32_t>());
+		if (rc) return rc;
+	}
+	return FSQ_OK;
+}
+
 int check_shape(fsq_ctx *ctx, fsq_msa const *msa)
 {
 	if (!ctx || !msa) return fail(ctx, FSQ_ERR_ARG, "null context or alignment");
@@ -865,144 +1219,44 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	if (!ctx->call_start) CK(cudaEventCreate(&ctx->call_start));
 	CK(cudaEventRecord(ctx->call_start, ctx->stream));
 
-	scan_state S;
-	if ((rc = prepare_scan(ctx, msa, S))) return rc;
-	geometry const &g = S.g;
+	fsq_shard run;
+	fsq_shard *P = &run;
+	if ((rc = shard_init(P, ctx, msa, n, L))) return rc;
+	if ((rc = prepare_scan(ctx, msa, P->S))) return rc;
+	geometry const &g = P->S.g;
 
 	// ---- pass B + DP; the top-list bound grows until the DP proves the result exact ----
-	uint64_t const dp_size = n - L + 1;
-	uint32_t const n_entries = (uint32_t) (n - 2 * L + 1);
-	uint32_t const n_blk = (uint32_t) (dp_size / 64 + 1);
-	uint32_t n_levels = 1;
-	while ((1ull << n_levels) <= n_blk) ++n_levels;
-	dbuf tb_max, tb_lb, tb_size, mk, lev, flags, chunk_level, cnt, h0, toplist;
-	CK(tb_max.alloc(ctx, dp_size * 4)); CK(tb_lb.alloc(ctx, dp_size * 4)); CK(tb_size.alloc(ctx, dp_size * 4)); CK(mk.alloc(ctx, dp_size * 8));
-	CK(lev.alloc(ctx, (size_t) n_levels * n_blk * 4)); CK(flags.alloc(ctx, 16));
-	CK(cnt.alloc(ctx, n * 4)); CK(h0.alloc(ctx, n * 4));
-	// chains: enough to fill the device a few times over, each a whole number of 64-entry rmq blocks
-	uint32_t chunk, n_chunks;
-	{
-		int64_t want = ctx->opt("dp_chunks", 0);
-		if (want <= 0) want = 4 * (int64_t) ctx->prop.multiProcessorCount;
-		uint64_t c = (n_entries + (uint64_t) want - 1) / (uint64_t) want;
-		c = std::max <uint64_t>(c, std::max <uint64_t>(256, 8 * L));
-		if (1 == want) c = n_entries;
-		c = (c + 63) / 64 * 64;
-		chunk = (uint32_t) std::min <uint64_t>(c, 0xffffffc0ull);
-		n_chunks = (n_entries + chunk - 1) / chunk;
-	}
-	CK(chunk_level.alloc(ctx, (size_t) n_chunks * 8));
-	uint32_t cap = (uint32_t) std::min <int64_t>(m, std::max <int64_t>(1, ctx->opt("cap", 127)));
-	// Pass B keeps the state of every column when 4 m n bytes fit comfortably (option store_states: -1 auto, 0 never,
-	// 1 always); the states at the traceback positions are then a gather instead of a third scan.
-	dbuf states;
-	uint64_t const state_stride = ((uint64_t) m + 3) & ~3ull;
-	{
-		int64_t const want = ctx->opt("store_states", -1);
-		size_t free_b = 0, total_b = 0;
-		bool keep = false;
-		if (g.chunked && 0 != want)
-		{
-			CK(cudaMemGetInfo(&free_b, &total_b));
-			size_t cached = 0;
-			for (auto const &blk : ctx->dev_cache) cached += blk.bytes;
-			size_t const need = (size_t) (state_stride * 4 * n);
-			size_t const other = (size_t) n * (cap + 1) * 8 + (size_t) n * 64 + ((size_t) 1 << 30);
-			keep = (1 == want) || need + other < free_b + cached;
-			if (keep && cudaSuccess != states.alloc(ctx, need)) { cudaGetLastError(); keep = false; }
-		}
-		ctx->stats["store_states"] = keep ? 1 : 0;
-	}
+	int64_t const max_rounds = std::max <int64_t>(2, ctx->opt("dp_max_rounds", 16));
+	int64_t const guess_rounds = ctx->opt("dp_guess_rounds", 8);      // after these the table is left to settle by itself
 	while (true)
 	{
-		CK(toplist.alloc(ctx, (size_t) n * (cap + 1) * sizeof(uint2)));
-		// entries the per-column DP writes start from 0 (the first round's stand-in for "nothing known"); the ones the
-		// reference never writes keep its defaults; masks and rmq cells start from values that index inside the table
-		CK(cudaMemsetAsync(tb_max.p, 0xff, dp_size * 4, ctx->stream));
-		CK(cudaMemsetAsync(tb_max.p, 0, (size_t) n_entries * 4, ctx->stream));
-		CK(cudaMemsetAsync(tb_size.p, 0xff, dp_size * 4, ctx->stream));
-		CK(cudaMemsetAsync(tb_lb.p, 0, dp_size * 4, ctx->stream));
-		CK(cudaMemsetAsync(mk.p, 0xff, dp_size * 8, ctx->stream));
-		CK(cudaMemsetAsync(lev.p, 0, (size_t) n_levels * n_blk * 4, ctx->stream));
+		if ((rc = shard_scan(P))) return rc;
+		while (true)
 		{
-			phase pb(ctx, "pass_b");
-			block_args A;
-			fill_common(A, msa, g);
-			A.mode = MODE_EXACT;
-			A.st_a = S.st_a.as <uint32_t>();
-			A.code = S.code.as <uint16_t>();
-			A.oldvals = S.oldvals.as <uint32_t>();
-			A.R = S.R.as <uint32_t>();
-			A.toplist = toplist.as <uint2>();
-			A.cap = cap;
-			A.cnt = cnt.as <uint32_t>();
-			A.h0 = h0.as <uint32_t>();
-			A.states = states.as <uint32_t>();
-			A.state_stride = state_stride;
-			CK(launch_scan(A, g.B, g, true, ctx->stream));
-			pb.stop();
-			ctx->stats["kernel_launches"] += 1;
+			uint32_t changed = 0, reach = 0;
+			if ((rc = shard_dp_round(P, &changed, &reach))) return rc;
+			if (1 == P->n_chunks || P->single_chain) break;      // a single chain is the reference's own order: exact as it stands
+			if (P->rounds > 1 && 0 == changed) break;            // nothing changed: every entry was computed from the table it is part of
+			if (P->rounds >= max_rounds)
+			{
+				// the guesses keep failing: one chain over everything, exact in a single round
+				P->single_chain = true;
+				ctx->stats["dp_fallbacks"] += 1;
+			}
+			else if (P->rounds <= guess_rounds)
+			{
+				if ((rc = shard_dp_sync(P, 1, reach))) return rc;
+			}
 		}
 		uint32_t ovf = 0;
-		{
-			phase pd(ctx, "dp");
-			dp_args D;
-			memset(&D, 0, sizeof D);
-			D.m = m; D.n = n; D.L = L;
-			D.toplist = toplist.as <uint2>(); D.cap = cap; D.cnt = cnt.as <uint32_t>(); D.h0 = h0.as <uint32_t>();
-			D.tb_max = tb_max.as <uint32_t>(); D.tb_lb = tb_lb.as <uint32_t>(); D.tb_size = tb_size.as <uint32_t>();
-			D.mk = mk.as <uint64_t>();
-			D.lev = lev.as <uint32_t>(); D.n_blk = n_blk; D.n_levels = n_levels;
-			D.n_entries = n_entries; D.chunk = chunk; D.n_chunks = n_chunks;
-			D.chunk_level = chunk_level.as <uint32_t>();
-			D.flags = flags.as <uint32_t>();
-			uint32_t h_flags[2] = {0, 0};
-			int64_t const max_rounds = std::max <int64_t>(2, ctx->opt("dp_max_rounds", 16));
-			int64_t const guess_rounds = ctx->opt("dp_guess_rounds", 8);      // after these the table is left to settle by itself
-			uint32_t rounds = 0;
-			CK(cudaMemsetAsync(flags.p, 0, 16, ctx->stream));
-			while (true)
-			{
-				CK(cudaMemsetAsync(flags.p, 0, 8, ctx->stream));
-				CK(launch_dp_chains(D, ctx->stream));
-				ctx->stats["kernel_launches"] += 1;
-				++rounds;
-				if (1 == D.n_chunks) break;             // a single chain is the reference's own order: exact as it stands
-				if (rounds > 1)
-				{
-					CK(cudaMemcpyAsync(h_flags, flags.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-					CK(cudaStreamSynchronize(ctx->stream));
-					if (0 == h_flags[0]) break;         // nothing changed: every entry was computed from the table it is part of
-				}
-				if (rounds >= max_rounds)
-				{
-					// the guesses keep failing: one chain over everything, exact in a single round
-					D.chunk = (n_entries + 63) / 64 * 64;
-					D.n_chunks = 1;
-					ctx->stats["dp_fallbacks"] += 1;
-				}
-				else if (rounds <= guess_rounds)
-				{
-					CK(launch_dp_guess(D, ctx->stream));
-					ctx->stats["kernel_launches"] += 4 + n_levels;
-				}
-			}
-			CK(launch_dp_final(D, ctx->stream));
-			ctx->stats["kernel_launches"] += 1;
-			ctx->stats["dp_rounds"] += rounds;
-			ctx->stats["dp_chunks"] = n_chunks;
-			pd.stop();
-			CK(cudaMemcpyAsync(h_flags, flags.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-			CK(cudaStreamSynchronize(ctx->stream));
-			ovf = h_flags[1];
-		}
+		if ((rc = shard_dp_final(P, &ovf))) return rc;
 		if (0 == ovf) break;
-		if (cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list at column %u with cap = m", ovf - 1);
-		cap = (uint32_t) std::min <uint64_t>(m, (uint64_t) cap * 4);
-		ctx->opts["cap"] = cap;          // later calls on this context start from the bound that worked
+		if (P->cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list at column %u with cap = m", ovf - 1);
+		P->cap = (uint32_t) std::min <uint64_t>(m, (uint64_t) P->cap * 4);
+		ctx->opts["cap"] = P->cap;          // later calls on this context start from the bound that worked
 		ctx->stats["cap_retries"] += 1;
 	}
-	ctx->stats["cap"] = cap;
+	ctx->stats["cap"] = P->cap;
 	ctx->stats["block_columns"] = g.C;
 	ctx->stats["blocks"] = g.B;
 	ctx->stats["warps"] = (g.blocked || g.chunked) ? g.T / 32 : g.n_warps;
@@ -1014,49 +1268,17 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	if (!seg) return fail(ctx, FSQ_ERR_NOMEM, "out of host memory");
 	struct guard { fsq_segmentation *&s; bool ok{false}; ~guard() { if (!ok) { fsq_segmentation_free(s); s = nullptr; } } } gd{seg};
 	seg->ctx = ctx; seg->m = m; seg->n = n; seg->L = L;
-	dbuf tr_lb, tr_rb, tr_max, tr_size;          // the traceback on the device, text order
-	uint32_t T = 0;
+	if ((rc = shard_traceback(P))) return rc;
+	seg->tb_rb = P->tb_rb_h; seg->tb_lb = P->tb_lb_h; seg->tb_max = P->tb_max_h; seg->tb_size = P->tb_size_h;
+	seg->K = P->K;
+	if (ctx->opt("keep_dp", 0))
 	{
-		phase pt(ctx, "traceback");
-		trace_args TA;
-		memset(&TA, 0, sizeof TA);
-		TA.tb_lb = tb_lb.as <uint32_t>(); TA.tb_max = tb_max.as <uint32_t>(); TA.tb_size = tb_size.as <uint32_t>();
-		TA.L = (uint32_t) L; TA.dp_size = (uint32_t) dp_size;
-		TA.levels = 1;
-		while ((1ull << TA.levels) <= dp_size / L + 1) ++TA.levels;
-		dbuf jump, count;
-		CK(jump.alloc(ctx, (size_t) TA.levels * dp_size * 4)); CK(count.alloc(ctx, 4));
-		TA.jump = jump.as <uint32_t>(); TA.count = count.as <uint32_t>();
-		CK(launch_trace_tables(TA, ctx->stream));
-		ctx->stats["kernel_launches"] += TA.levels + 1;
-		CK(cudaMemcpyAsync(&T, count.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+		uint64_t const dp_size = P->dp_size;
+		seg->dp_lb.resize(dp_size); seg->dp_max.resize(dp_size); seg->dp_size.resize(dp_size);
+		CK(cudaMemcpyAsync(seg->dp_lb.data(), P->tb_lb.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(seg->dp_max.data(), P->tb_max.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(seg->dp_size.data(), P->tb_size.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaStreamSynchronize(ctx->stream));
-		CK(tr_lb.alloc(ctx, (size_t) T * 4)); CK(tr_rb.alloc(ctx, (size_t) T * 8)); CK(tr_max.alloc(ctx, (size_t) T * 4)); CK(tr_size.alloc(ctx, (size_t) T * 4));
-		TA.out_lb = tr_lb.as <uint32_t>(); TA.out_rb = tr_rb.as <uint64_t>(); TA.out_max = tr_max.as <uint32_t>(); TA.out_size = tr_size.as <uint32_t>();
-		CK(launch_trace_gather(TA, T, ctx->stream));
-		ctx->stats["kernel_launches"] += 1;
-		hbuf stage;
-		CK(stage.alloc(ctx, (size_t) T * 20));
-		uint64_t *h_rb = stage.as <uint64_t>();
-		uint32_t *h_lb = (uint32_t *) (h_rb + T), *h_max = h_lb + T, *h_size = h_max + T;
-		CK(cudaMemcpyAsync(h_rb, tr_rb.p, (size_t) T * 8, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(h_lb, tr_lb.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(h_max, tr_max.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(h_size, tr_size.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		if (ctx->opt("keep_dp", 0))
-		{
-			seg->dp_lb.resize(dp_size); seg->dp_max.resize(dp_size); seg->dp_size.resize(dp_size);
-			CK(cudaMemcpyAsync(seg->dp_lb.data(), tb_lb.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
-			CK(cudaMemcpyAsync(seg->dp_max.data(), tb_max.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
-			CK(cudaMemcpyAsync(seg->dp_size.data(), tb_size.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		}
-		CK(cudaStreamSynchronize(ctx->stream));
-		seg->tb_rb.assign(h_rb, h_rb + T);
-		seg->tb_lb.assign(h_lb, h_lb + T);
-		seg->tb_max.assign(h_max, h_max + T);
-		seg->tb_size.assign(h_size, h_size + T);
-		seg->K = seg->tb_max.back();
-		pt.stop();
 	}
 	if (!(seg->K < m))
 	{
@@ -1066,72 +1288,15 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 		return fail(ctx, FSQ_ERR_NOT_REDUCIBLE, "the maximum segment size %u is equal to the number of input sequences", seg->K);
 	}
 
-	// ---- pass C: states at the traceback right bounds (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35) ----
-	dbuf st_a, st_d;
-	CK(st_a.alloc(ctx, (size_t) T * m * 4)); CK(st_d.alloc(ctx, (size_t) T * m * 4));
-	if (states.p)
-	{
-		phase pc(ctx, "pass_c");
-		dim3 const grid((m + 255) / 256, T);
-		gather_stored_states_kernel <<<grid, 256, 0, ctx->stream>>>(states.as <uint32_t>(), state_stride, tr_rb.as <uint64_t>(), m, g.C, msa->col0,
-			S.oldvals.as <uint32_t>(), S.R.as <uint32_t>(), st_a.as <uint32_t>(), st_d.as <uint32_t>());
-		CK(cudaGetLastError());
-		pc.stop();
-		ctx->stats["kernel_launches"] += 1;
-		states.release();
-	}
-	else if ((rc = dump_states(ctx, msa, S, seg->tb_rb, st_a.as <uint32_t>(), st_d.as <uint32_t>()))) return rc;
-
-	// ---- greedy reduction (segmentation_lp_context.cc:335-390) ----
-	hbuf chosen_buf;
-	CK(chosen_buf.alloc(ctx, (size_t) T * 4));
-	uint32_t *chosen = chosen_buf.as <uint32_t>();
-	uint32_t cntS = 0;
-	{
-		phase pr(ctx, "reduce");
-		dbuf d_next, d_nsize;
-		hbuf h_next;
-		CK(d_next.alloc(ctx, (size_t) T * 4)); CK(d_nsize.alloc(ctx, (size_t) T * 4)); CK(h_next.alloc(ctx, (size_t) T * 8));
-		reduce_args Rg;
-		Rg.m = m; Rg.T = T; Rg.K = seg->K;
-		Rg.tb_rb = tr_rb.as <uint64_t>(); Rg.tb_size = tr_size.as <uint32_t>(); Rg.st_d = st_d.as <uint32_t>();
-		Rg.next = d_next.as <uint32_t>(); Rg.next_size = d_nsize.as <uint32_t>();
-		CK(launch_reduce(Rg, ctx->stream));
-		ctx->stats["kernel_launches"] += 1;
-		uint32_t *nxt = h_next.as <uint32_t>(), *nsz = nxt + T;
-		CK(cudaMemcpyAsync(nxt, d_next.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(nsz, d_nsize.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaStreamSynchronize(ctx->stream));
-		uint64_t cur_lb = 0;
-		for (uint32_t u = 0; u < T; )
-		{
-			uint32_t const last = nxt[u];
-			seg->lb.push_back(cur_lb);
-			seg->rb.push_back(seg->tb_rb[last]);
-			seg->size.push_back(nsz[u]);
-			chosen[cntS++] = last;
-			cur_lb = seg->tb_rb[last];
-			u = last + 1;
-		}
-		pr.stop();
-	}
-
-	// ---- the reduced samples: device copy for the follow-on kernels, host copy for the joiners ----
-	{
-		phase pg(ctx, "gather");
-		dbuf d_idx, da, dd;
-		CK(d_idx.alloc(ctx, (size_t) cntS * 4));
-		CK(cudaMemcpyAsync(d_idx.p, chosen, (size_t) cntS * 4, cudaMemcpyHostToDevice, ctx->stream));
-		CK(da.alloc(ctx, (size_t) cntS * m * 4)); CK(dd.alloc(ctx, (size_t) cntS * m * 4));
-		dim3 const grid((m + 255) / 256, cntS);
-		gather_states_kernel <<<grid, 256, 0, ctx->stream>>>(st_a.as <uint32_t>(), st_d.as <uint32_t>(), d_idx.as <uint32_t>(), m, da.as <uint32_t>(), dd.as <uint32_t>());
-		CK(cudaGetLastError());
-		ctx->stats["kernel_launches"] += 1;
-		pg.stop();
-		CK(cudaStreamSynchronize(ctx->stream));
-		seg->d_bytes[0] = da.bytes; seg->d_bytes[1] = dd.bytes;
-		seg->d_a = (uint32_t *) da.detach(); seg->d_d = (uint32_t *) dd.detach();
-	}
+	// ---- greedy reduction (segmentation_lp_context.cc:335-390), then the states at the reduced right bounds
+	//      (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35) ----
+	if ((rc = shard_reduce_lists(P))) return rc;
+	if ((rc = shard_reduce(P))) return rc;
+	if ((rc = shard_reduced_states(P))) return rc;
+	seg->lb = P->red_lb; seg->rb = P->red_rb; seg->size = P->red_size;
+	seg->d_bytes[0] = P->red_a.bytes; seg->d_bytes[1] = P->red_d.bytes;
+	seg->d_a = (uint32_t *) P->red_a.detach(); seg->d_d = (uint32_t *) P->red_d.detach();
+	CK(cudaStreamSynchronize(ctx->stream));
 	gd.ok = true;
 	*out = seg;
 	return FSQ_OK;

@@ -78,10 +78,11 @@ __device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, ui
 {
 	uint32_t const lane = lane_id();
 	uint32_t const L = (uint32_t) A.L;
-	uint32_t const cw = A.cnt[k];
+	uint64_t const kl = k - A.col_base;
+	uint32_t const cw = A.cnt[kl];
 	uint32_t const E = cw & 0x7fffffffu;
 	bool const complete = cw >> 31;
-	uint2 const *list = A.toplist + k * (A.cap + 1);
+	uint2 const *list = A.toplist + kl * (A.cap + 1);
 	uint32_t const hi_clip = (uint32_t) (k + 2 - L);
 
 	unsigned long long best = ~0ull;
@@ -131,7 +132,7 @@ __device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, ui
 	reach = max(reach, (uint32_t) t_out - far);
 	if (0 == lane)
 	{
-		uint32_t const h0 = A.h0[k];
+		uint32_t const h0 = A.h0[kl];
 		uint32_t const whole = A.m - h0;          // == m when value 0 is absent
 		uint32_t const best_val = (uint32_t) (best >> 32);
 		uint32_t lb = 0, mx = whole, sz = whole;
@@ -160,8 +161,10 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 	uint32_t const lane = lane_id();
 	uint32_t const L = (uint32_t) A.L;
 	uint32_t const W = L < 64 ? L : 64;
-	uint32_t const t_begin = blockIdx.x * A.chunk;
-	uint32_t const t_end = min(A.n_entries, t_begin + A.chunk);
+	// chains sit on a global grid of `chunk` entries; this rank runs the ones that meet [t_first, t_last)
+	uint32_t const c = A.t_first / A.chunk + blockIdx.x;
+	uint32_t const t_begin = max(A.t_first, c * A.chunk);
+	uint32_t const t_end = min(A.t_last, (c + 1) * A.chunk);
 	uint32_t reach = 0;
 
 	for (uint32_t t0 = t_begin; t0 < t_end; t0 += W)
@@ -209,7 +212,9 @@ cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st)
 	uint32_t const W = (uint32_t) (A.L < 64 ? A.L : 64);
 	uint32_t const passes = (W + 15) / 16;
 	uint32_t const n_warps = (W + passes - 1) / passes;
-	dp_chain_kernel <<<A.n_chunks, n_warps * 32, 0, st>>>(A);
+	if (A.t_first >= A.t_last) return cudaSuccess;
+	uint32_t const own_chunks = (A.t_last - 1) / A.chunk - A.t_first / A.chunk + 1;
+	dp_chain_kernel <<<own_chunks, n_warps * 32, 0, st>>>(A);
 	return cudaGetLastError();
 }
 
@@ -319,6 +324,18 @@ cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st)
 }
 
 
+// Masks and rmq tables as a function of the table as it stands (no levelling): what a rank does after it has received the
+// other ranks' entries.
+cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st)
+{
+	dp_masks_kernel <<<(A.n_entries + 7) / 8, 256, 0, st>>>(A);
+	uint32_t const n_complete = A.n_entries / 64;
+	for (uint32_t p = 0; p < A.n_levels && (1ull << p) <= n_complete; ++p)
+		dp_levels_kernel <<<(n_complete + 255) / 256, 256, 0, st>>>(A, p);
+	return cudaGetLastError();
+}
+
+
 // ---- traceback (reference: segmentation_lp_context.cc:191-224) --------------------------------------------------------------
 constexpr uint32_t TRACE_END = 0xffffffffu;
 
@@ -382,10 +399,36 @@ cudaError_t launch_trace_gather(trace_args const &A, uint32_t count, cudaStream_
 
 
 // ---- greedy reduction (reference: segmentation_lp_context.cc:335-390; pbwt.hh:206-216) ------------------------------
-// #{d_rb > lb} is the number of distinct rows over [lb, rb), which cannot decrease as rb grows, so the run that the
-// reference's sequential loop would merge from a given start is a function of the start alone: one warp per start u
-// (u = 0: left bound 0; u >= 1: left bound rb[u-1]) extends while the count stays <= K.  The host then follows
-// next[] from u = 0.
+// The reference merges traceback segments while #{d_rb > cur_lb} <= K.  That count is the number of distinct rows over
+// [cur_lb, rb), which cannot decrease as rb grows, so the run merged from a given start is a function of the start
+// alone: one warp per start u (u = 0: left bound 0; u >= 1: left bound rb[u - 1]) extends while the count stays <= K;
+// the host then follows next[] from u = 0.
+// The count itself comes from the top list of column rb - 1: with v* the largest divergence value <= lb,
+// #{d > lb} = #{d > v*} (no value lies in (v*, lb]), which is the S of the first list entry whose v is <= lb.  Only
+// entries with S <= K matter -- no such entry means the count exceeds K (K < m here) -- so each traceback position
+// keeps K + 1 entries, which is also what column-sharded ranks exchange instead of whole states.
+__global__ void reduce_lists_kernel(reduce_args const A)
+{
+	uint32_t const pos = A.pos_first + blockIdx.x;
+	uint64_t const kl = A.tb_rb[pos] - 1 - A.col_base;
+	uint32_t const E = A.cnt[kl] & 0x7fffffffu;
+	uint2 const *list = A.toplist + kl * (A.cap + 1);
+	uint2 *out = A.lists + (size_t) pos * A.width;
+	for (uint32_t i = threadIdx.x; i < A.width; i += blockDim.x)
+	{
+		uint2 e = make_uint2(0xffffffffu, 0xffffffffu);
+		if (i < E) { uint2 const x = list[i]; if (x.y <= A.K) e = x; }
+		out[i] = e;
+	}
+}
+
+cudaError_t launch_reduce_lists(reduce_args const &A, cudaStream_t st)
+{
+	if (A.pos_first >= A.pos_last) return cudaSuccess;
+	reduce_lists_kernel <<<A.pos_last - A.pos_first, 64, 0, st>>>(A);
+	return cudaGetLastError();
+}
+
 __global__ void reduce_kernel(reduce_args const A)
 {
 	uint32_t const lane = lane_id();
@@ -395,11 +438,19 @@ __global__ void reduce_kernel(reduce_args const A)
 	uint32_t prev = u, size = A.tb_size[u];
 	for (uint32_t t = u + 1; t < A.T; ++t)
 	{
-		uint32_t const *d = A.st_d + (size_t) t * A.m;
-		uint32_t s = 0;
-		for (uint32_t i = lane; i < A.m; i += 32)
-			s += (cur_lb < d[i]);
-		s = __reduce_add_sync(FSQ_FULL, s);
+		uint2 const *list = A.lists + (size_t) t * A.width;
+		uint32_t s = 0xffffffffu;
+		for (uint32_t i0 = 0; i0 < A.width; i0 += 32)
+		{
+			uint32_t const i = i0 + lane;
+			uint2 const e = i < A.width ? list[i] : make_uint2(0xffffffffu, 0xffffffffu);
+			uint32_t const hit = __ballot_sync(FSQ_FULL, e.x <= cur_lb);       // the padding (v = ~0) never matches
+			if (hit)
+			{
+				s = __shfl_sync(FSQ_FULL, e.y, __ffs(hit) - 1);
+				break;
+			}
+		}
 		if (s <= A.K) { size = s; prev = t; }
 		else break;
 	}

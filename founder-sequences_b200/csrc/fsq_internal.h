@@ -118,9 +118,11 @@ cudaError_t launch_stitch(stitch_args const &A, cudaStream_t st);
 struct dp_args
 {
 	uint32_t m;
-	uint64_t n;                 // columns (global == local for one GPU)
+	uint64_t n;                 // columns of the whole alignment
 	uint64_t L;
-	uint2 const *toplist; uint32_t cap; uint32_t const *cnt; uint32_t const *h0;
+	uint64_t col_base;          // global index of the first column this rank holds top lists for (0 on one GPU)
+	uint32_t t_first, t_last;   // the entries this rank computes: [t_first, t_last) (0 and n_entries on one GPU)
+	uint2 const *toplist; uint32_t cap; uint32_t const *cnt; uint32_t const *h0;     // indexed by column - col_base
 	uint32_t *tb_max, *tb_lb, *tb_size;   // [n - L + 1]; entry t describes right bound t + L
 	uint64_t *mk;               // [n - L + 1] in-block minima masks (see fsq_dp.cu)
 	uint32_t *lev;              // [n_levels][n_blk] rmq tables
@@ -136,6 +138,7 @@ struct dp_args
 cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st);       // every chain once, against the table as it stands
 cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st);        // between rounds: level the table, rebuild masks and rmq tables
 cudaError_t launch_dp_final(dp_args const &A, cudaStream_t st);        // the last column (entry n - L)
+cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st);      // masks and rmq tables from the table as it stands
 
 // Traceback (reference: segmentation_lp_context.cc:191-224) by pointer doubling: jump[k][t] = the entry 2^k hops
 // before t on the path t -> lb[t] - L.  The walk from the last entry is then T independent binary descents.
@@ -151,16 +154,21 @@ struct trace_args
 cudaError_t launch_trace_tables(trace_args const &A, cudaStream_t st);     // jump tables + count
 cudaError_t launch_trace_gather(trace_args const &A, uint32_t count, cudaStream_t st);
 
-// next[j] / size for the greedy reduction; see fsq_dp.cu
+// Greedy reduction (fsq_dp.cu).  The counts #{d_rb > lb} it needs are read off the top lists: for every traceback
+// position a row of `width` = K + 1 entries (v, #{d > v}) with #{d > v} <= K, v descending, padded with (~0, ~0).
 struct reduce_args
 {
-	uint32_t m, T, K;
+	uint32_t T, K, width;
 	uint64_t const *tb_rb;       // [T] right bounds of the traceback
 	uint32_t const *tb_size;     // [T]
-	uint32_t const *st_d;        // [T][m] d at every right bound
-	uint32_t *next;              // [T + 1]: entry j + 1 is for cur_lb = rb[j]; entry 0 for cur_lb = 0
-	uint32_t *next_size;         // [T + 1]
+	uint2 *lists;                // [T][width]
+	uint32_t *next;              // [T]: the last traceback entry merged into the segment that starts at entry u
+	uint32_t *next_size;         // [T]: that segment's size
+	// launch_reduce_lists only: the top lists of this rank's columns and the traceback positions it owns
+	uint2 const *toplist; uint32_t cap; uint32_t const *cnt; uint64_t col_base;
+	uint32_t pos_first, pos_last;
 };
+cudaError_t launch_reduce_lists(reduce_args const &A, cudaStream_t st);    // fill lists[pos_first .. pos_last)
 cudaError_t launch_reduce(reduce_args const &A, cudaStream_t st);
 
 cudaError_t launch_segment_sets(uint32_t const *a, uint32_t const *d, uint32_t m, uint64_t lb, uint32_t *run_off, uint32_t *ids, uint32_t *class_of_row, uint32_t *n_runs, cudaStream_t st);
