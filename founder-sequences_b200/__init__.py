@@ -31,8 +31,10 @@ EXPORTS = [
     "fsq_segmentation_count", "fsq_segmentation_max_segment_size", "fsq_segmentation_bounds",
     "fsq_segmentation_states", "fsq_segmentation_states_view", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
     "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights",
-    "fsq_local_summary", "fsq_summary_free", "fsq_summary_device_pi", "fsq_summary_device_delta",
-    "fsq_apply_summary",
+    "fsq_msa_set_first_column", "fsq_shard_create", "fsq_shard_free", "fsq_shard_local_summary", "fsq_shard_set_start",
+    "fsq_shard_scan", "fsq_shard_dp_table", "fsq_shard_dp_round", "fsq_shard_dp_sync", "fsq_shard_dp_single_chain",
+    "fsq_shard_dp_final", "fsq_shard_grow_cap", "fsq_shard_traceback", "fsq_shard_get_traceback",
+    "fsq_shard_reduce_lists", "fsq_shard_reduce", "fsq_shard_bounds", "fsq_shard_states",
 ]
 
 
@@ -90,6 +92,25 @@ def load_library():
     proto("fsq_distinct_rows", ci, [vp, vp, vp, vp, C.POINTER(u32)])
     proto("fsq_segment_sets", ci, [vp, vp, u32, vp, vp, vp, C.POINTER(u32)])
     proto("fsq_pair_weights", ci, [vp, vp, u32, vp, C.POINTER(u32), C.POINTER(u32)])
+    pu32, pu64 = C.POINTER(u32), C.POINTER(u64)
+    proto("fsq_msa_set_first_column", ci, [vp, u64])
+    proto("fsq_shard_create", ci, [vp, vp, u64, u64, pp])
+    proto("fsq_shard_free", None, [vp])
+    proto("fsq_shard_local_summary", ci, [vp, pp, pp])
+    proto("fsq_shard_set_start", ci, [vp, vp, vp, vp, u32])
+    proto("fsq_shard_scan", ci, [vp])
+    proto("fsq_shard_dp_table", ci, [vp, pp, pp, pp, pu64, pu64, pu64])
+    proto("fsq_shard_dp_round", ci, [vp, pu32, pu32])
+    proto("fsq_shard_dp_sync", ci, [vp, ci, u32])
+    proto("fsq_shard_dp_single_chain", ci, [vp])
+    proto("fsq_shard_dp_final", ci, [vp, pu32])
+    proto("fsq_shard_grow_cap", ci, [vp])
+    proto("fsq_shard_traceback", ci, [vp, pu32, pu32])
+    proto("fsq_shard_get_traceback", ci, [vp, vp, vp, vp, vp])
+    proto("fsq_shard_reduce_lists", ci, [vp, pp, pu32, pu32, pu32])
+    proto("fsq_shard_reduce", ci, [vp, pu32, pu32, pu32])
+    proto("fsq_shard_bounds", ci, [vp, vp, vp, vp])
+    proto("fsq_shard_states", ci, [vp, vp, vp])
     _lib = lib
     return lib
 
@@ -103,6 +124,7 @@ class Context:
 
     def __init__(self, device=0):
         self.lib = load_library()
+        self.device = device
         h = C.c_void_p()
         rc = self.lib.fsq_create(device, C.byref(h))
         if rc:

@@ -101,14 +101,6 @@ struct fsq_segmentation
 	std::vector <uint32_t> dp_lb, dp_max, dp_size;   // keep_dp
 };
 
-struct fsq_summary
-{
-	fsq_ctx *ctx{};
-	uint32_t m{};
-	uint64_t first{}, last{};
-	uint32_t *pi{}, *delta{};
-};
-
 namespace {
 
 int fail(fsq_ctx *ctx, int code, char const *fmt, ...)
@@ -122,6 +114,7 @@ int fail(fsq_ctx *ctx, int code, char const *fmt, ...)
 	return code;
 }
 
+#define CK_(ctx, call) do { cudaError_t e_ = (call); if (cudaSuccess != e_) return fail(ctx, FSQ_ERR_CUDA, "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while (0)
 #define CK(call) do { cudaError_t e_ = (call); if (cudaSuccess != e_) return fail(ctx, FSQ_ERR_CUDA, "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while (0)
 
 // RAII workspace buffers (device / pinned host) out of the context's cache
@@ -1174,6 +1167,13 @@ void fsq_msa_free(fsq_msa *msa)
 	delete msa;
 }
 
+int fsq_msa_set_first_column(fsq_msa *msa, uint64_t first_column)
+{
+	if (!msa) return FSQ_ERR_ARG;
+	msa->col0 = first_column;
+	return FSQ_OK;
+}
+
 uint32_t fsq_msa_rows(const fsq_msa *msa) { return msa ? msa->m : 0; }
 uint64_t fsq_msa_columns(const fsq_msa *msa) { return msa ? msa->n : 0; }
 
@@ -1485,29 +1485,241 @@ int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, int3
 }
 
 // ---- column-sharded operation -------------------------------------------------------------------------------------------
+// One process per GPU; rank r holds the columns [c0_r, c1_r) of one alignment.  The stages below are the long path of
+// fsq_segment() cut where ranks exchange data; the exchange itself (NCCL through torch.distributed, see
+// founder-sequences_b200/sharded.py) is the caller's.
 
-int fsq_local_summary(fsq_ctx *ctx, const fsq_msa *msa, uint64_t first_column, fsq_summary **out)
+int fsq_shard_create(fsq_ctx *ctx, const fsq_msa *msa, uint64_t n_total, uint64_t L, fsq_shard **out)
 {
-	(void) first_column;
-	if (!ctx || !msa || !out) return fail(ctx, FSQ_ERR_ARG, "null argument");
-	return fail(ctx, FSQ_ERR_UNSUPPORTED, "column-sharded operation is not built yet");
+	int rc = check_shape(ctx, msa);
+	if (rc) return rc;
+	if (!out) return fail(ctx, FSQ_ERR_ARG, "null out pointer");
+	if (0 == L) return fail(ctx, FSQ_ERR_ARG, "segment length bound must be positive");
+	if (msa->col0 + msa->n > n_total) return fail(ctx, FSQ_ERR_ARG, "the shard's columns end beyond the alignment");
+	if (n_total >= (1ull << 31)) return fail(ctx, FSQ_ERR_UNSUPPORTED, "n = %llu columns: positions are kept in 32 bits (n < 2^31)", (unsigned long long) n_total);
+	if (n_total < 2 * L) return fail(ctx, FSQ_ERR_SHORT, "n = %llu < 2L = %llu: short path", (unsigned long long) n_total, (unsigned long long) (2 * L));
+	CK(cudaSetDevice(ctx->device));
+	fsq_shard *P = new (std::nothrow) fsq_shard;
+	if (!P) return fail(ctx, FSQ_ERR_NOMEM, "out of host memory");
+	if ((rc = shard_init(P, ctx, msa, n_total, L))) { delete P; return rc; }
+	*out = P;
+	return FSQ_OK;
 }
 
-void fsq_summary_free(fsq_summary *s)
+void fsq_shard_free(fsq_shard *P)
 {
-	if (!s) return;
-	cudaFree(s->pi);
-	cudaFree(s->delta);
-	delete s;
+	if (!P) return;
+	cudaSetDevice(P->ctx->device);
+	cudaStreamSynchronize(P->ctx->stream);
+	delete P;
 }
 
-uint32_t *fsq_summary_device_pi(fsq_summary *s) { return s ? s->pi : nullptr; }
-uint32_t *fsq_summary_device_delta(fsq_summary *s) { return s ? s->delta : nullptr; }
-
-int fsq_apply_summary(fsq_ctx *ctx, const fsq_summary *s, uint32_t *d_a, uint32_t *d_d)
+int fsq_shard_local_summary(fsq_shard *P, const uint32_t **d_pi, const uint32_t **d_delta)
 {
-	(void) s; (void) d_a; (void) d_d;
-	return fail(ctx, FSQ_ERR_UNSUPPORTED, "column-sharded operation is not built yet");
+	if (!P || !d_pi || !d_delta) return FSQ_ERR_ARG;
+	fsq_ctx *ctx = P->ctx;
+	CK(cudaSetDevice(ctx->device));
+	flush_phases(ctx);
+	if (!ctx->call_start) CK(cudaEventCreate(&ctx->call_start));
+	CK(cudaEventRecord(ctx->call_start, ctx->stream));
+	int const rc = local_scan(ctx, P->msa, P->S);
+	if (rc) return rc;
+	CK(cudaStreamSynchronize(ctx->stream));
+	// the state at the end of the last block, relative to the identity state at c0: this rank's summary
+	*d_pi = P->S.st_a.as <uint32_t>() + (size_t) P->S.g.B * P->m;
+	*d_delta = P->S.st_d.as <uint32_t>() + (size_t) P->S.g.B * P->m;
+	return FSQ_OK;
+}
+
+int fsq_shard_set_start(fsq_shard *P, const uint32_t *d_pis, const uint32_t *d_deltas, const uint64_t *first_columns, uint32_t count)
+{
+	if (!P) return FSQ_ERR_ARG;
+	fsq_ctx *ctx = P->ctx;
+	CK(cudaSetDevice(ctx->device));
+	if (!P->S.sum_a.p) return fail(ctx, FSQ_ERR_ARG, "fsq_shard_local_summary has not run");
+	uint32_t const m = P->m;
+	if (0 == count)
+	{
+		if (0 != P->c0) return fail(ctx, FSQ_ERR_ARG, "a shard that does not start at column 0 needs the summaries of the ranks before it");
+	}
+	else
+	{
+		if (!d_pis || !d_deltas || !first_columns) return fail(ctx, FSQ_ERR_ARG, "null argument");
+		if (0 != first_columns[0]) return fail(ctx, FSQ_ERR_ARG, "the first summary must start at column 0");
+		// true state at c0 = summary_0 o summary_1 o ... (summary_0 starts from the true initial state); one CTA, in order
+		dbuf tmp_a, tmp_d;
+		CK(tmp_a.alloc(ctx, (size_t) 2 * m * 4)); CK(tmp_d.alloc(ctx, (size_t) 2 * m * 4));
+		uint32_t const *cur_a = d_pis, *cur_d = d_deltas;
+		if (count > 1)
+		{
+			stitch_plan plan;
+			for (uint32_t i = 1; i < count; ++i)
+			{
+				stitch_item it;
+				memset(&it, 0, sizeof it);
+				it.in_a = cur_a; it.in_d = cur_d;
+				it.pi = d_pis + (size_t) i * m; it.delta = d_deltas + (size_t) i * m;
+				it.out_a = tmp_a.as <uint32_t>() + (size_t) (i & 1) * m; it.out_d = tmp_d.as <uint32_t>() + (size_t) (i & 1) * m;
+				it.s_mark = (uint32_t) first_columns[i];
+				plan.items.push_back(it);
+				plan.end_level();              // one launch per step: each reads what the previous one wrote
+				cur_a = it.out_a; cur_d = it.out_d;
+			}
+			phase ps(ctx, "stitch");
+			CK(cudaStreamSynchronize(ctx->stream));
+			int const rc = run_stitch_plan(ctx, P->S, plan, m, {});
+			if (rc) return rc;
+			ps.stop();
+			CK(cudaStreamSynchronize(ctx->stream));
+		}
+		int const rc = apply_start_state(ctx, P->msa, P->S, cur_a, cur_d);
+		if (rc) return rc;
+		CK(cudaStreamSynchronize(ctx->stream));
+	}
+	int const rc = compress_starts(ctx, P->msa, P->S);
+	if (rc) return rc;
+	P->started = true;
+	return FSQ_OK;
+}
+
+int fsq_shard_scan(fsq_shard *P)
+{
+	if (!P) return FSQ_ERR_ARG;
+	fsq_ctx *ctx = P->ctx;
+	CK(cudaSetDevice(ctx->device));
+	if (!P->started) return fail(ctx, FSQ_ERR_ARG, "fsq_shard_set_start has not run");
+	int const rc = shard_scan(P);
+	if (rc) return rc;
+	CK(cudaStreamSynchronize(ctx->stream));
+	return FSQ_OK;
+}
+
+int fsq_shard_dp_table(fsq_shard *P, uint32_t **d_max, uint32_t **d_lb, uint32_t **d_size, uint64_t *entries, uint64_t *own_first, uint64_t *own_last)
+{
+	if (!P || !d_max || !d_lb || !d_size || !entries || !own_first || !own_last) return FSQ_ERR_ARG;
+	if (!P->tb_max.p) return fail(P->ctx, FSQ_ERR_ARG, "fsq_shard_scan has not run");
+	*d_max = P->tb_max.as <uint32_t>(); *d_lb = P->tb_lb.as <uint32_t>(); *d_size = P->tb_size.as <uint32_t>();
+	*entries = P->dp_size;
+	*own_first = P->t_first;
+	*own_last = (P->c1 == P->n) ? P->dp_size : P->t_last;       // the rank with the last column also owns the final entry
+	return FSQ_OK;
+}
+
+int fsq_shard_dp_round(fsq_shard *P, uint32_t *changed, uint32_t *reach)
+{
+	if (!P || !changed || !reach) return FSQ_ERR_ARG;
+	CK_(P->ctx, cudaSetDevice(P->ctx->device));
+	return shard_dp_round(P, changed, reach);
+}
+
+int fsq_shard_dp_sync(fsq_shard *P, int guess, uint32_t reach)
+{
+	if (!P) return FSQ_ERR_ARG;
+	CK_(P->ctx, cudaSetDevice(P->ctx->device));
+	return shard_dp_sync(P, guess, reach);
+}
+
+int fsq_shard_dp_single_chain(fsq_shard *P)
+{
+	if (!P) return FSQ_ERR_ARG;
+	P->single_chain = true;
+	P->ctx->stats["dp_fallbacks"] += 1;
+	return FSQ_OK;
+}
+
+int fsq_shard_dp_final(fsq_shard *P, uint32_t *overflow)
+{
+	if (!P || !overflow) return FSQ_ERR_ARG;
+	CK_(P->ctx, cudaSetDevice(P->ctx->device));
+	return shard_dp_final(P, overflow);
+}
+
+int fsq_shard_grow_cap(fsq_shard *P)
+{
+	if (!P) return FSQ_ERR_ARG;
+	fsq_ctx *ctx = P->ctx;
+	if (P->cap >= P->m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list with cap = m");
+	P->cap = (uint32_t) std::min <uint64_t>(P->m, (uint64_t) P->cap * 4);
+	ctx->opts["cap"] = P->cap;
+	ctx->stats["cap_retries"] += 1;
+	return FSQ_OK;
+}
+
+int fsq_shard_traceback(fsq_shard *P, uint32_t *count, uint32_t *K)
+{
+	if (!P || !count || !K) return FSQ_ERR_ARG;
+	CK_(P->ctx, cudaSetDevice(P->ctx->device));
+	int const rc = shard_traceback(P);
+	if (rc) return rc;
+	*count = P->T;
+	*K = P->K;
+	return FSQ_OK;
+}
+
+int fsq_shard_get_traceback(const fsq_shard *P, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
+{
+	if (!P || !lb || !rb || !max_size || !size) return FSQ_ERR_ARG;
+	std::copy(P->tb_lb_h.begin(), P->tb_lb_h.end(), lb);
+	std::copy(P->tb_rb_h.begin(), P->tb_rb_h.end(), rb);
+	std::copy(P->tb_max_h.begin(), P->tb_max_h.end(), max_size);
+	std::copy(P->tb_size_h.begin(), P->tb_size_h.end(), size);
+	return FSQ_OK;
+}
+
+int fsq_shard_reduce_lists(fsq_shard *P, uint32_t **d_lists, uint32_t *width, uint32_t *own_first, uint32_t *own_last)
+{
+	if (!P || !d_lists || !width || !own_first || !own_last) return FSQ_ERR_ARG;
+	fsq_ctx *ctx = P->ctx;
+	CK(cudaSetDevice(ctx->device));
+	if (!(P->K < P->m)) return fail(ctx, FSQ_ERR_NOT_REDUCIBLE, "the maximum segment size %u is equal to the number of input sequences", P->K);
+	int const rc = shard_reduce_lists(P);
+	if (rc) return rc;
+	CK(cudaStreamSynchronize(ctx->stream));
+	*d_lists = P->lists.as <uint32_t>();
+	*width = P->K + 1;
+	*own_first = P->pos_first;
+	*own_last = P->pos_last;
+	return FSQ_OK;
+}
+
+int fsq_shard_reduce(fsq_shard *P, uint32_t *count, uint32_t *own_first, uint32_t *own_last)
+{
+	if (!P || !count || !own_first || !own_last) return FSQ_ERR_ARG;
+	fsq_ctx *ctx = P->ctx;
+	CK(cudaSetDevice(ctx->device));
+	int rc = shard_reduce(P);
+	if (rc) return rc;
+	if ((rc = shard_reduced_states(P))) return rc;
+	CK(cudaStreamSynchronize(ctx->stream));
+	*count = (uint32_t) P->red_lb.size();
+	*own_first = P->seg_first;
+	*own_last = P->seg_last;
+	ctx->stats["cap"] = P->cap;
+	ctx->stats["block_columns"] = P->S.g.C;
+	ctx->stats["blocks"] = P->S.g.B;
+	return FSQ_OK;
+}
+
+int fsq_shard_bounds(const fsq_shard *P, uint64_t *lb, uint64_t *rb, uint32_t *size)
+{
+	if (!P || !lb || !rb || !size) return FSQ_ERR_ARG;
+	std::copy(P->red_lb.begin(), P->red_lb.end(), lb);
+	std::copy(P->red_rb.begin(), P->red_rb.end(), rb);
+	std::copy(P->red_size.begin(), P->red_size.end(), size);
+	return FSQ_OK;
+}
+
+int fsq_shard_states(fsq_shard *P, uint32_t *a, uint32_t *d)
+{
+	if (!P || !a || !d) return FSQ_ERR_ARG;
+	fsq_ctx *ctx = P->ctx;
+	CK(cudaSetDevice(ctx->device));
+	size_t const bytes = (size_t) (P->seg_last - P->seg_first) * P->m * 4;
+	if (0 == bytes) return FSQ_OK;
+	CK(cudaMemcpyAsync(a, P->red_a.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(d, P->red_d.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	return FSQ_OK;
 }
 
 } // extern "C"

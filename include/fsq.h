@@ -36,7 +36,7 @@ typedef enum fsq_status {
 typedef struct fsq_ctx fsq_ctx;                     /* one per device / host thread */
 typedef struct fsq_msa fsq_msa;                     /* column-major, 4-bit packed alignment resident in HBM */
 typedef struct fsq_segmentation fsq_segmentation;   /* result of the long path, device + host copies */
-typedef struct fsq_summary fsq_summary;             /* a rank's column-range scan summary (multi-GPU) */
+typedef struct fsq_shard fsq_shard;                 /* one rank's part of a column-sharded run of the long path */
 
 /* ---- context ------------------------------------------------------------------------------------------ */
 
@@ -130,18 +130,54 @@ int fsq_segment_sets(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment
  * adjacent reduced segments (segment, segment + 1): W[i * runs_rhs + j] = |S_i ∩ T_j| over the runs in PBWT order. */
 int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment, int32_t *W, uint32_t *runs_lhs, uint32_t *runs_rhs);
 
-/* ---- column-sharded operation (one process per GPU; the exchange itself is done by the caller over NCCL) ---- */
-
-/* Rank-local scan of this rank's columns from the identity state: the (π, δ) summary of the whole range
- * (SURVEY.md A.10).  Summaries compose associatively. */
-int fsq_local_summary(fsq_ctx *ctx, const fsq_msa *msa, uint64_t first_column, fsq_summary **out);
-void fsq_summary_free(fsq_summary *s);
-/* Device pointers for the exchange (m uint32 each) and the column range the summary covers. */
-uint32_t *fsq_summary_device_pi(fsq_summary *s);
-uint32_t *fsq_summary_device_delta(fsq_summary *s);
-/* Given the true state (a, d on the device, m uint32 each) at the first column of the summary, produce the true
- * state at its last column + 1 in place. */
-int fsq_apply_summary(fsq_ctx *ctx, const fsq_summary *s, uint32_t *d_a, uint32_t *d_d);
+/* ---- column-sharded operation (one process per GPU; the exchange itself is done by the caller over NCCL) ----------
+ *
+ * The reference runs the path in one process (no counterpart); these are the stages of fsq_segment() cut
+ * where column shards exchange data.  Rank r holds the columns [c0_r, c1_r) of ONE alignment of n_total columns as an
+ * fsq_msa whose first column is c0_r (fsq_msa_synth with col0, or fsq_msa_set_first_column).  Order of calls, with the
+ * caller's collectives in brackets (founder-sequences_b200/sharded.py is the reference driver):
+ *
+ *   fsq_shard_local_summary      local scan from the identity state + prefix composition -> this rank's (pi, delta)
+ *   [all-gather of the summaries]
+ *   fsq_shard_set_start          true state at c0_r = composition of the summaries of the ranks before; block starts
+ *   fsq_shard_scan               exact scan: top lists (and kept states) for the own columns; resets the DP table
+ *   repeat: fsq_shard_dp_round   own DP entries against the table as it stands
+ *           [broadcast of every rank's slice of tb_max; max-reduce of changed / reach]
+ *           fsq_shard_dp_sync    level guess (optional) + masks and rmq tables of the whole table
+ *   until no rank changed anything
+ *   fsq_shard_dp_final           last entry (rank with the last column); [broadcast of the tb_max/tb_lb/tb_size slices;
+ *                                max-reduce of the overflow flag -> fsq_shard_grow_cap and back to fsq_shard_scan]
+ *   fsq_shard_traceback          every rank, from the complete table
+ *   fsq_shard_reduce_lists       rows of the reduction's count lists for the own traceback positions
+ *   [broadcast of every rank's rows]
+ *   fsq_shard_reduce             greedy reduction (every rank) + the states of the own reduced segments
+ * Results are independent of the number of ranks and of the block size (tests/test_sharded*.py). */
+int fsq_msa_set_first_column(fsq_msa *msa, uint64_t first_column);
+int fsq_shard_create(fsq_ctx *ctx, const fsq_msa *msa, uint64_t n_total, uint64_t segment_length_bound, fsq_shard **out);
+void fsq_shard_free(fsq_shard *s);
+/* Device pointers (m uint32 each, owned by the shard): the state after this rank's last column had the scan started
+ * from the identity state at its first column. */
+int fsq_shard_local_summary(fsq_shard *s, const uint32_t **d_pi, const uint32_t **d_delta);
+/* d_pis / d_deltas: device arrays [count][m] with the summaries of the ranks before this one, in rank order;
+ * first_columns[count]: their first columns (host).  count == 0 for the rank that starts at column 0. */
+int fsq_shard_set_start(fsq_shard *s, const uint32_t *d_pis, const uint32_t *d_deltas, const uint64_t *first_columns, uint32_t count);
+int fsq_shard_scan(fsq_shard *s);
+/* The DP table (device, `entries` uint32 each; entry t describes right bound t + L) and the range of entries this rank
+ * computes, i.e. the slice it must send to the others. */
+int fsq_shard_dp_table(fsq_shard *s, uint32_t **d_max, uint32_t **d_lb, uint32_t **d_size, uint64_t *entries, uint64_t *own_first, uint64_t *own_last);
+int fsq_shard_dp_round(fsq_shard *s, uint32_t *changed, uint32_t *reach);
+int fsq_shard_dp_sync(fsq_shard *s, int guess, uint32_t reach);
+int fsq_shard_dp_single_chain(fsq_shard *s);       /* fallback: the next rounds run the own entries as one chain */
+int fsq_shard_dp_final(fsq_shard *s, uint32_t *overflow);
+int fsq_shard_grow_cap(fsq_shard *s);
+int fsq_shard_traceback(fsq_shard *s, uint32_t *count, uint32_t *max_segment_size);
+int fsq_shard_get_traceback(const fsq_shard *s, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size);
+/* Device array [count][width] of (v, #{d > v}) pairs (2 uint32 each) and the rows [own_first, own_last) this rank filled. */
+int fsq_shard_reduce_lists(fsq_shard *s, uint32_t **d_lists, uint32_t *width, uint32_t *own_first, uint32_t *own_last);
+/* Reduced segments: their number and the range [own_first, own_last) whose states this rank holds. */
+int fsq_shard_reduce(fsq_shard *s, uint32_t *count, uint32_t *own_first, uint32_t *own_last);
+int fsq_shard_bounds(const fsq_shard *s, uint64_t *lb, uint64_t *rb, uint32_t *size);
+int fsq_shard_states(fsq_shard *s, uint32_t *a, uint32_t *d);      /* (own_last - own_first) x m each, to host memory */
 
 #ifdef __cplusplus
 }
