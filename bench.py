@@ -9,9 +9,9 @@ re-scan, greedy reduction) over one synthetic founder-mosaic alignment.  `value`
 alignment already resident in HBM; `e2e` times the same through the C ABI from host rows (pinned), with the
 host->device copy, the transpose/pack and the device->host copy of the result inside the timed region.
 
-N > 1 (torchrun, one rank per GPU): every rank segments its own alignment of the same shape (independent
-alignments, e.g. chromosomes: no data-path collective) -> "scaling": "weak".  Column-sharding ONE alignment over
-ranks is not built yet (multi-GPU).
+N > 1 (torchrun, one rank per GPU): ONE alignment of N x n columns, column-sharded -- rank r holds columns
+[r n, (r + 1) n) -- through founder-sequences_b200/sharded.py (boundary summaries all-gathered, DP table slices
+broadcast per round, reduction lists exchanged; NCCL).  Per-GPU work is fixed as N grows -> "scaling": "weak".
 
 --impl reference times the reference's own CPU code for the path (oracle/_ref when it was built, else the C
 restatement in oracle/), rank 0 only, on a bounded column sample of the same workload.
@@ -33,7 +33,7 @@ BYTES_PER_CELL = 16.5     # read a,d (8) + write a,d (8) + one
 WORKLOADS = {
     # name: (m, n, L, founders, gaps, seed, description)
     "c1": (64, 100_000, 10, 8, False, 1, "synthetic 64 x 100k, sigma=4, L=10"),
-    "c2": (1000, 1_000_000, 20, 16, True, 2, "synthetic 1,000 x 1M, sigma=5 (ACGT+gap), L=20"),
+    "c2": (1000, 1_000_000, 20, 16, True, 2, "synthetic 1,000 x 1M per GPU, sigma=5 (ACGT+gap), L=20"),
     "c2s": (1000, 200_000, 20, 16, True, 2, "synthetic 1,000 x 200k (1/5 of config 2), sigma=5, L=20"),
     "c3s": (5000, 1_000_000, 50, 32, True, 3, "synthetic 5,000 x 1M (1/10 of config 3), sigma=5, L=50"),
     "c4s": (2500, 1_000_000, 50, 24, True, 4, "synthetic 2,500 x 1M (1/5 of config 4), L=50"),
@@ -60,12 +60,20 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def window(self, t0, t1):
+        """Keep the samples taken inside the timed region (the sampler is started before the warm-up so that its own
+        start-up does not fall into the region); if the region was shorter than the sampling period, the nearest ones."""
+        inside = [ln for t, ln in self.lines if t0 <= t <= t1]
+        if not inside and self.lines:
+            mid = 0.5 * (t0 + t1)
+            inside = [min(self.lines, key=lambda x: abs(x[0] - mid))[1]]
+        self.lines = inside
 
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -74,6 +82,8 @@ class ClockSampler:
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for ln in self.lines:
+            if isinstance(ln, tuple):
+                ln = ln[1]
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 6:
                 continue
@@ -201,6 +211,7 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     dev = local_rank
+    torch.cuda.set_device(dev)
     ctx = fsq.Context(dev)
     if args.block_columns:
         ctx.set_option("block_columns", args.block_columns)
@@ -208,8 +219,15 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
         ctx.set_option("warps", args.warps)
     if args.cap:
         ctx.set_option("cap", args.cap)
-    my_seed = seed + 1000 * rank     # every rank has its own alignment
-    msa = ctx.msa_synth(m, n, my_seed, founders, gaps)
+    sharded = None
+    comm = None
+    n_total = n * world
+    if world > 1:
+        from __graft_entry__ import load_sharded
+        sharded = load_sharded()
+        comm = sharded.TorchComm()
+    # every rank holds its columns of the same alignment: the generator is a pure function of (seed, row, column)
+    msa = ctx.msa_synth(m, n, seed, founders, gaps, col0=rank * n)
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -218,41 +236,53 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             torch.cuda.synchronize(dev)
 
     def step():
-        seg = ctx.segment(msa, L)
-        info = (seg.max_segment_size, seg.count)
-        seg.free()
-        return info
+        if sharded is None:
+            seg = ctx.segment(msa, L)
+            info = (seg.max_segment_size, seg.count)
+            seg.free()
+            return info
+        eng = sharded.GpuShard(ctx, msa, rank * n, n_total, L)
+        try:
+            res = sharded.segment_sharded(eng, comm, want_states=False)
+        finally:
+            eng.close()
+        return (res.K, len(res.lb))
 
+    sampler = ClockSampler(dev)
+    sampler.start()
     for _ in range(args.warmup):
         info = step()
     ctx.reset_stats()
-    sampler = ClockSampler(dev)
-    sampler.start()
     barrier()
+    ctx.set_option("timer", 1)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         info = step()
+    ctx.set_option("timer", 0)
     barrier()
     t1 = time.perf_counter()
+    sampler.window(t0, t1)
     clocks = sampler.stop()
-    secs = t1 - t0
+    wall = t1 - t0
+    secs = ctx.stat("ms_timer") * 1e-3        # CUDA events on the stream the kernels are launched on
     if dist is not None:
-        t = torch.tensor([secs], device="cuda:%d" % dev, dtype=torch.float64)
+        t = torch.tensor([secs, wall], device="cuda:%d" % dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        secs = float(t.item())
+        secs, wall = float(t[0].item()), float(t[1].item())
     phases = {}
-    for k in ("pass_a", "stitch", "prep", "pass_b", "dp", "traceback", "pass_c", "reduce", "gather"):
+    for k in ("pass_a", "stitch", "prep", "pass_b", "dp", "traceback", "reduce", "pass_c"):
         phases[k] = ctx.stat("ms_" + k) / args.steps
     launches = ctx.stat("kernel_launches")
     cap = ctx.stat("cap")
     geom = {"block_columns": int(ctx.stat("block_columns")), "blocks": int(ctx.stat("blocks")), "warps_per_block": int(ctx.stat("warps")), "cap": int(cap), "cap_retries": int(ctx.stat("cap_retries")),
-            "chunk": int(ctx.stat("chunk")), "dp_chains": int(ctx.stat("dp_chunks")), "dp_rounds_per_step": ctx.stat("dp_rounds") / args.steps}
+            "chunk": int(ctx.stat("chunk")), "dp_chains": int(ctx.stat("dp_chunks")), "dp_rounds_per_step": ctx.stat("dp_rounds") / args.steps,
+            "states_kept_by_pass_b": bool(ctx.stat("store_states"))}
 
     # ---- end to end: host rows -> C ABI -> host results ----
     e2e = None
     if not args.no_e2e:
         rows_dev = torch.empty((m, n), dtype=torch.uint8, device="cuda:%d" % dev)
-        ctx.synth_rows_device(rows_dev.data_ptr(), n, m, n, my_seed, founders, gaps)
+        ctx.synth_rows_device(rows_dev.data_ptr(), n, m, n, seed, founders, gaps, col0=rank * n)
         rows_host = torch.empty((m, n), dtype=torch.uint8, pin_memory=True)
         rows_host.copy_(rows_dev)
         del rows_dev
@@ -263,10 +293,18 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             comp[ch] = i + 1
 
         def e2e_step():
-            with ctx.msa_from_rows(rows_np, comp) as mm, ctx.segment(mm, L) as seg:
-                lb, rb, sz = seg.reduced_traceback()
-                a, d = seg.reduced_pbwt_samples_view()
-                return seg.max_segment_size, len(lb), lb.nbytes + rb.nbytes + sz.nbytes + a.nbytes + d.nbytes
+            if sharded is None:
+                with ctx.msa_from_rows(rows_np, comp) as mm, ctx.segment(mm, L) as seg:
+                    lb, rb, sz = seg.reduced_traceback()
+                    a, d = seg.reduced_pbwt_samples_view()
+                    return seg.max_segment_size, len(lb), lb.nbytes + rb.nbytes + sz.nbytes + a.nbytes + d.nbytes
+            with ctx.msa_from_rows(rows_np, comp) as mm:
+                eng = sharded.GpuShard(ctx, mm, rank * n, n_total, L)
+                try:
+                    res = sharded.segment_sharded(eng, comm, want_states=True)
+                finally:
+                    eng.close()
+                return res.K, len(res.lb), res.lb.nbytes + res.rb.nbytes + res.size.nbytes + res.a.nbytes + res.d.nbytes
 
         e_steps = max(1, min(args.steps, 3))
         e2e_step()
@@ -281,9 +319,10 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             esecs = float(t.item())
         assert einfo[:2] == info, (einfo, info)
-        dp_bytes = 3 * 4 * (n - L + 1)      # the DP table columns read back for the traceback
+        tb_bytes = 20 * einfo[1]            # the traceback read back for the reduction (an upper bound uses the segment count)
         e2e = {"value": world * cells * e_steps / esecs, "unit": "cells/s", "h2d_bytes_per_step": m * n + 256,
-               "d2h_bytes_per_step": int(einfo[2]) + dp_bytes, "steps": e_steps}
+               "d2h_bytes_per_step": int(einfo[2]) + tb_bytes, "steps": e_steps,
+               "timing": "host clock around the C-ABI calls (they block), barrier + device synchronise on both sides, max over ranks"}
 
     if rank != 0:
         msa.free()
@@ -302,7 +341,8 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
         "warmup": args.warmup, "ms_per_step": 1e3 * secs / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": desc, "K": info[0], "segments": info[1], "inputs": "packed alignment %.0f MB per rank (> 126 MB L2), regenerated state per step" % (msa.m / 2 * n / 1e6),
-                   "parallelism": "1 GPU" if world == 1 else "independent alignments, one per rank (no collective)", **geom},
+                   "parallelism": "1 GPU" if world == 1 else "one alignment of %d columns, column-sharded over %d ranks (NCCL: summary all-gather, DP table broadcasts, reduction lists)" % (n_total, world),
+                   "timing": "CUDA events on the library's stream around the timed steps, max over ranks; wall %.3f ms/step" % (1e3 * wall / args.steps), **geom},
         "phases_ms": phases, "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline,
     }
     if e2e:

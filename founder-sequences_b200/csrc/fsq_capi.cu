@@ -31,6 +31,7 @@ struct fsq_ctx
 	std::map <std::string, int64_t> opts;
 	std::map <std::string, double> stats;
 	std::vector <std::pair <std::string, std::pair <cudaEvent_t, cudaEvent_t>>> pending;   // phase timers
+	cudaEvent_t timer_ev[2]{nullptr, nullptr};   // option "timer": 1 records the start, 0 the stop, on the context's stream ("ms_timer")
 	cudaEvent_t call_start{nullptr};       // recorded at the entry of fsq_segment: phases report their offset from it ("at_<phase>")
 
 	int64_t opt(char const *k, int64_t dflt) const { auto it = opts.find(k); return opts.end() == it ? dflt : it->second; }
@@ -1019,6 +1020,22 @@ const char *fsq_last_error(const fsq_ctx *ctx) { return ctx ? ctx->error.c_str()
 int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
 {
 	if (!ctx || !key) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	if (0 == strcmp("timer", key))
+	{
+		// device-side timing of a region of calls, on the stream the kernels are launched on
+		CK(cudaSetDevice(ctx->device));
+		int const which = value ? 0 : 1;
+		if (!ctx->timer_ev[which]) CK(cudaEventCreate(&ctx->timer_ev[which]));
+		CK(cudaEventRecord(ctx->timer_ev[which], ctx->stream));
+		if (1 == which && ctx->timer_ev[0])
+		{
+			float ms = 0;
+			CK(cudaEventSynchronize(ctx->timer_ev[1]));
+			CK(cudaEventElapsedTime(&ms, ctx->timer_ev[0], ctx->timer_ev[1]));
+			ctx->stats["ms_timer"] = ms;
+		}
+		return FSQ_OK;
+	}
 	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", nullptr};
 	for (char const **k = known; *k; ++k)
 		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }

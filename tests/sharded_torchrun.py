@@ -1,0 +1,58 @@
+"""Parity of the column-sharded path under torchrun + NCCL (one rank per GPU) against the oracle's unsharded answer.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tests/sharded_torchrun.py
+
+tests/test_sharded_gpu.py launches this when the box has more than one GPU; with one GPU the same driver is covered with
+ranks as threads."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from __graft_entry__ import load_package, load_sharded, load_synth
+    import oraclelib
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    fsq, sh, synth = load_package(), load_sharded(), load_synth()
+    comm = sh.TorchComm()
+    for m, n, L, C in [(64, 4000, 10, 96), (1000, 6000, 20, 0), (300, 2500, 7, 50)]:
+        rows = synth.synth_rows(m, n, seed=m + L, founders=8, gaps=True)
+        c0, c1 = sh.split_columns(n, world)[rank]
+        ctx = fsq.Context(local)
+        if C:
+            ctx.set_option("block_columns", C)
+        comp = np.zeros(256, np.uint8)
+        for i, ch in enumerate(sorted(set(rows.tobytes()) | {0})):
+            comp[ch] = i
+        msa = ctx.msa_from_rows(np.ascontiguousarray(rows[:, c0:c1]), comp)
+        eng = sh.GpuShard(ctx, msa, c0, n, L)
+        res = sh.segment_sharded(eng, comm)
+        eng.close(); msa.free(); ctx.close()
+        with oraclelib.oracle().open(rows) as o:
+            assert o.segment(L) == 0
+            olb, orb, _, osz = o.reduced()
+            oa, od = o.reduced_states()
+            assert res.K == o.K()
+            for x, y in zip(res.traceback, o.traceback()):
+                assert np.array_equal(x, y)
+        assert np.array_equal(res.lb, olb) and np.array_equal(res.rb, orb) and np.array_equal(res.size, osz)
+        f, l = res.own
+        assert np.array_equal(res.a, oa[f:l]) and np.array_equal(res.d, od[f:l])
+        owns = comm.gather_objects(res.own)
+        assert owns[0][0] == 0 and owns[-1][1] == len(olb) and all(owns[i][1] == owns[i + 1][0] for i in range(world - 1))
+        if rank == 0:
+            print("sharded ok: %d x %d, L = %d over %d ranks: K = %d, %d segments, %d DP rounds" % (m, n, L, world, res.K, len(olb), res.dp_rounds))
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

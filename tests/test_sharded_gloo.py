@@ -1,0 +1,62 @@
+"""The column-sharded protocol on CPU: world_size 2 and 3 over gloo, the per-rank engine replaced by the plain-Python
+stand-in of tests/cpu_shard.py (there is no CPU path in the product).  Covers the host logic of
+founder-sequences_b200/sharded.py: summary all-gather and prefix composition, the DP table exchange and its fixed-point
+rule, the exchange of the reduction lists, and the assembly of the result."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch.multiprocessing as mp
+
+from sharded_worker import run_rank
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+@pytest.mark.parametrize("world,case", [
+    (2, (10, 260, 6, 1, None)),
+    (2, (14, 300, 9, 2, [(0, 13), (13, 300)])),          # a boundary inside the first 2L columns
+    (3, (12, 330, 5, 3, None)),
+    (3, (9, 200, 4, 4, [(0, 64), (64, 199), (199, 200)])),   # a one-column last shard
+])
+def test_sharded_protocol_over_gloo(tmp_path, world, case):
+    port = free_port()
+    mp.spawn(run_rank, args=(world, port, case, str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        assert os.path.exists(tmp_path / ("ok%d.npy" % r))
+
+
+def test_stitch_composition_is_associative():
+    """compose() of cpu_shard.py against straight scans, for random cut points."""
+    from cpu_shard import compose, pbwt_step
+    rng = np.random.default_rng(7)
+    for _ in range(20):
+        m, n = int(rng.integers(2, 9)), int(rng.integers(3, 30))
+        sym = rng.integers(0, 3, size=(m, n))
+        cuts = sorted(set([0, n] + [int(x) for x in rng.integers(0, n, size=3)]))
+        a, d = np.arange(m), np.zeros(m, np.int64)
+        truth = {0: (a, d)}
+        for k in range(n):
+            a, d = pbwt_step(a, d, sym[:, k], k + 1)
+            truth[k + 1] = (a, d)
+        summaries = []
+        for s, e in zip(cuts[:-1], cuts[1:]):
+            a, d = np.arange(m), np.full(m, s)
+            for k in range(s, e):
+                a, d = pbwt_step(a, d, sym[:, k], k + 1)
+            summaries.append((s, a, d))
+        state = truth[0]
+        for s, pi, delta in summaries:
+            state = compose(state[0], state[1], pi, delta, s)
+        assert np.array_equal(state[0], truth[n][0]) and np.array_equal(state[1], truth[n][1])
+        # right-to-left grouping gives the same state
+        acc = summaries[-1]
+        for s, pi, delta in reversed(summaries[:-1]):
+            acc = (s,) + compose(pi, delta, acc[1], acc[2], acc[0])
+        state = compose(truth[0][0], truth[0][1], acc[1], acc[2], 0)
+        assert np.array_equal(state[0], truth[n][0]) and np.array_equal(state[1], truth[n][1])

@@ -118,3 +118,17 @@ def test_sharded_small_cap_retries_and_sequential_fallback(fsq, oracle, synth):
     finally:
         sh.segment_sharded = orig
     check_against_oracle(oracle, rows, 6, res)
+
+
+def test_sharded_under_torchrun_nccl():
+    """One rank per GPU over NCCL, when the box has more than one GPU."""
+    import os, subprocess, sys, torch
+    n_gpus = torch.cuda.device_count()
+    if n_gpus < 2:
+        pytest.skip("one GPU: the NCCL run needs at least two")
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(min(n_gpus, 8)),
+           "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(here, "sharded_torchrun.py")]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert r.stdout.count("sharded ok") == 3, r.stdout[-3000:]
