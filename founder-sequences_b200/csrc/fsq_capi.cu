@@ -206,7 +206,7 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 	g.sym0 = lo;
 	g.ns = hi - lo + 1;
 	int64_t const kern = ctx->opt("kernel", 0);        // 0 auto, 1 striped, 2 blocked, 3 chunked
-	g.chunked = (0 == kern || 3 == kern) && g.ns <= 8 && m <= 384u * 33u;
+	g.chunked = (0 == kern || 3 == kern) && g.ns <= 8 && m <= 512u * 33u;
 	g.blocked = !g.chunked && (1 != kern) && g.ns <= 8 && m <= 448u * 33u;
 	uint32_t threads = g.n_warps * 32, regs = 64;
 	if (g.chunked)
@@ -234,7 +234,7 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 		regs = 9 == g.E ? 64 : 128;
 	}
 
-	g.cg = (uint32_t) std::max <uint64_t>(1, (g.chunked ? 1024 : 2048) / msa->col_stride);
+	g.cg = (uint32_t) std::max <uint64_t>(1, (g.chunked ? 512 : 2048) / msa->col_stride);
 	int64_t C = ctx->opt("block_columns", 0);
 	if (C <= 0)
 	{
@@ -250,7 +250,7 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 			P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m;
 			P.C = (uint32_t) std::min <uint64_t>(4096, std::max <uint64_t>(64, msa->n / (ctx->prop.multiProcessorCount * 8)));
 			smem = cblock_smem_bytes(P, g.T, g.E, g.ns, true) + 1024;
-			per_sm = std::min <uint64_t>(per_sm, 65536 / ((uint64_t) threads * (9 == g.E ? 64 : (17 == g.E ? 128 : 168))));
+			per_sm = std::min <uint64_t>(per_sm, 65536 / ((uint64_t) threads * (9 == g.E ? 64 : 128)));
 		}
 		per_sm = std::min <uint64_t>(per_sm, (227 * 1024) / smem);
 		per_sm = std::max <uint64_t>(per_sm, 1);

@@ -84,7 +84,7 @@ inline size_t cblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uin
 	t += r16(sizeof(uint32_t) * words);
 	t += r16(sizeof(uint32_t) * (size_t) T * (NS | 1));
 	t += r16(sizeof(uint32_t) * n_warps * 2 * NS);
-	if (hist) t += r16(sizeof(uint32_t) * ((size_t) A.m + A.C + 8)) + r16(sizeof(uint32_t) * (size_t) A.m);
+	if (hist) t += r16(sizeof(uint32_t) * ((size_t) A.m + A.C + 8));
 	return t;
 }
 cudaError_t launch_cblock_e9(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
