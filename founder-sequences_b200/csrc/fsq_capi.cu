@@ -328,8 +328,8 @@ __global__ void gather_stored_states_kernel(
 	uint32_t const *oldvals, uint32_t const *R, uint32_t *dst_a, uint32_t *dst_d
 )
 {
-	uint32_t const t = blockIdx.y;
-	uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t const t = blockIdx.x;                 // grid.x: up to 2^31 - 1 positions
+	uint32_t const i = blockIdx.y * blockDim.x + threadIdx.x;
 	if (i >= m) return;
 	uint64_t const k = rbs[t] - 1;                 // local column whose output state this is
 	uint32_t const b = (uint32_t) (k / C);
@@ -652,7 +652,7 @@ int shard_init(fsq_shard *P, fsq_ctx *ctx, fsq_msa const *msa, uint64_t n_total,
 	// chains: enough to fill the device a few times over, each a whole number of 64-entry rmq blocks, on a global grid
 	{
 		int64_t want = ctx->opt("dp_chunks", 0);
-		if (want <= 0) want = 4 * (int64_t) ctx->prop.multiProcessorCount;
+		if (want <= 0) want = (int64_t) ctx->prop.multiProcessorCount * (2048 / (32 * (int64_t) std::min <uint64_t>(L, 16)) > 8 ? 8 : 2048 / (32 * (int64_t) std::min <uint64_t>(L, 16)));      // one resident wave of chains
 		uint64_t const own = std::max <uint64_t>(1, P->t_last - P->t_first);
 		uint64_t c = (own + (uint64_t) want - 1) / (uint64_t) want;
 		c = std::max <uint64_t>(c, std::max <uint64_t>(256, 8 * L));
@@ -748,6 +748,7 @@ int shard_dp_round(fsq_shard *P, uint32_t *changed, uint32_t *reach)
 	CK(cudaStreamSynchronize(ctx->stream));
 	*changed = h_flags[0];
 	*reach = h_flags[2];
+	ctx->stats["dp_reach"] = h_flags[2];
 	return FSQ_OK;
 }
 
@@ -916,7 +917,7 @@ int shard_reduced_states(fsq_shard *P)
 		for (uint32_t i = 0; i < cnt; ++i) h_rb.as <uint64_t>()[i] = P->red_rb[P->seg_first + i] - P->c0;      // local right bounds
 		CK(cudaMemcpyAsync(d_rb.p, h_rb.p, (size_t) cnt * 8, cudaMemcpyHostToDevice, ctx->stream));
 		phase pc(ctx, "pass_c");
-		dim3 const grid((m + 255) / 256, cnt);
+		dim3 const grid(cnt, (m + 255) / 256);
 		gather_stored_states_kernel <<<grid, 256, 0, ctx->stream>>>(P->states.as <uint32_t>(), P->state_stride, d_rb.as <uint64_t>(), m, P->S.g.C, P->c0,
 			P->S.oldvals.as <uint32_t>(), P->S.R.as <uint32_t>(), P->red_a.as <uint32_t>(), P->red_d.as <uint32_t>());
 		CK(cudaGetLastError());

@@ -13,13 +13,42 @@ namespace fsq {
 // mask: bit j of mk[t] is set iff entry 64 b + j (j <= t mod 64, b = t / 64) is <= every later entry up to t; the
 // lowest set bit at or above a position is then the leftmost minimum of [position, t].
 
-__device__ __forceinline__ uint32_t inblock_min(uint64_t const *mk, uint32_t first, uint32_t last)
+// Where the table is read from.  table_global: HBM / L2.  table_ring: the last DP_RING entries behind a chain's wavefront
+// in shared memory (entries, masks and the first DP_SLEV rmq levels), global memory for anything older.
+struct table_global
 {
-	unsigned long long const msk = mk[last] & (~0ull << (first & 63u));
+	uint32_t const *Mg; uint64_t const *mkg; uint32_t const *levg; uint32_t n_blk;
+	__device__ __forceinline__ uint32_t M(uint32_t i) const { return Mg[i]; }
+	__device__ __forceinline__ unsigned long long mask(uint32_t i) const { return mkg[i]; }
+	__device__ __forceinline__ uint32_t lev(uint32_t p, uint32_t i) const { return levg[(size_t) p * n_blk + i]; }
+};
+
+constexpr uint32_t DP_RING = 2048;            // entries; a multiple of 64 and a power of two
+constexpr uint32_t DP_RING_BLK = DP_RING / 64;
+constexpr uint32_t DP_SLEV = 6;               // levels 0 .. 5: ranges of up to 63 full blocks
+
+struct table_ring
+{
+	table_global g;
+	uint32_t *sM; unsigned long long *smk; uint32_t *slev;      // [DP_RING], [DP_RING], [DP_SLEV][DP_RING_BLK]
+	uint32_t lo;                                                  // entries >= lo are in the ring (lo is a multiple of 64)
+	__device__ __forceinline__ uint32_t M(uint32_t i) const { return i >= lo ? sM[i & (DP_RING - 1)] : g.Mg[i]; }
+	__device__ __forceinline__ unsigned long long mask(uint32_t i) const { return i >= lo ? smk[i & (DP_RING - 1)] : g.mkg[i]; }
+	__device__ __forceinline__ uint32_t lev(uint32_t p, uint32_t i) const
+	{
+		return (p < DP_SLEV && 64u * i >= lo) ? slev[p * DP_RING_BLK + (i & (DP_RING_BLK - 1))] : g.lev(p, i);
+	}
+};
+
+template <typename V>
+__device__ __forceinline__ uint32_t inblock_min(V const &v, uint32_t first, uint32_t last)
+{
+	unsigned long long const msk = v.mask(last) & (~0ull << (first & 63u));
 	return (last & ~63u) + (uint32_t) __ffsll((long long) msk) - 1u;
 }
 
-__device__ __forceinline__ uint32_t rmq_query(uint32_t const *M, uint64_t const *mk, uint32_t const *lev, uint32_t n_blk, uint32_t beg, uint32_t end)
+template <typename V>
+__device__ __forceinline__ uint32_t rmq_query(V const &v, uint32_t beg, uint32_t end)
 {
 	uint32_t const bb = beg / 64 + 1;
 	uint32_t const eb = end / 64;
@@ -28,30 +57,31 @@ __device__ __forceinline__ uint32_t rmq_query(uint32_t const *M, uint64_t const 
 	{
 		// naive_min(beg, end): at most two consecutive blocks
 		if ((beg >> 6) == (last >> 6))
-			return inblock_min(mk, beg, last);
-		uint32_t const left = inblock_min(mk, beg, beg | 63u);
-		uint32_t const right = inblock_min(mk, last & ~63u, last);
-		return (M[right] < M[left]) ? right : left;
+			return inblock_min(v, beg, last);
+		uint32_t const left = inblock_min(v, beg, beg | 63u);
+		uint32_t const right = inblock_min(v, last & ~63u, last);
+		return (v.M(right) < v.M(left)) ? right : left;
 	}
 	uint32_t const p = 31u - __clz(eb - bb);
-	uint32_t const s1 = lev[(size_t) p * n_blk + bb];
-	uint32_t const s2 = lev[(size_t) p * n_blk + eb - (1u << p)];
-	uint32_t smp = (M[s2] < M[s1]) ? s2 : s1;
-	uint32_t const left = inblock_min(mk, beg, beg | 63u);
-	smp = (M[left] < M[smp]) ? left : smp;
+	uint32_t const s1 = v.lev(p, bb);
+	uint32_t const s2 = v.lev(p, eb - (1u << p));
+	uint32_t smp = (v.M(s2) < v.M(s1)) ? s2 : s1;
+	uint32_t const left = inblock_min(v, beg, beg | 63u);
+	smp = (v.M(left) < v.M(smp)) ? left : smp;
 	if (end == eb * 64)
 		return smp;
-	uint32_t const right = inblock_min(mk, eb * 64, last);
-	return (M[right] < M[smp]) ? right : smp;
+	uint32_t const right = inblock_min(v, eb * 64, last);
+	return (v.M(right) < v.M(smp)) ? right : smp;
 }
 
 // mk[t] from the table; one warp.  Returns the mask in every lane.
-__device__ __forceinline__ unsigned long long make_mask(uint32_t const *M, uint32_t t)
+template <typename V>
+__device__ __forceinline__ unsigned long long make_mask(V const &v, uint32_t t)
 {
 	uint32_t const lane = lane_id();
 	uint32_t const blk = t & ~63u, tt = t & 63u;
-	uint32_t const v0 = lane <= tt ? M[blk + lane] : 0xffffffffu;
-	uint32_t const v1 = lane + 32 <= tt ? M[blk + 32 + lane] : 0xffffffffu;
+	uint32_t const v0 = lane <= tt ? v.M(blk + lane) : 0xffffffffu;
+	uint32_t const v1 = lane + 32 <= tt ? v.M(blk + 32 + lane) : 0xffffffffu;
 	uint32_t s0 = v0, s1 = v1;          // inclusive suffix minima inside each half (shfl_down returns the own value past lane 31)
 #pragma unroll
 	for (int o = 1; o < 32; o <<= 1)
@@ -69,48 +99,85 @@ __device__ __forceinline__ unsigned long long make_mask(uint32_t const *M, uint3
 	return (unsigned long long) b0 | ((unsigned long long) b1 << 32);
 }
 
+// The head of a column's top list, loaded ahead of time (the list lives in HBM; the DP itself runs out of shared memory).
+struct list_head
+{
+	uint32_t cw, h0;        // entry count | complete << 31; #{d == 0}
+	uint2 top;              // entry 0
+	uint2 e0, e1;           // entries 1 + lane and 33 + lane
+	uint32_t old_max;       // what the table holds for this entry (change detection without a round trip at write time)
+	unsigned long long old_mask;
+};
+
+__device__ __forceinline__ list_head load_list_head(dp_args const &A, uint64_t k)
+{
+	uint32_t const lane = lane_id();
+	uint64_t const kl = k - A.col_base;
+	uint2 const *list = A.toplist + kl * (A.cap + 1);
+	list_head h;
+	h.cw = A.cnt[kl];
+	h.h0 = A.h0[kl];
+	uint32_t const E = h.cw & 0x7fffffffu;
+	// a column's slots all exist (cap + 1 of them), so these loads need not wait for the count; slots past E are ignored later
+	(void) E;
+	h.top = list[0];
+	h.e0 = 1 + lane <= A.cap ? list[1 + lane] : make_uint2(0, 0);
+	h.e1 = 33 + lane <= A.cap ? list[33 + lane] : make_uint2(0, 0);
+	h.old_max = 0; h.old_mask = 0;
+	return h;
+}
+
 // One column of calculate_segmentation_lp_dp_arg (reference: founder-sequences/segmentation_lp_context.cc:393-481),
 // evaluated by one warp over the column's top list.  Only ranges whose segment size S is <= cap are listed; any
 // other range has a candidate value > cap, so the result is exact whenever it is <= cap (or the list is complete).
 // The list is in descending order of the divergence value, i.e. ascending S, and a candidate is worth at least its
 // S: once S exceeds the best value so far nothing later can win or tie.
-__device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, uint64_t const t_out, uint32_t &reach)
+// Returns (in every lane) the entry's max; lb and size through the references.
+template <typename V>
+__device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list_head const &h, uint64_t const k, uint64_t const t_out, uint32_t &reach, uint32_t &lb_out, uint32_t &size_out)
 {
 	uint32_t const lane = lane_id();
 	uint32_t const L = (uint32_t) A.L;
 	uint64_t const kl = k - A.col_base;
-	uint32_t const cw = A.cnt[kl];
-	uint32_t const E = cw & 0x7fffffffu;
-	bool const complete = cw >> 31;
+	uint32_t const E = h.cw & 0x7fffffffu;
+	bool const complete = h.cw >> 31;
 	uint2 const *list = A.toplist + kl * (A.cap + 1);
 	uint32_t const hi_clip = (uint32_t) (k + 2 - L);
 
 	unsigned long long best = ~0ull;
 	uint32_t best_idx = 0, best_S = 0;
 	uint32_t far = (uint32_t) t_out;      // the lowest table entry a candidate looked at
+	uint32_t carry_x = h.top.x;            // value of the entry before this round's first
+	uint32_t carry_S = 0;                  // ... and its S: a lower bound for every later S
 	for (uint32_t t0 = 1; t0 < E; t0 += 32)
 	{
-		if ((uint32_t) (best >> 32) < list[t0].y)
-			break;
+		if ((uint32_t) (best >> 32) < carry_S)
+			break;                          // before touching the next part of the list
 		uint32_t const t = t0 + lane;
+		uint2 en;
+		if (1 == t0) en = h.e0;
+		else if (33 == t0) en = h.e1;
+		else en = t < E ? list[t] : make_uint2(0, 0);
+		uint32_t const first_S = __shfl_sync(FSQ_FULL, en.y, 0);
+		if ((uint32_t) (best >> 32) < first_S)
+			break;
+		uint32_t up = __shfl_up_sync(FSQ_FULL, en.x, 1);
+		if (0 == lane) up = carry_x;
+		carry_x = __shfl_sync(FSQ_FULL, en.x, 31);
+		carry_S = t0 + 31 < E ? __shfl_sync(FSQ_FULL, en.y, 31) : 0xffffffffu;
 		unsigned long long key = ~0ull;
-		uint32_t idx = 0, S = 0;
-		if (t < E)
+		uint32_t idx = 0;
+		uint32_t const S = en.y;
+		if (t < E && 0 != en.x)        // the range starting at value 0 is the whole-range candidate, below
 		{
-			uint2 const en = list[t];
-			uint32_t const up = list[t - 1].x;
-			S = en.y;
-			if (0 != en.x)         // the range starting at value 0 is the whole-range candidate, below
+			uint32_t const lo = max(en.x, L);
+			uint32_t const hi = min(up, hi_clip);
+			if (lo < hi)
 			{
-				uint32_t const lo = max(en.x, L);
-				uint32_t const hi = min(up, hi_clip);
-				if (lo < hi)
-				{
-					far = min(far, lo - L);
-					idx = rmq_query(A.tb_max, A.mk, A.lev, A.n_blk, lo - L, hi - L);
-					uint32_t const val = max(A.tb_max[idx], S);
-					key = ((unsigned long long) val << 32) | (0xffffffffu - t);   // ties: the lowest range (largest t) wins
-				}
+				far = min(far, lo - L);
+				idx = rmq_query(v, lo - L, hi - L);
+				uint32_t const val = max(v.M(idx), S);
+				key = ((unsigned long long) val << 32) | (0xffffffffu - t);   // ties: the lowest range (largest t) wins
 			}
 		}
 		unsigned long long kmin = key;
@@ -130,19 +197,14 @@ __device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, ui
 	}
 	far = __reduce_min_sync(FSQ_FULL, far);
 	reach = max(reach, (uint32_t) t_out - far);
-	if (0 == lane)
-	{
-		uint32_t const h0 = A.h0[kl];
-		uint32_t const whole = A.m - h0;          // == m when value 0 is absent
-		uint32_t const best_val = (uint32_t) (best >> 32);
-		uint32_t lb = 0, mx = whole, sz = whole;
-		if (~0ull != best && best_val < whole) { lb = best_idx + L; mx = best_val; sz = best_S; }
-		if (!complete && mx > A.cap)
-			atomicMax(&A.flags[1], (uint32_t) (k + 1));
-		if (A.tb_max[t_out] != mx) { A.tb_max[t_out] = mx; A.flags[0] = 1; }
-		A.tb_lb[t_out] = lb;
-		A.tb_size[t_out] = sz;
-	}
+	uint32_t const whole = A.m - h.h0;          // == m when value 0 is absent
+	uint32_t const best_val = (uint32_t) (best >> 32);
+	uint32_t lb = 0, mx = whole, sz = whole;
+	if (~0ull != best && best_val < whole) { lb = best_idx + L; mx = best_val; sz = best_S; }
+	if (0 == lane && !complete && mx > A.cap)
+		atomicMax(&A.flags[1], (uint32_t) (k + 1));
+	lb_out = lb; size_out = sz;
+	return mx;
 }
 
 // First pass staging (reference: segmentation_lp_context.cc:26-188).  Entry t (column t + L - 1) reads only
@@ -154,64 +216,131 @@ __device__ __forceinline__ void dp_column(dp_args const &A, uint64_t const k, ui
 // after one round, so at most n_chunks rounds are needed; the guess after the first round makes it two or three).
 // Everything stored is written by exactly one chain: entries, masks and level-0 cells by the chunk's owner, a cell
 // lev[p][i] by the owner of block i + 2^p - 1, whose completion defines it (rmq.hh:61-84).
+//
+// A chain is latency-bound (a wavefront is a handful of dependent look-ups), so it works out of shared memory: the
+// last DP_RING entries, their masks and the low rmq levels sit in a ring behind the wavefront (a column looks back a
+// few hundred entries at most on real data; anything older is read from global memory), every result is written
+// through to global memory for the other chains and the later stages, and the head of the next wavefront's top lists
+// is loaded while the current one is computed.  One warp per column of the wavefront.
 __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 {
+	__shared__ uint32_t sM[DP_RING];
+	__shared__ unsigned long long smk[DP_RING];
+	__shared__ uint32_t slev[DP_SLEV * DP_RING_BLK];
 	uint32_t const warp = threadIdx.x >> 5;
-	uint32_t const n_warps = blockDim.x >> 5;
+	uint32_t const W = blockDim.x >> 5;           // columns per wavefront, <= min(L, 32)
 	uint32_t const lane = lane_id();
 	uint32_t const L = (uint32_t) A.L;
-	uint32_t const W = L < 64 ? L : 64;
 	// chains sit on a global grid of `chunk` entries; this rank runs the ones that meet [t_first, t_last)
 	uint32_t const c = A.t_first / A.chunk + blockIdx.x;
 	uint32_t const t_begin = max(A.t_first, c * A.chunk);
 	uint32_t const t_end = min(A.t_last, (c + 1) * A.chunk);
 	uint32_t reach = 0;
 
+	table_ring v;
+	v.g.Mg = A.tb_max; v.g.mkg = A.mk; v.g.levg = A.lev; v.g.n_blk = A.n_blk;
+	v.sM = sM; v.smk = smk; v.slev = slev;
+	// what the table holds behind the chain, as the previous round (or the other chains) left it
+	{
+		uint32_t const hi = (t_begin + 63u) & ~63u;
+		uint32_t const lo = hi > DP_RING ? hi - DP_RING : 0u;
+		for (uint32_t i = lo + threadIdx.x; i < t_begin; i += blockDim.x)
+		{
+			sM[i & (DP_RING - 1)] = A.tb_max[i];
+			smk[i & (DP_RING - 1)] = A.mk[i];
+		}
+		for (uint32_t j = threadIdx.x; j < DP_SLEV * DP_RING_BLK; j += blockDim.x)
+		{
+			uint32_t const p = j / DP_RING_BLK, i = lo / 64 + j % DP_RING_BLK;
+			if (p < A.n_levels && i < A.n_blk) slev[p * DP_RING_BLK + (i & (DP_RING_BLK - 1))] = A.lev[(size_t) p * A.n_blk + i];
+		}
+		v.lo = lo;
+	}
+	__syncthreads();
+
+	auto load_head = [&](uint32_t t) {
+		list_head h = load_list_head(A, (uint64_t) t + L - 1);
+		h.old_max = A.tb_max[t];
+		h.old_mask = A.mk[t];
+		return h;
+	};
+	list_head next;
+	if (t_begin + warp < t_end) next = load_head(t_begin + warp);
+	uint32_t pend_old = 0, pend_new = 0;      // warp 0: a level cell's previous and new value, compared one completion later
+
 	for (uint32_t t0 = t_begin; t0 < t_end; t0 += W)
 	{
 		uint32_t const t1 = min(t_end, t0 + W);
-		for (uint32_t t = t0 + warp; t < t1; t += n_warps)
-			dp_column(A, (uint64_t) t + L - 1, t, reach);
+		uint32_t const t = t0 + warp;
+		// the ring keeps [lo, t1): entries that would share a slot with this wavefront's are read from global memory
+		uint32_t const hi = (t1 + 63u) & ~63u;
+		v.lo = max(v.lo, hi > DP_RING ? hi - DP_RING : 0u);
+		list_head const cur = next;
+		if (t + W < t_end) next = load_head(t + W);
+		if (t < t1)
+		{
+			uint32_t lb = 0, sz = 0;
+			uint32_t const mx = dp_column(A, v, cur, (uint64_t) t + L - 1, t, reach, lb, sz);
+			if (0 == lane)
+			{
+				A.tb_max[t] = mx;
+				A.tb_lb[t] = lb;
+				A.tb_size[t] = sz;
+				if (cur.old_max != mx) A.flags[0] = 1;
+				sM[t & (DP_RING - 1)] = mx;       // this slot's previous tenant is older than anything the wavefront reads from the ring
+			}
+		}
 		__syncthreads();
 
 		// masks of the new entries; then rmq.update for the block that completed, if one did (W <= 64: at most one)
-		for (uint32_t t = t0 + warp; t < t1; t += n_warps)
+		if (t < t1)
 		{
-			unsigned long long const msk = make_mask(A.tb_max, t);
-			if (0 == lane && A.mk[t] != msk) { A.mk[t] = msk; A.flags[0] = 1; }
-		}
-		__syncthreads();
-		if (0 == warp && (t1 >> 6) != (t0 >> 6))
-		{
-			uint32_t const b = (t1 >> 6) - 1;
-			uint32_t const smp0 = 64 * b + (uint32_t) __ffsll((long long) A.mk[64 * b + 63]) - 1u;      // leftmost minimal entry of the block
-			uint32_t const val0 = A.tb_max[smp0];
-			uint32_t const p = lane;
-			if (0 == p)
+			unsigned long long const msk = make_mask(v, t);
+			if (0 == lane)
 			{
-				if (A.lev[b] != smp0) { A.lev[b] = smp0; A.flags[0] = 1; }
-			}
-			else if (p < A.n_levels && (1ull << p) <= (uint64_t) b + 1)
-			{
-				uint32_t const i = b + 1 - (1u << p);
-				uint32_t const prev = A.lev[(size_t) (p - 1) * A.n_blk + i];
-				uint32_t const res = (val0 < A.tb_max[prev]) ? smp0 : prev;
-				uint32_t *cell = &A.lev[(size_t) p * A.n_blk + i];
-				if (*cell != res) { *cell = res; A.flags[0] = 1; }
+				smk[t & (DP_RING - 1)] = msk;
+				A.mk[t] = msk;
+				if (cur.old_mask != msk) A.flags[0] = 1;
 			}
 		}
-		// the next wavefront's queries may read what was just written
 		__syncthreads();
+		if ((t1 >> 6) != (t0 >> 6))
+		{
+			if (0 == warp)
+			{
+				uint32_t const b = (t1 >> 6) - 1;
+				uint32_t const smp0 = 64 * b + (uint32_t) __ffsll((long long) v.mask(64 * b + 63)) - 1u;      // leftmost minimal entry of the block
+				uint32_t const val0 = v.M(smp0);
+				if (pend_old != pend_new) A.flags[0] = 1;
+				pend_old = pend_new = 0;
+				// lev[p][b + 1 - 2^p] from lev[p - 1][b + 1 - 2^p], which an earlier block's completion wrote: independent across p
+				uint32_t const p = lane;
+				if (p < A.n_levels && (0 == p || (1ull << p) <= (uint64_t) b + 1))
+				{
+					uint32_t const i = b + 1 - (1u << p);
+					uint32_t res = smp0;
+					if (p)
+					{
+						uint32_t const prev = v.lev(p - 1, i);
+						res = (val0 < v.M(prev)) ? smp0 : prev;
+					}
+					pend_new = res;
+					pend_old = atomicExch(&A.lev[(size_t) p * A.n_blk + i], res);     // the old value is looked at a block later
+					if (p < DP_SLEV && 64u * i >= v.lo) slev[p * DP_RING_BLK + (i & (DP_RING_BLK - 1))] = res;
+				}
+			}
+			// the next wavefront's queries may read what was just written
+			__syncthreads();
+		}
 	}
+	if (0 == warp && pend_old != pend_new) A.flags[0] = 1;
 	if (0 == lane && reach) atomicMax(&A.flags[2], reach);
 }
 
 cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st)
 {
-	// one warp per column of a wavefront, in as few equal passes as 16 warps allow
-	uint32_t const W = (uint32_t) (A.L < 64 ? A.L : 64);
-	uint32_t const passes = (W + 15) / 16;
-	uint32_t const n_warps = (W + passes - 1) / passes;
+	// one warp per column of a wavefront
+	uint32_t const n_warps = (uint32_t) (A.L < 16 ? A.L : 16);
 	if (A.t_first >= A.t_last) return cudaSuccess;
 	uint32_t const own_chunks = (A.t_last - 1) / A.chunk - A.t_first / A.chunk + 1;
 	dp_chain_kernel <<<own_chunks, n_warps * 32, 0, st>>>(A);
@@ -221,8 +350,18 @@ cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st)
 // segmentation_lp_context.cc:165-185: the final column, from the final histogram
 __global__ void dp_final_kernel(dp_args const A)
 {
-	uint32_t reach = 0;
-	dp_column(A, A.n - 1, A.n - A.L, reach);
+	uint32_t reach = 0, lb = 0, sz = 0;
+	table_global v;
+	v.Mg = A.tb_max; v.mkg = A.mk; v.levg = A.lev; v.n_blk = A.n_blk;
+	uint64_t const t = A.n - A.L;
+	list_head const h = load_list_head(A, A.n - 1);
+	uint32_t const mx = dp_column(A, v, h, A.n - 1, t, reach, lb, sz);
+	if (0 == lane_id())
+	{
+		A.tb_max[t] = mx;
+		A.tb_lb[t] = lb;
+		A.tb_size[t] = sz;
+	}
 }
 
 cudaError_t launch_dp_final(dp_args const &A, cudaStream_t st)
@@ -294,7 +433,9 @@ __global__ void dp_masks_kernel(dp_args const A)
 {
 	uint32_t const t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if (t >= A.n_entries) return;
-	unsigned long long const msk = make_mask(A.tb_max, t);
+	table_global v;
+	v.Mg = A.tb_max; v.mkg = A.mk; v.levg = A.lev; v.n_blk = A.n_blk;
+	unsigned long long const msk = make_mask(v, t);
 	if (0 == lane_id()) A.mk[t] = msk;
 }
 
