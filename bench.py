@@ -161,6 +161,18 @@ def main():
     return run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, torch, fsq)
 
 
+def ncu_traffic(workload, phase):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant scan launch from the committed `ncu --set full`
+    capture (profiles/roofline_traffic.json; per launch, same workload), or None when no capture covers this case."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            t = json.load(f)
+        e = t[workload][phase]
+        return e["dram_bytes"], e["source"]
+    except (OSError, KeyError, ValueError):
+        return None, None
+
+
 def make_rows_sample(np, torch, fsq, m, nc, seed, founders, gaps, device_ok):
     if device_ok:
         with fsq.Context(0) as ctx:
@@ -333,8 +345,9 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
     peak, peak_src = measured_peak()
     dom = max(("pass_a", "pass_b", "pass_c"), key=lambda k: phases[k])
     ach = cells * BYTES_PER_CELL / (phases[dom] * 1e-3) / 1e9 if phases[dom] > 0 else 0.0
-    roofline = {"bound": "hbm", "kernel": "pbwt_block_kernel (%s)" % dom, "achieved": ach, "peak": peak, "unit": "GB/s",
-                "frac": ach / peak, "traffic": None, "peak_source": peak_src,
+    traffic, traffic_src = ncu_traffic(args.workload, dom)
+    roofline = {"bound": "hbm", "kernel": "pbwt_cblock_kernel (%s)" % dom, "achieved": ach, "peak": peak, "unit": "GB/s",
+                "frac": ach / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": cells * BYTES_PER_CELL, "launch_ms": phases[dom]}
     line = {
         "metric": METRIC, "value": world * cells * args.steps / secs, "unit": "cells/s", "n_gpus": world, "steps": args.steps,
