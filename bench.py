@@ -255,9 +255,11 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             return info
         eng = sharded.GpuShard(ctx, msa, rank * n, n_total, L)
         try:
-            res = sharded.segment_sharded(eng, comm, want_states=False)
+            res = sharded.segment_sharded(eng, comm, want_states=False, want_traceback=False)
         finally:
             eng.close()
+        if getattr(res, "trace", None) and rank == 0:
+            sys.stderr.write("shard trace (rank 0, ms): " + ", ".join("%s %.3f" % kv for kv in res.trace) + "\n")
         return (res.K, len(res.lb))
 
     sampler = ClockSampler(dev)

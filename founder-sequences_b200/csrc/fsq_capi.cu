@@ -600,6 +600,7 @@ struct fsq_shard
 	uint64_t dp_size{};
 	uint32_t n_entries{}, n_blk{}, n_levels{}, t_first{}, t_last{};
 	uint32_t chunk{}, n_chunks{}, cap{}, rounds{};
+	uint32_t reach_known{};     // the farthest look-back any rank has seen in the rounds so far
 	bool single_chain{false};
 	dbuf tb_max, tb_lb, tb_size, mk, lev, flags, chunk_level, cnt, h0, toplist, states;
 	uint64_t state_stride{};
@@ -629,6 +630,12 @@ struct fsq_shard
 		D.n_chunks = single_chain ? 1 : n_chunks;
 		D.chunk_level = chunk_level.as <uint32_t>();
 		D.flags = flags.as <uint32_t>();
+		D.reach_bound = reach_known;
+		{
+			// what this rank's chains can read: its own entries and the look-back before them (twice the bound, for slack)
+			uint64_t const back = 2 * (uint64_t) reach_known + 128;
+			D.w_first = (uint32_t) ((t_first > back ? t_first - back : 0) & ~63ull);
+		}
 		return D;
 	}
 };
@@ -708,6 +715,7 @@ int shard_scan(fsq_shard *P)
 	CK(cudaMemsetAsync(P->lev.p, 0, (size_t) P->n_levels * P->n_blk * 4, ctx->stream));
 	CK(cudaMemsetAsync(P->flags.p, 0, 16, ctx->stream));
 	P->rounds = 0;
+	P->reach_known = 0;
 	P->single_chain = false;
 	{
 		phase pb(ctx, "pass_b");
@@ -731,7 +739,10 @@ int shard_scan(fsq_shard *P)
 	return FSQ_OK;
 }
 
-// One DP round: every own chain once against the table as it stands.  changed: some stored value changed;
+// One DP round: every own chain once against the table as it stands.  changed: another round is needed -- in the first
+// round, some stored value changed; later, some value changed that a chain after its owner may have read while it was
+// still the old one (dp_chain_kernel: the last reach_known entries of a chain, or any rmq cell), or a chain read
+// further back than that.  A round without such a change has computed every entry from final values.
 // reach: the farthest any column has looked back so far (entries).
 int shard_dp_round(fsq_shard *P, uint32_t *changed, uint32_t *reach)
 {
@@ -739,6 +750,7 @@ int shard_dp_round(fsq_shard *P, uint32_t *changed, uint32_t *reach)
 	phase pd(ctx, "dp");
 	dp_args const D = P->dp();
 	CK(cudaMemsetAsync(P->flags.p, 0, 4, ctx->stream));
+	CK(cudaMemsetAsync(P->flags.as <uint32_t>() + 3, 0, 4, ctx->stream));
 	CK(launch_dp_chains(D, ctx->stream));
 	ctx->stats["kernel_launches"] += 1;
 	++P->rounds;
@@ -746,8 +758,9 @@ int shard_dp_round(fsq_shard *P, uint32_t *changed, uint32_t *reach)
 	CK(cudaMemcpyAsync(h_flags, P->flags.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
 	pd.stop();
 	CK(cudaStreamSynchronize(ctx->stream));
-	*changed = h_flags[0];
+	*changed = (h_flags[0] && (1 == P->rounds || h_flags[3])) ? 1u : 0u;
 	*reach = h_flags[2];
+	P->reach_known = std::max(P->reach_known, h_flags[2]);
 	ctx->stats["dp_reach"] = h_flags[2];
 	return FSQ_OK;
 }
@@ -758,6 +771,7 @@ int shard_dp_sync(fsq_shard *P, int guess, uint32_t reach)
 	fsq_ctx *ctx = P->ctx;
 	phase pd(ctx, "dp");
 	dp_args const D = P->dp();
+	P->reach_known = std::max(P->reach_known, reach);
 	if (guess)
 	{
 		CK(cudaMemcpyAsync(P->flags.as <uint32_t>() + 2, &reach, 4, cudaMemcpyHostToDevice, ctx->stream));

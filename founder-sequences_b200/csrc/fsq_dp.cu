@@ -134,7 +134,7 @@ __device__ __forceinline__ list_head load_list_head(dp_args const &A, uint64_t k
 // S: once S exceeds the best value so far nothing later can win or tie.
 // Returns (in every lane) the entry's max; lb and size through the references.
 template <typename V>
-__device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list_head const &h, uint64_t const k, uint64_t const t_out, uint32_t &reach, uint32_t &lb_out, uint32_t &size_out)
+__device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list_head const &h, uint64_t const k, uint64_t const t_out, uint32_t &reach, uint32_t &lowest, uint32_t &lb_out, uint32_t &size_out)
 {
 	uint32_t const lane = lane_id();
 	uint32_t const L = (uint32_t) A.L;
@@ -197,6 +197,7 @@ __device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list
 	}
 	far = __reduce_min_sync(FSQ_FULL, far);
 	reach = max(reach, (uint32_t) t_out - far);
+	lowest = min(lowest, far);
 	uint32_t const whole = A.m - h.h0;          // == m when value 0 is absent
 	uint32_t const best_val = (uint32_t) (best >> 32);
 	uint32_t lb = 0, mx = whole, sz = whole;
@@ -236,6 +237,12 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 	uint32_t const t_begin = max(A.t_first, c * A.chunk);
 	uint32_t const t_end = min(A.t_last, (c + 1) * A.chunk);
 	uint32_t reach = 0;
+	// What a later chain may have read of this one while it ran: the last reach_bound entries (the look-back seen in the
+	// rounds before).  A round in which no chain changed anything there, and no chain read below that window, has
+	// computed every entry from values that are final: flags[3] counts the chains for which this cannot be said.
+	uint32_t const tail_from = t_end > A.reach_bound ? t_end - A.reach_bound : 0u;
+	uint32_t lowest = 0xffffffffu;
+	bool unsettled = false;
 
 	table_ring v;
 	v.g.Mg = A.tb_max; v.g.mkg = A.mk; v.g.levg = A.lev; v.g.n_blk = A.n_blk;
@@ -280,13 +287,13 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 		if (t < t1)
 		{
 			uint32_t lb = 0, sz = 0;
-			uint32_t const mx = dp_column(A, v, cur, (uint64_t) t + L - 1, t, reach, lb, sz);
+			uint32_t const mx = dp_column(A, v, cur, (uint64_t) t + L - 1, t, reach, lowest, lb, sz);
 			if (0 == lane)
 			{
 				A.tb_max[t] = mx;
 				A.tb_lb[t] = lb;
 				A.tb_size[t] = sz;
-				if (cur.old_max != mx) A.flags[0] = 1;
+				if (cur.old_max != mx) { A.flags[0] = 1; unsettled |= t >= tail_from; }
 				sM[t & (DP_RING - 1)] = mx;       // this slot's previous tenant is older than anything the wavefront reads from the ring
 			}
 		}
@@ -300,7 +307,7 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 			{
 				smk[t & (DP_RING - 1)] = msk;
 				A.mk[t] = msk;
-				if (cur.old_mask != msk) A.flags[0] = 1;
+				if (cur.old_mask != msk) { A.flags[0] = 1; unsettled |= t >= tail_from; }
 			}
 		}
 		__syncthreads();
@@ -311,7 +318,7 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 				uint32_t const b = (t1 >> 6) - 1;
 				uint32_t const smp0 = 64 * b + (uint32_t) __ffsll((long long) v.mask(64 * b + 63)) - 1u;      // leftmost minimal entry of the block
 				uint32_t const val0 = v.M(smp0);
-				if (pend_old != pend_new) A.flags[0] = 1;
+				if (pend_old != pend_new) { A.flags[0] = 1; unsettled = true; }
 				pend_old = pend_new = 0;
 				// lev[p][b + 1 - 2^p] from lev[p - 1][b + 1 - 2^p], which an earlier block's completion wrote: independent across p
 				uint32_t const p = lane;
@@ -333,8 +340,11 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 			__syncthreads();
 		}
 	}
-	if (0 == warp && pend_old != pend_new) A.flags[0] = 1;
+	if (0 == warp && pend_old != pend_new) { A.flags[0] = 1; unsettled = true; }
 	if (0 == lane && reach) atomicMax(&A.flags[2], reach);
+	// reads below the own entries must stay inside the window the chains before this one watch
+	if (0xffffffffu != lowest && lowest < t_begin && t_begin - lowest > A.reach_bound) unsettled = true;
+	if (__any_sync(FSQ_FULL, unsettled) && 0 == lane) atomicAdd(&A.flags[3], 1u);
 }
 
 cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st)
@@ -350,12 +360,12 @@ cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st)
 // segmentation_lp_context.cc:165-185: the final column, from the final histogram
 __global__ void dp_final_kernel(dp_args const A)
 {
-	uint32_t reach = 0, lb = 0, sz = 0;
+	uint32_t reach = 0, lowest = 0xffffffffu, lb = 0, sz = 0;
 	table_global v;
 	v.Mg = A.tb_max; v.mkg = A.mk; v.levg = A.lev; v.n_blk = A.n_blk;
 	uint64_t const t = A.n - A.L;
 	list_head const h = load_list_head(A, A.n - 1);
-	uint32_t const mx = dp_column(A, v, h, A.n - 1, t, reach, lb, sz);
+	uint32_t const mx = dp_column(A, v, h, A.n - 1, t, reach, lowest, lb, sz);
 	if (0 == lane_id())
 	{
 		A.tb_max[t] = mx;
@@ -429,9 +439,11 @@ __global__ void dp_raise_kernel(dp_args const A)
 	if (A.tb_max[t] < lvl) A.tb_max[t] = lvl;
 }
 
+// Masks and rmq cells are rebuilt from A.w_first on (a multiple of 64): a column-sharded rank reads the table only
+// from its own entries back to the look-back bound, and a chain that reads below that bound asks for another round.
 __global__ void dp_masks_kernel(dp_args const A)
 {
-	uint32_t const t = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	uint32_t const t = A.w_first + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if (t >= A.n_entries) return;
 	table_global v;
 	v.Mg = A.tb_max; v.mkg = A.mk; v.levg = A.lev; v.n_blk = A.n_blk;
@@ -442,7 +454,7 @@ __global__ void dp_masks_kernel(dp_args const A)
 // Level p of the rmq tables for every cell whose defining block is complete.
 __global__ void dp_levels_kernel(dp_args const A, uint32_t p)
 {
-	uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t const i = A.w_first / 64 + blockIdx.x * blockDim.x + threadIdx.x;
 	uint32_t const n_complete = A.n_entries / 64;
 	uint64_t const b = (uint64_t) i + (1ull << p) - 1;       // the block whose completion defines lev[p][i]
 	if (b >= n_complete) return;
@@ -454,14 +466,11 @@ __global__ void dp_levels_kernel(dp_args const A, uint32_t p)
 
 cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st)
 {
+	// (launch_dp_rebuild is declared in fsq_internal.h)
 	dp_chunk_level_kernel <<<A.n_chunks, 128, 0, st>>>(A);
 	dp_level_kernel <<<1, 1024, 0, st>>>(A);
 	dp_raise_kernel <<<(A.n_entries + 255) / 256, 256, 0, st>>>(A);
-	dp_masks_kernel <<<(A.n_entries + 7) / 8, 256, 0, st>>>(A);
-	uint32_t const n_complete = A.n_entries / 64;
-	for (uint32_t p = 0; p < A.n_levels && (1ull << p) <= n_complete; ++p)
-		dp_levels_kernel <<<(n_complete + 255) / 256, 256, 0, st>>>(A, p);
-	return cudaGetLastError();
+	return launch_dp_rebuild(A, st);
 }
 
 
@@ -469,10 +478,13 @@ cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st)
 // other ranks' entries.
 cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st)
 {
-	dp_masks_kernel <<<(A.n_entries + 7) / 8, 256, 0, st>>>(A);
+	if (A.w_first >= A.n_entries) return cudaSuccess;
+	uint32_t const span = A.n_entries - A.w_first;
+	dp_masks_kernel <<<(span + 7) / 8, 256, 0, st>>>(A);
 	uint32_t const n_complete = A.n_entries / 64;
-	for (uint32_t p = 0; p < A.n_levels && (1ull << p) <= n_complete; ++p)
-		dp_levels_kernel <<<(n_complete + 255) / 256, 256, 0, st>>>(A, p);
+	uint32_t const first_blk = A.w_first / 64;
+	for (uint32_t p = 0; p < A.n_levels && (1ull << p) <= n_complete && first_blk < n_complete; ++p)
+		dp_levels_kernel <<<(n_complete - first_blk + 255) / 256, 256, 0, st>>>(A, p);
 	return cudaGetLastError();
 }
 

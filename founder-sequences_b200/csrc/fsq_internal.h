@@ -133,6 +133,9 @@ struct dp_args
 	uint32_t *chunk_level;      // [2 n_chunks] scratch for the guess
 	uint32_t *flags;            // [0] some stored value changed  [1] 1 + column whose top list was too short to be exact
 	                            // [2] the farthest any column looked back in the table (entries), over all rounds
+	                            // [3] chains of this round whose result a later chain may have read half-way (see dp_chain_kernel)
+	uint32_t reach_bound;       // the look-back known when the round starts (0 in the first round)
+	uint32_t w_first;           // masks and rmq cells are rebuilt for entries >= w_first (a multiple of 64)
 };
 
 cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st);       // every chain once, against the table as it stands

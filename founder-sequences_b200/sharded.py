@@ -13,7 +13,9 @@ broadcast per rank of its slice of the table (4 bytes per column) plus two scala
 columns once at the end, and K + 1 (value, count) pairs per traceback position for the reduction.
 """
 import ctypes as C
+import os
 import threading
+import time
 
 import numpy as np
 import torch
@@ -48,6 +50,19 @@ class TorchComm:
         t = torch.tensor([int(value)], dtype=torch.int64, device=device)
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
         return int(t.item())
+
+    def max_many(self, values, device):
+        """Element-wise maximum over the ranks of a few non-negative integers: one collective, one read-back."""
+        t = torch.tensor([int(v) for v in values], dtype=torch.int64, device=device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+        return [int(v) for v in t.tolist()]
+
+    def gather_ints(self, values, device):
+        """Every rank's tuple of integers, in rank order (one all-gather of a small tensor; no pickling)."""
+        t = torch.tensor([int(v) for v in values], dtype=torch.int64, device=device)
+        out = [torch.empty_like(t) for _ in range(self.size)]
+        self.dist.all_gather(out, t, group=self.group)
+        return [tuple(r) for r in torch.stack(out).tolist()]
 
     def gather_objects(self, obj):
         out = [None] * self.size
@@ -97,6 +112,13 @@ class ThreadComm:
 
     def max(self, value, device):
         return max(int(v) for v in self._exchange(int(value)))
+
+    def max_many(self, values, device):
+        vals = self._exchange([int(v) for v in values])
+        return [max(col) for col in zip(*vals)]
+
+    def gather_ints(self, values, device):
+        return [tuple(v) for v in self._exchange([int(v) for v in values])]
 
     def gather_objects(self, obj):
         return self._exchange(obj)
@@ -248,23 +270,51 @@ def _exchange_slices(comm, tensors, ranges):
             comm.broadcast(t[f:l], src)
 
 
-def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=True):
+def entry_range(c0, c1, n, L):
+    """The DP entries computed by the rank that holds columns [c0, c1) of n: entry t belongs to column t + L - 1, and
+    the rank with the last column also owns the final entry (fsq_shard_dp_table; shard_init in fsq_capi.cu)."""
+    n_entries, dp_size = n - 2 * L + 1, n - L + 1
+    first = min(max(0, c0 + 1 - L), n_entries)
+    last = dp_size if c1 == n else min(max(0, c1 + 1 - L), n_entries)
+    return first, last
+
+
+def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=True, want_traceback=True):
     """Run the long path over the column shards held by the ranks of `comm`; `engine` is this rank's shard.
     Raises NotReducible when K == m (generate_context.cc:192-200)."""
     res = ShardedResult()
     dev = getattr(engine, "device", torch.device("cpu"))
+    trace = [] if os.environ.get("FSQ_SHARD_TRACE") else None
+    t_prev = [time.perf_counter()]
+
+    def mark(name):
+        # host-side stage clock (FSQ_SHARD_TRACE=1): the stages block, so no device synchronise is needed here
+        if trace is not None:
+            now = time.perf_counter()
+            trace.append((name, 1e3 * (now - t_prev[0])))
+            t_prev[0] = now
 
     # 1. local scans, then the boundary states: rank r composes the summaries of the ranks before it
     summary = engine.local_summary()
-    summaries = comm.all_gather(summary)
-    firsts = comm.gather_objects(engine.c0)
+    mark("local_summary")
+    # the column range of every rank travels with its summary: no separate exchange
+    m = summary.shape[1]
+    tail = torch.tensor([engine.c0, engine.c1], dtype=summary.dtype, device=summary.device)
+    packed = comm.all_gather(torch.cat([summary.reshape(-1), tail]))
+    summaries = [p[: 2 * m].view(2, m) for p in packed]
+    cols = torch.stack([p[2 * m:] for p in packed]).cpu().tolist()
+    firsts = [int(c[0]) for c in cols]
+    mark("all_gather summaries")
     engine.set_start(summaries[: comm.rank], firsts[: comm.rank])
+    mark("set_start")
 
     # 2. exact scan + DP until the table is a fixed point everywhere; the top-list bound grows if the DP says so
     while True:
         engine.scan()
+        mark("scan")
         tabs, own = engine.dp_table()
-        ranges = comm.gather_objects(own)
+        ranges = [entry_range(int(c[0]), int(c[1]), engine.n, engine.L) for c in cols]
+        assert tuple(ranges[comm.rank]) == tuple(own), (ranges[comm.rank], own)
         rounds = 0
         sequential = False
         while True:
@@ -278,10 +328,12 @@ def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=Tru
                 rounds += 1
                 break
             changed, reach = engine.dp_round()
+            mark("dp_round")
             rounds += 1
             _exchange_slices(comm, tabs[:1], ranges)
-            changed = comm.max(changed, dev)
-            reach = comm.max(reach, dev)
+            mark("dp exchange")
+            changed, reach = comm.max_many((changed, reach), dev)
+            mark("dp flags")
             if comm.size == 1 and rounds > 1 and not changed:
                 break
             if rounds > 1 and not changed:
@@ -292,9 +344,12 @@ def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=Tru
                 engine.dp_sync(False, reach)
                 continue
             engine.dp_sync(rounds <= guess_rounds, reach)
+            mark("dp_sync")
         overflow = engine.dp_final()
+        mark("dp_final")
         _exchange_slices(comm, tabs, ranges)
         overflow = comm.max(overflow, dev)
+        mark("table exchange")
         res.dp_rounds += rounds
         if not overflow:
             break
@@ -303,18 +358,26 @@ def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=Tru
 
     # 3. traceback (replicated), reduction lists (exchanged), greedy reduction (replicated), own states
     T, K = engine.traceback()
+    mark("traceback")
     res.K = K
-    res.traceback = engine.get_traceback(T)
+    if want_traceback:
+        res.traceback = engine.get_traceback(T)
+        mark("get_traceback")
     if not K < engine.m:
         raise NotReducible("the maximum segment size %d is equal to the number of input sequences" % K)
     lists, row, own_pos = engine.reduce_lists(T)
-    pos_ranges = comm.gather_objects(own_pos)
+    mark("reduce_lists")
+    pos_ranges = comm.gather_ints(own_pos, dev)
     _exchange_slices(comm, [lists], [(f * row, l * row) for f, l in pos_ranges])
+    mark("lists exchange")
     count, own_seg = engine.reduce()
+    mark("reduce")
     res.lb, res.rb, res.size = engine.bounds(count)
     res.own = own_seg
     if want_states:
         res.a, res.d = engine.states(own_seg)
+    mark("bounds/states")
+    res.trace = trace
     return res
 
 
