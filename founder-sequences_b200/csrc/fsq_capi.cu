@@ -386,6 +386,7 @@ int run_stitch_plan(fsq_ctx *ctx, scan_state &S, stitch_plan const &plan, uint32
 		SA.n_ctas = (uint32_t) count;
 		SA.m = m;
 		SA.n_tiles = S.g.n_tiles;
+		SA.use_sort = ctx->opt("stitch_sort", 1) ? 1u : 0u;
 		CK(launch_stitch(SA, ctx->stream));
 		ctx->stats["kernel_launches"] += 1;
 	}
@@ -1051,7 +1052,7 @@ int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
 		}
 		return FSQ_OK;
 	}
-	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", nullptr};
+	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", nullptr};
 	for (char const **k = known; *k; ++k)
 		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }
 	return fail(ctx, FSQ_ERR_ARG, "unknown option '%s'", key);

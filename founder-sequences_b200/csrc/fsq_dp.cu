@@ -144,14 +144,16 @@ __device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list
 	uint2 const *list = A.toplist + kl * (A.cap + 1);
 	uint32_t const hi_clip = (uint32_t) (k + 2 - L);
 
-	unsigned long long best = ~0ull;
+	// candidates compare as (value, range index) packed into 32 bits -- both are < 2^16 (m <= 65000) -- so that the
+	// minimum over the warp is one redux instruction; ties: the lowest range (largest t) wins
+	uint32_t best = 0xffffffffu;
 	uint32_t best_idx = 0, best_S = 0;
 	uint32_t far = (uint32_t) t_out;      // the lowest table entry a candidate looked at
 	uint32_t carry_x = h.top.x;            // value of the entry before this round's first
 	uint32_t carry_S = 0;                  // ... and its S: a lower bound for every later S
 	for (uint32_t t0 = 1; t0 < E; t0 += 32)
 	{
-		if ((uint32_t) (best >> 32) < carry_S)
+		if ((best >> 16) < carry_S)
 			break;                          // before touching the next part of the list
 		uint32_t const t = t0 + lane;
 		uint2 en;
@@ -159,13 +161,13 @@ __device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list
 		else if (33 == t0) en = h.e1;
 		else en = t < E ? list[t] : make_uint2(0, 0);
 		uint32_t const first_S = __shfl_sync(FSQ_FULL, en.y, 0);
-		if ((uint32_t) (best >> 32) < first_S)
+		if ((best >> 16) < first_S)
 			break;
 		uint32_t up = __shfl_up_sync(FSQ_FULL, en.x, 1);
 		if (0 == lane) up = carry_x;
 		carry_x = __shfl_sync(FSQ_FULL, en.x, 31);
 		carry_S = t0 + 31 < E ? __shfl_sync(FSQ_FULL, en.y, 31) : 0xffffffffu;
-		unsigned long long key = ~0ull;
+		uint32_t key = 0xffffffffu;
 		uint32_t idx = 0;
 		uint32_t const S = en.y;
 		if (t < E && 0 != en.x)        // the range starting at value 0 is the whole-range candidate, below
@@ -177,16 +179,10 @@ __device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list
 				far = min(far, lo - L);
 				idx = rmq_query(v, lo - L, hi - L);
 				uint32_t const val = max(v.M(idx), S);
-				key = ((unsigned long long) val << 32) | (0xffffffffu - t);   // ties: the lowest range (largest t) wins
+				key = (val << 16) | (0xffffu - t);
 			}
 		}
-		unsigned long long kmin = key;
-#pragma unroll
-		for (int o = 16; o > 0; o >>= 1)
-		{
-			unsigned long long const other = __shfl_xor_sync(FSQ_FULL, kmin, o);
-			kmin = other < kmin ? other : kmin;
-		}
+		uint32_t const kmin = __reduce_min_sync(FSQ_FULL, key);
 		if (kmin < best)
 		{
 			uint32_t const owner = __ffs(__ballot_sync(FSQ_FULL, key == kmin)) - 1;
@@ -199,9 +195,9 @@ __device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list
 	reach = max(reach, (uint32_t) t_out - far);
 	lowest = min(lowest, far);
 	uint32_t const whole = A.m - h.h0;          // == m when value 0 is absent
-	uint32_t const best_val = (uint32_t) (best >> 32);
+	uint32_t const best_val = best >> 16;
 	uint32_t lb = 0, mx = whole, sz = whole;
-	if (~0ull != best && best_val < whole) { lb = best_idx + L; mx = best_val; sz = best_S; }
+	if (0xffffffffu != best && best_val < whole) { lb = best_idx + L; mx = best_val; sz = best_S; }
 	if (0 == lane && !complete && mx > A.cap)
 		atomicMax(&A.flags[1], (uint32_t) (k + 1));
 	lb_out = lb; size_out = sz;

@@ -109,6 +109,7 @@ struct stitch_args
 	uint32_t const *item_begin;    // device array [n_ctas + 1]
 	uint32_t n_ctas;
 	uint32_t m, n_tiles;
+	uint32_t use_sort;             // m <= 1024: the one-sort formulation (stitch_sort_kernel)
 };
 
 size_t stitch_smem_bytes(uint32_t m, uint32_t n_warps);

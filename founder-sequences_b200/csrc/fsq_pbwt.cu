@@ -323,6 +323,128 @@ __global__ void __launch_bounds__(1024) stitch_kernel(stitch_args const A)
 	}
 }
 
+
+// ---- boundary stitch, small m: one sort instead of radix passes ---------------------------------------------------
+// The same composition for m <= 1024 rows with one row per thread: the incoming positions are sorted by
+// (class in the summary, incoming position) -- a bitonic network, in registers below 32 lanes apart and through shared
+// memory above -- and the divergence of a row that follows a row of its own class is the maximum of the incoming
+// divergences between the two incoming positions, read from a sparse table (two look-ups).  About a quarter of the
+// time of the radix formulation, which stays for larger m.
+__global__ void __launch_bounds__(1024) stitch_sort_kernel(stitch_args const A)
+{
+	extern __shared__ __align__(128) uint8_t smem_raw[];
+	__shared__ uint32_t wtot[32];
+	uint32_t const tid = threadIdx.x;
+	uint32_t const lane = tid & 31u, warp = tid >> 5;
+	uint32_t const p2 = blockDim.x;                        // power of two >= m, >= 32
+	uint32_t const m = A.m;
+	uint32_t levels = 1;                                   // sparse-table levels: spans of 2^l positions, 2^(levels - 1) <= m
+	while ((2u << (levels - 1)) <= m) ++levels;
+	uint32_t *ks0 = (uint32_t *) smem_raw;                 // [p2] exchange buffers of the sorting network
+	uint32_t *ks1 = ks0 + p2;                              // [p2]
+	uint32_t *st = ks1 + p2;                               // [levels][p2] range maxima of the incoming divergences
+	uint16_t *cls = (uint16_t *) (st + (size_t) levels * p2);      // [p2] class of a row id
+	uint16_t *sa = cls + p2;                               // [p2] incoming prefix array
+
+	uint32_t const step_end = A.item_begin[blockIdx.x + 1];
+	for (uint32_t step = A.item_begin[blockIdx.x]; step < step_end; ++step)
+	{
+		stitch_item const it = A.items[step];
+		uint32_t const s_mark = it.s_mark;
+		bool const live = tid < m;
+		// every global read of the item happens before its first write (outputs may alias the summary)
+		uint32_t const dl = live ? it.delta[tid] : 0u;
+		uint32_t const pi = live ? it.pi[tid] : 0u;
+		uint32_t const a_in = live ? (it.identity_in ? tid : it.in_a[tid]) : 0u;
+		uint32_t const d_in = live ? (it.identity_in ? it.identity_d : it.in_d[tid]) : 0u;
+		bool const start = live && (0 == tid || dl > s_mark);
+
+		// class of every row: inclusive count of class starts in summary order
+		uint32_t const bal = __ballot_sync(FSQ_FULL, start);
+		if (0 == lane) wtot[warp] = __popc(bal);
+		st[tid] = d_in;
+		if (live) sa[tid] = (uint16_t) a_in;
+		__syncthreads();
+		{
+			uint32_t const w = lane < (p2 >> 5) ? wtot[lane] : 0u;
+			uint32_t const incl = warp_incl_sum(w);
+			uint32_t const before = __shfl_sync(FSQ_FULL, incl - w, warp);
+			uint32_t const c = before + __popc(bal & (0xffffffffu >> (31u - lane)));      // >= 1 for every live row
+			if (live) cls[pi] = (uint16_t) (c - 1);
+		}
+		__syncthreads();
+
+		// sparse table over the incoming divergences (positions past m hold 0)
+		for (uint32_t l = 1; l < levels; ++l)
+		{
+			uint32_t const half = 1u << (l - 1);
+			uint32_t const x = st[(size_t) (l - 1) * p2 + tid];
+			uint32_t const y = tid + half < p2 ? st[(size_t) (l - 1) * p2 + tid + half] : 0u;
+			st[(size_t) l * p2 + tid] = max(x, y);
+			__syncthreads();
+		}
+
+		// sort by (class, incoming position); padding keys sort last
+		uint32_t key = live ? (((uint32_t) cls[a_in] << 16) | tid) : 0xffffffffu;
+		uint32_t flip = 0;
+		for (uint32_t k = 2; k <= p2; k <<= 1)
+			for (uint32_t j = k >> 1; j > 0; j >>= 1)
+			{
+				uint32_t other;
+				if (j >= 32)
+				{
+					uint32_t *buf = flip ? ks1 : ks0;
+					flip ^= 1u;
+					buf[tid] = key;
+					__syncthreads();
+					other = buf[tid ^ j];
+				}
+				else
+					other = __shfl_xor_sync(FSQ_FULL, key, j);
+				bool const keep_min = (0 == (tid & j)) == (0 == (tid & k));
+				key = keep_min ? min(key, other) : max(key, other);
+			}
+		uint32_t *buf = flip ? ks1 : ks0;
+		buf[tid] = key;
+		__syncthreads();
+
+		if (live)
+		{
+			uint32_t const i = key & 0xffffu;
+			uint32_t od = dl;
+			if (!start)
+			{
+				uint32_t const ip = buf[tid - 1] & 0xffffu;      // the row before in the same class: ip < i
+				uint32_t const len = i - ip;                      // max over incoming positions ip + 1 .. i
+				uint32_t const l = 31u - __clz(len);
+				od = max(st[(size_t) l * p2 + ip + 1], st[(size_t) l * p2 + i + 1 - (1u << l)]);
+			}
+			it.out_a[tid] = sa[i];
+			it.out_d[tid] = od;
+		}
+		__syncthreads();
+		__threadfence();
+	}
+}
+
+size_t stitch_sort_smem_bytes(uint32_t m, uint32_t p2)
+{
+	uint32_t levels = 1;
+	while ((2u << (levels - 1)) <= m) ++levels;
+	return (size_t) p2 * 4 * (2 + levels) + (size_t) p2 * 2 * 2;
+}
+
+static cudaError_t launch_stitch_sort(stitch_args const &A, cudaStream_t st)
+{
+	uint32_t p2 = 32;
+	while (p2 < A.m) p2 <<= 1;
+	size_t const smem = stitch_sort_smem_bytes(A.m, p2);
+	cudaError_t err = cudaFuncSetAttribute(stitch_sort_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+	if (cudaSuccess != err) return err;
+	stitch_sort_kernel <<<A.n_ctas, p2, smem, st>>>(A);
+	return cudaGetLastError();
+}
+
 size_t stitch_smem_bytes(uint32_t m, uint32_t n_warps)
 {
 	auto r16 = [](size_t b) { return (b + 15) & ~size_t(15); };
@@ -342,6 +464,7 @@ static cudaError_t launch_stitch_t(stitch_args const &A, uint32_t n_warps, cudaS
 
 cudaError_t launch_stitch(stitch_args const &A, cudaStream_t st)
 {
+	if (A.use_sort && A.m <= 1024) return launch_stitch_sort(A, st);
 	uint32_t const n_warps = A.n_tiles < 32 ? A.n_tiles : 32;
 	uint32_t const tpw = (A.n_tiles + n_warps - 1) / n_warps;
 #define FSQ_CASE(T) if (tpw <= T) return launch_stitch_t <T>(A, n_warps, st);

@@ -218,6 +218,18 @@ def test_states_invariant_under_stitch_grouping(ctx, oracle, synth, G):
     check_states(ctx, oracle, rows, 12, columns=np.arange(1, 501, 7))
 
 
+@pytest.mark.parametrize("sort,m", [(0, 130), (1, 130), (1, 33), (1, 1000), (0, 1000), (1, 1024), (1, 1025)])
+def test_states_invariant_under_stitch_kernel(ctx, oracle, synth, sort, m):
+    """The boundary stitch has two formulations (one sort with a sparse table for m <= 1024, radix passes otherwise)."""
+    rows = synth.synth_rows(m, 420, seed=31 + m, founders=11, gaps=True, recomb_block=37, mu=0.01)
+    ctx.set_option("stitch_sort", sort)
+    ctx.set_option("block_columns", 30)
+    try:
+        check_states(ctx, oracle, rows, 12, columns=np.arange(1, 421, 11))
+    finally:
+        ctx.set_option("stitch_sort", 1)
+
+
 @pytest.mark.parametrize("chunks,max_rounds", [(1, 12), (3, 12), (0, 12), (1000, 12), (1000, 2)])
 def test_segmentation_invariant_under_dp_chaining(ctx, oracle, synth, chunks, max_rounds):
     """The DP table is cut into chains that run at once and repeat until a round changes nothing; one chain, many chains
