@@ -144,6 +144,7 @@ def main():
     ap.add_argument("--block-columns", type=int, default=0)
     ap.add_argument("--warps", type=int, default=0)
     ap.add_argument("--cap", type=int, default=0)
+    ap.add_argument("--opt", action="append", default=[], help="library option key=value (experiments)")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -231,6 +232,9 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
         ctx.set_option("warps", args.warps)
     if args.cap:
         ctx.set_option("cap", args.cap)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        ctx.set_option(k, int(v))
     sharded = None
     comm = None
     n_total = n * world
@@ -255,12 +259,12 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             return info
         eng = sharded.GpuShard(ctx, msa, rank * n, n_total, L)
         try:
-            res = sharded.segment_sharded(eng, comm, want_states=False, want_traceback=False)
+            res = sharded.segment_sharded(eng, comm, want_states=False, want_traceback=False, want_bounds=False)
         finally:
             eng.close()
         if getattr(res, "trace", None) and rank == 0:
             sys.stderr.write("shard trace (rank 0, ms): " + ", ".join("%s %.3f" % kv for kv in res.trace) + "\n")
-        return (res.K, len(res.lb))
+        return (res.K, res.count)
 
     sampler = ClockSampler(dev)
     sampler.start()

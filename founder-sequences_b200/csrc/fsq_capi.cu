@@ -898,6 +898,7 @@ int shard_reduce(fsq_shard *P)
 	pr.stop();
 	CK(cudaStreamSynchronize(ctx->stream));
 	P->red_lb.clear(); P->red_rb.clear(); P->red_size.clear(); P->red_pos.clear();
+	P->red_lb.reserve(T); P->red_rb.reserve(T); P->red_size.reserve(T); P->red_pos.reserve(T);
 	uint64_t cur_lb = 0;
 	for (uint32_t u = 0; u < T; )
 	{

@@ -58,16 +58,25 @@ __device__ __forceinline__ float onehot(float a, float b)
 	return r;
 }
 
-// When a != b: one count moves from the histogram cell at `from` to the one at `to` (shared-window byte addresses).
-__device__ __forceinline__ void hist_move_if_ne(float a, float b, uint32_t to, uint32_t from)
+// When a != b: one count moves from the histogram cell of code word `from` to that of `to` (cells are 32 bits wide at
+// base + 4 code).  One branch around both updates, with the address arithmetic inside it: ptxas turns a predicated
+// red.shared into a branch region of its own, which costs nine instructions per element even when nothing changes.
+__device__ __forceinline__ void hist_move_if_ne(float a, float b, uint32_t to, uint32_t from, uint32_t base)
 {
 	asm volatile(
 		"{\n"
 		".reg .pred q;\n"
+		".reg .b32 t0, t1;\n"
 		"setp.ne.f32 q, %0, %1;\n"
-		"@q red.shared.add.u32 [%2], 1;\n"
-		"@q red.shared.add.u32 [%3], -1;\n"
-		"}\n" :: "f"(a), "f"(b), "r"(to), "r"(from) : "memory");
+		"@!q bra SKIP;\n"
+		"shl.b32 t0, %2, 2;\n"
+		"shl.b32 t1, %3, 2;\n"
+		"add.u32 t0, t0, %4;\n"
+		"add.u32 t1, t1, %4;\n"
+		"red.shared.add.u32 [t0], 1;\n"
+		"red.shared.add.u32 [t1], -1;\n"
+		"SKIP:\n"
+		"}\n" :: "f"(a), "f"(b), "r"(to), "r"(from), "r"(base) : "memory");
 }
 
 // bytes (a2, a3, b2, b3) -> result bytes 0..3: the high half of a under the high half of b
@@ -234,7 +243,7 @@ __device__ __forceinline__ void column_step_chunked(
 		{
 			// one count moves from the old code to the new one; 4 (0x4B000000 + c) = 0x2C000000 + 4 c (mod 2^32)
 			uint32_t const Hb = H - 0x2C000000u;
-			hist_move_if_ne(out, dvf, ob * 4u + Hb, db * 4u + Hb);
+			hist_move_if_ne(out, dvf, ob, db, Hb);
 		}
 	}
 

@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 	// computed every entry from values that are final: flags[3] counts the chains for which this cannot be said.
 	uint32_t const tail_from = t_end > A.reach_bound ? t_end - A.reach_bound : 0u;
 	uint32_t lowest = 0xffffffffu;
-	bool unsettled = false;
+	bool unsettled = false, changed = false;      // published once per warp at the end (a store per entry would pile up on one address)
 
 	table_ring v;
 	v.g.Mg = A.tb_max; v.g.mkg = A.mk; v.g.levg = A.lev; v.g.n_blk = A.n_blk;
@@ -289,7 +289,7 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 				A.tb_max[t] = mx;
 				A.tb_lb[t] = lb;
 				A.tb_size[t] = sz;
-				if (cur.old_max != mx) { A.flags[0] = 1; unsettled |= t >= tail_from; }
+				if (cur.old_max != mx) { changed = true; unsettled |= t >= tail_from; }
 				sM[t & (DP_RING - 1)] = mx;       // this slot's previous tenant is older than anything the wavefront reads from the ring
 			}
 		}
@@ -303,7 +303,7 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 			{
 				smk[t & (DP_RING - 1)] = msk;
 				A.mk[t] = msk;
-				if (cur.old_mask != msk) { A.flags[0] = 1; unsettled |= t >= tail_from; }
+				if (cur.old_mask != msk) { changed = true; unsettled |= t >= tail_from; }
 			}
 		}
 		__syncthreads();
@@ -314,7 +314,7 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 				uint32_t const b = (t1 >> 6) - 1;
 				uint32_t const smp0 = 64 * b + (uint32_t) __ffsll((long long) v.mask(64 * b + 63)) - 1u;      // leftmost minimal entry of the block
 				uint32_t const val0 = v.M(smp0);
-				if (pend_old != pend_new) { A.flags[0] = 1; unsettled = true; }
+				if (pend_old != pend_new) { changed = true; unsettled = true; }
 				pend_old = pend_new = 0;
 				// lev[p][b + 1 - 2^p] from lev[p - 1][b + 1 - 2^p], which an earlier block's completion wrote: independent across p
 				uint32_t const p = lane;
@@ -336,7 +336,8 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 			__syncthreads();
 		}
 	}
-	if (0 == warp && pend_old != pend_new) { A.flags[0] = 1; unsettled = true; }
+	if (0 == warp && pend_old != pend_new) { changed = true; unsettled = true; }
+	if (__any_sync(FSQ_FULL, changed) && 0 == lane) A.flags[0] = 1;
 	if (0 == lane && reach) atomicMax(&A.flags[2], reach);
 	// reads below the own entries must stay inside the window the chains before this one watch
 	if (0xffffffffu != lowest && lowest < t_begin && t_begin - lowest > A.reach_bound) unsettled = true;

@@ -255,6 +255,7 @@ class ShardedResult:
 
     def __init__(self):
         self.K = 0
+        self.count = 0                 # reduced segments
         self.traceback = None          # (lb, rb, max, size), replicated
         self.lb = self.rb = self.size = None
         self.own = (0, 0)              # reduced segments [first, last) held here
@@ -279,7 +280,7 @@ def entry_range(c0, c1, n, L):
     return first, last
 
 
-def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=True, want_traceback=True):
+def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=True, want_traceback=True, want_bounds=True):
     """Run the long path over the column shards held by the ranks of `comm`; `engine` is this rank's shard.
     Raises NotReducible when K == m (generate_context.cc:192-200)."""
     res = ShardedResult()
@@ -372,7 +373,9 @@ def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=Tru
     mark("lists exchange")
     count, own_seg = engine.reduce()
     mark("reduce")
-    res.lb, res.rb, res.size = engine.bounds(count)
+    res.count = count
+    if want_bounds:
+        res.lb, res.rb, res.size = engine.bounds(count)
     res.own = own_seg
     if want_states:
         res.a, res.d = engine.states(own_seg)
