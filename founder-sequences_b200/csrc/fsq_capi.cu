@@ -301,6 +301,7 @@ void fill_common(block_args &A, fsq_msa const *msa, geometry const &g)
 	A.sym0 = g.sym0;
 	A.C = g.C;
 	A.cg = g.cg;
+	A.magic = 0x4B000000u;
 }
 
 __global__ void iota_kernel(uint32_t *a, uint32_t *d, uint32_t m, uint32_t dval)

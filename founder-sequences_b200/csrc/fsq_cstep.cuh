@@ -92,9 +92,14 @@ struct cstep_shared
 	uint32_t st;        // shared-window byte address of the packed state [T E]
 	uint32_t tb;        // ... of the per-thread bucket table [T][NSP]: byte address of the thread's next slot per symbol
 	uint32_t *wx;       // [W][2 NS] per-warp totals and (after-value | has << 16), W > 1 only
+	uint32_t magic;     // 0x4B000000 from a kernel argument (see column_step_chunked)
 };
 
-constexpr int cstep_nsp(int NS) { return NS | 1; }     // odd row length: conflict-free table rows
+// The column's symbols reach the step as u = 6 s (one byte per row): u is the counter shift as it stands, and u & ~3
+// (0, 4, 12, 16, 24, 28, 36, 40 for s = 0 .. 7: distinct and word-aligned) is the symbol's byte offset in the thread's
+// bucket-table row, so neither needs arithmetic per element.
+constexpr int cstep_tb_off(int c) { return (6 * c) & ~3; }
+constexpr int cstep_nsp(int NS) { return (cstep_tb_off(NS - 1) / 4 + 1) | 1; }     // words per table row, odd: conflict-free
 
 // Bit-field counters, 6 bits per symbol (E <= 63).
 template <int NS, bool WIDE = (NS * 6 > 32)> struct chunk_counters;
@@ -102,11 +107,10 @@ template <int NS, bool WIDE = (NS * 6 > 32)> struct chunk_counters;
 template <int NS> struct chunk_counters <NS, false>
 {
 	uint32_t v{0};
-	__device__ __forceinline__ uint32_t bump(uint32_t s)
+	__device__ __forceinline__ uint32_t bump(uint32_t u)       // u = 6 s
 	{
-		uint32_t const sh = s * 6u;
-		uint32_t const r = (v >> sh) & 63u;
-		v += 1u << sh;
+		uint32_t const r = (v >> u) & 63u;
+		v += 1u << u;
 		return r;
 	}
 	__device__ __forceinline__ uint32_t field(int c) const { return (v >> (c * 6)) & 63u; }
@@ -115,10 +119,10 @@ template <int NS> struct chunk_counters <NS, false>
 template <int NS> struct chunk_counters <NS, true>
 {
 	uint32_t lo{0}, hi{0};      // symbols 0..4 and 5..
-	__device__ __forceinline__ uint32_t bump(uint32_t s)
+	__device__ __forceinline__ uint32_t bump(uint32_t u)       // u = 6 s
 	{
-		bool const up = s >= 5u;
-		uint32_t const sh = (up ? s - 5u : s) * 6u;
+		bool const up = u >= 30u;
+		uint32_t const sh = up ? u - 30u : u;
 		uint32_t const one = 1u << sh;
 		uint32_t const r = ((up ? hi : lo) >> sh) & 63u;
 		lo += up ? 0u : one;
@@ -187,9 +191,9 @@ __device__ __forceinline__ void lane_scans(
 	}
 }
 
-// The step.  NS symbols (0 .. NS - 1 as found in sym8, already offset by the smallest symbol that occurs), E elements per
-// thread, blockDim.x threads.  sym8: shared-window byte address of this column's symbols, one byte per row id (and
-// NS - 1 for the padding ids).  HIST: maintain the divergence-code histogram H (32-bit counters).
+// The step.  NS symbols s = 0 .. NS - 1 (already offset by the smallest symbol that occurs), E elements per thread,
+// blockDim.x threads.  sym8: shared-window byte address of this column's symbols as u = 6 s, one byte per row id
+// (and 6 (NS - 1) for the padding ids).  HIST: maintain the divergence-code histogram H (32-bit counters).
 template <int E, int NS, bool HIST>
 __device__ __forceinline__ void column_step_chunked(
 	cstep_shared const &sh,
@@ -208,8 +212,11 @@ __device__ __forceinline__ void column_step_chunked(
 	uint32_t const mytb = sh.tb + tid * (NSP * 4u);
 
 	uint32_t wd[E];     // row id | out << 16
-	uint32_t mt[E];     // sym * 4 | local rank << 8
-	uint32_t const magic = 0x4B000000u;
+	uint32_t mt[E];     // u | local rank << 8
+	// 0x4B00hhll is the float 2^23 + code.  The maxima live in that biased form (0 = "nothing seen": below every
+	// biased value), so a code goes in with one PRMT and comes out with none.  The constant comes from a kernel argument:
+	// as a literal, ptxas gives it the PRMT's immediate slot and re-materialises the selector in a register per element.
+	uint32_t const magic = sh.magic;
 
 	// ---- phase 1: walk the chunk -------------------------------------------------------------------------------
 	chunk_counters <NS> cnt;
@@ -222,23 +229,23 @@ __device__ __forceinline__ void column_step_chunked(
 	{
 		uint32_t const w = lds32(mine + 4u * j);
 		uint32_t const x = w & 0xffffu;
-		uint32_t const s = lds8(sym8 + x);
-		uint32_t const db = prmt_7632(w, magic);                     // 0x4B00hhll: the float 2^23 + code
-		float const dvf = __uint_as_float(db) - 8388608.0f;
-		float const sf = (float) s;
-		uint32_t const lr = cnt.bump(s);
+		uint32_t const u = lds8(sym8 + x);                           // 6 s
+		uint32_t const db = prmt_7632(w, magic);                     // 0x4B00hhll
+		float const dvf = __uint_as_float(db);
+		float const uf = (float) u;
+		uint32_t const lr = cnt.bump(u);
 		float out = 0.0f;
 #pragma unroll
 		for (int c = 0; c < NS; ++c)
 		{
-			float const oh = onehot(sf, (float) c);
+			float const oh = onehot(uf, (float) (6 * c));
 			float const nm = fmaxf(rm[c], dvf);
 			out = fmaf(nm, oh, out);
 			rm[c] = fmaf(-nm, oh, nm);
 		}
-		uint32_t const ob = __float_as_uint(out + 8388608.0f);      // 0x4B00hhll
+		uint32_t const ob = __float_as_uint(out);                    // 0x4B00hhll
 		wd[j] = __byte_perm(w, ob, 0x5410);
-		mt[j] = lr * 256u + s * 4u;
+		mt[j] = lr * 256u + u;
 		if (HIST)
 		{
 			// one count moves from the old code to the new one; 4 (0x4B000000 + c) = 0x2C000000 + 4 c (mod 2^32)
@@ -254,7 +261,7 @@ __device__ __forceinline__ void column_step_chunked(
 		for (int c = 0; c < NS; ++c)
 		{
 			n[c] = cnt.field(c);
-			af[c] = __float_as_uint(rm[c] + 8388608.0f) & 0xffffu;
+			af[c] = __float_as_uint(fmaxf(rm[c], 8388608.0f)) & 0xffffu;      // 0 when nothing was seen
 		}
 	}
 	uint32_t ex[NS], tot[NS], pv[NS], wkey[NS], nohas;
@@ -309,7 +316,7 @@ __device__ __forceinline__ void column_step_chunked(
 		{
 			slot[c] = sh.st + 4u * (base + wex[c] + ex[c]);
 			cin[c] = ((nohas >> c) & 1u) ? max(pv[c], wcin[c]) : pv[c];
-			sts32(mytb + 4u * c, slot[c]);
+			sts32(mytb + (uint32_t) cstep_tb_off(c), slot[c]);
 			base += tot[c];
 		}
 	}

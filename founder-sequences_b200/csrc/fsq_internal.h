@@ -24,6 +24,7 @@ struct block_args
 	uint32_t C;                // columns per block
 	uint32_t cg;               // columns per TMA stage
 	uint32_t first_block;
+	uint32_t magic;            // 0x4B000000, passed as an argument so that the step's PRMT reads it from the constant bank
 	int mode;
 
 	// start states (MODE_EXACT, MODE_DUMP)
@@ -82,7 +83,7 @@ inline size_t cblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uin
 	t += r16(2 * sizeof(uint64_t));
 	t += r16((size_t) A.cg * ((words + 15) & ~size_t(15)));
 	t += r16(sizeof(uint32_t) * words);
-	t += r16(sizeof(uint32_t) * (size_t) T * (NS | 1));
+	t += r16(sizeof(uint32_t) * (size_t) T * ((((6 * (NS - 1)) & ~3u) / 4 + 1) | 1));      // cstep_nsp(NS), fsq_cstep.cuh
 	t += r16(sizeof(uint32_t) * n_warps * 2 * NS);
 	if (hist) t += r16(sizeof(uint32_t) * ((size_t) A.m + A.C + 8));
 	return t;
