@@ -221,6 +221,8 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
     if world > 1:
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # the version banner goes to stdout, which carries the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     dev = local_rank

@@ -637,6 +637,8 @@ struct fsq_shard
 			// what this rank's chains can read: its own entries and the look-back before them (twice the bound, for slack)
 			uint64_t const back = 2 * (uint64_t) reach_known + 128;
 			D.w_first = (uint32_t) ((t_first > back ? t_first - back : 0) & ~63ull);
+			D.w_last = n_entries;
+			if (c1 != n) D.w_last = (uint32_t) std::min <uint64_t>(n_entries, t_last);      // nothing this rank reads lies past its own entries
 		}
 		return D;
 	}

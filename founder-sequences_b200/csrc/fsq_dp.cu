@@ -436,12 +436,13 @@ __global__ void dp_raise_kernel(dp_args const A)
 	if (A.tb_max[t] < lvl) A.tb_max[t] = lvl;
 }
 
-// Masks and rmq cells are rebuilt from A.w_first on (a multiple of 64): a column-sharded rank reads the table only
-// from its own entries back to the look-back bound, and a chain that reads below that bound asks for another round.
+// Masks and rmq cells are rebuilt for entries [A.w_first, A.w_last) (w_first a multiple of 64): a column-sharded rank
+// reads the table only from its own last entry back to the look-back bound before its first, and a chain that reads
+// below that bound asks for another round.
 __global__ void dp_masks_kernel(dp_args const A)
 {
 	uint32_t const t = A.w_first + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-	if (t >= A.n_entries) return;
+	if (t >= A.w_last) return;
 	table_global v;
 	v.Mg = A.tb_max; v.mkg = A.mk; v.levg = A.lev; v.n_blk = A.n_blk;
 	unsigned long long const msk = make_mask(v, t);
@@ -452,7 +453,7 @@ __global__ void dp_masks_kernel(dp_args const A)
 __global__ void dp_levels_kernel(dp_args const A, uint32_t p)
 {
 	uint32_t const i = A.w_first / 64 + blockIdx.x * blockDim.x + threadIdx.x;
-	uint32_t const n_complete = A.n_entries / 64;
+	uint32_t const n_complete = A.w_last / 64;
 	uint64_t const b = (uint64_t) i + (1ull << p) - 1;       // the block whose completion defines lev[p][i]
 	if (b >= n_complete) return;
 	uint32_t const smp0 = 64 * (uint32_t) b + (uint32_t) __ffsll((long long) A.mk[64 * b + 63]) - 1u;
@@ -475,10 +476,10 @@ cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st)
 // other ranks' entries.
 cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st)
 {
-	if (A.w_first >= A.n_entries) return cudaSuccess;
-	uint32_t const span = A.n_entries - A.w_first;
+	if (A.w_first >= A.w_last) return cudaSuccess;
+	uint32_t const span = A.w_last - A.w_first;
 	dp_masks_kernel <<<(span + 7) / 8, 256, 0, st>>>(A);
-	uint32_t const n_complete = A.n_entries / 64;
+	uint32_t const n_complete = A.w_last / 64;
 	uint32_t const first_blk = A.w_first / 64;
 	for (uint32_t p = 0; p < A.n_levels && (1ull << p) <= n_complete && first_blk < n_complete; ++p)
 		dp_levels_kernel <<<(n_complete - first_blk + 255) / 256, 256, 0, st>>>(A, p);

@@ -137,7 +137,7 @@ struct dp_args
 	                            // [2] the farthest any column looked back in the table (entries), over all rounds
 	                            // [3] chains of this round whose result a later chain may have read half-way (see dp_chain_kernel)
 	uint32_t reach_bound;       // the look-back known when the round starts (0 in the first round)
-	uint32_t w_first;           // masks and rmq cells are rebuilt for entries >= w_first (a multiple of 64)
+	uint32_t w_first, w_last;   // masks and rmq cells are rebuilt for entries [w_first, w_last) (w_first a multiple of 64)
 };
 
 cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st);       // every chain once, against the table as it stands

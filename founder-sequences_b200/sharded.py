@@ -46,6 +46,11 @@ class TorchComm:
         self.dist.all_gather(out, tensor, group=self.group)
         return out
 
+    def fence(self, device):
+        """The engine launches on its own stream: what a collective wrote must have landed before the next stage."""
+        if getattr(device, "type", "cpu") == "cuda":
+            torch.cuda.synchronize(device)
+
     def max(self, value, device):
         t = torch.tensor([int(value)], dtype=torch.int64, device=device)
         self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
@@ -109,6 +114,9 @@ class ThreadComm:
             torch.cuda.synchronize(tensor.device)
         self.sh.barrier.wait()
         return out
+
+    def fence(self, device):
+        pass        # broadcast / all_gather above synchronise the device themselves
 
     def max(self, value, device):
         return max(int(v) for v in self._exchange(int(value)))
@@ -269,6 +277,8 @@ def _exchange_slices(comm, tensors, ranges):
     for src, (f, l) in enumerate(ranges):
         for t in tensors:
             comm.broadcast(t[f:l], src)
+    if tensors:
+        comm.fence(tensors[0].device)
 
 
 def entry_range(c0, c1, n, L):
@@ -325,6 +335,7 @@ def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=Tru
                     if r == comm.rank:
                         engine.dp_round()
                     comm.broadcast(tabs[0][ranges[r][0]: ranges[r][1]], r)
+                    comm.fence(dev)
                     engine.dp_sync(False, 0)
                 rounds += 1
                 break
