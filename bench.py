@@ -218,7 +218,12 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
         return 1
 
     dist = None
+    saved_stdout = None
     if world > 1:
+        # stdout carries the one JSON line: whatever the libraries print while the ranks run (the NCCL banner) goes to stderr
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
@@ -373,7 +378,11 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
         nc = sample_columns(m, True)
         rows = make_rows_sample(np, torch, fsq, m, nc, seed, founders, gaps, True)
         line["cpu_baseline"] = cpu_baseline(rows, L, use_ref)
+    if saved_stdout is not None:
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
     print(json.dumps(line))
+    sys.stdout.flush()
     msa.free()
     ctx.close()
     if dist is not None:

@@ -273,10 +273,20 @@ class ShardedResult:
 
 
 def _exchange_slices(comm, tensors, ranges):
-    """Every rank sends its own slice [first, last) of each tensor to all others; ranges: per rank, from gather_objects."""
-    for src, (f, l) in enumerate(ranges):
-        for t in tensors:
-            comm.broadcast(t[f:l], src)
+    """Every rank sends its own slice [first, last) of each tensor to all others (ranges: per rank).  One all-gather
+    per tensor over slices padded to the longest one -- a broadcast per rank costs a collective launch per rank and
+    adds up the ranks' skew -- then the received slices are copied into place."""
+    width = max(l - f for f, l in ranges)
+    if width == 0:
+        return
+    for t in tensors:
+        f, l = ranges[comm.rank]
+        send = torch.zeros(width, dtype=t.dtype, device=t.device)
+        send[: l - f] = t[f:l]
+        got = comm.all_gather(send)
+        for src, (f, l) in enumerate(ranges):
+            if src != comm.rank and l > f:
+                t[f:l] = got[src][: l - f]
     if tensors:
         comm.fence(tensors[0].device)
 
