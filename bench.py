@@ -41,62 +41,109 @@ WORKLOADS = {
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    """SM clock and clock-event (throttle) reasons DURING the timed region (B200_PROFILING.md's clocks line).  Sampled
+    in-process through NVML every 200 ms: an `nvidia-smi -lms` process beside the run was measured to stall this
+    process's launches by ~9 ms per sample (a 10 % error on a 9 ms step); `--clock-sampler smi` keeps that variant."""
 
-    def __init__(self, index):
-        self.index = index
+    REASONS = [("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)]
+
+    def __init__(self, index, kind="nvml", period=0.2):
+        self.index, self.kind, self.period = index, kind, period
         self.proc = None
-        self.lines = []
+        self.nvml = None
+        self.lines = []          # (time, sm_mhz, max_mhz, [reasons])
+        self.stop_flag = threading.Event()
+        self.thread = None
 
     def start(self):
+        if self.kind == "none":
+            return
+        if self.kind == "nvml":
+            try:
+                import pynvml
+                pynvml.nvmlInit()
+                self.nvml = pynvml
+                self.handle = self._nvml_handle(pynvml)
+                self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+                self._sample_nvml()
+                self.thread = threading.Thread(target=self._loop_nvml, daemon=True)
+                self.thread.start()
+                return
+            except Exception:
+                self.nvml = None
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "200"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread = threading.Thread(target=self._read_smi, daemon=True)
             self.thread.start()
         except OSError:
             self.proc = None
 
-    def _read(self):
+    def _nvml_handle(self, pynvml):
+        # the visible device `index` of this process: CUDA_VISIBLE_DEVICES may renumber
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            ids = [x.strip() for x in vis.split(",") if x.strip()]
+            if self.index < len(ids):
+                if ids[self.index].isdigit():
+                    return pynvml.nvmlDeviceGetHandleByIndex(int(ids[self.index]))
+                return pynvml.nvmlDeviceGetHandleByUUID(ids[self.index])
+        return pynvml.nvmlDeviceGetHandleByIndex(self.index)
+
+    def _sample_nvml(self):
+        p = self.nvml
+        sm = float(p.nvmlDeviceGetClockInfo(self.handle, p.NVML_CLOCK_SM))
+        try:
+            mask = int(p.nvmlDeviceGetCurrentClocksEventReasons(self.handle))
+        except Exception:
+            mask = int(p.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+        self.lines.append((time.perf_counter(), sm, self.max_mhz, [n for n, bit in self.REASONS if mask & bit]))
+
+    def _loop_nvml(self):
+        while not self.stop_flag.wait(self.period):
+            try:
+                self._sample_nvml()
+            except Exception:
+                return
+
+    def _read_smi(self):
         for line in self.proc.stdout:
-            self.lines.append((time.perf_counter(), line.strip()))
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm, mx = float(f[0]), float(f[1])
+            except ValueError:
+                continue
+            names = [n for n, _ in self.REASONS]
+            self.lines.append((time.perf_counter(), sm, mx, [n for n, v in zip(names, f[2:6]) if v.lower().startswith("active")]))
 
     def window(self, t0, t1):
         """Keep the samples taken inside the timed region (the sampler is started before the warm-up so that its own
         start-up does not fall into the region); if the region was shorter than the sampling period, the nearest ones."""
-        inside = [ln for t, ln in self.lines if t0 <= t <= t1]
+        inside = [ln for ln in self.lines if t0 <= ln[0] <= t1]
         if not inside and self.lines:
             mid = 0.5 * (t0 + t1)
-            inside = [min(self.lines, key=lambda x: abs(x[0] - mid))[1]]
+            inside = [min(self.lines, key=lambda x: abs(x[0] - mid))]
         self.lines = inside
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-        sm, mx, reasons = [], None, set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            if isinstance(ln, tuple):
-                ln = ln[1]
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 6:
-                continue
+        self.stop_flag.set()
+        if self.proc:
+            self.proc.terminate()
             try:
-                sm.append(float(f[0]))
-                mx = float(f[1])
-            except ValueError:
-                continue
-            for nm, v in zip(names, f[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(nm)
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+        if not self.lines:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no clock samples (%s)" % self.kind]}
+        sm = sorted(ln[1] for ln in self.lines)
+        reasons = set()
+        for ln in self.lines:
+            reasons.update(ln[3])
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.lines[-1][2], "reasons": sorted(reasons), "samples": len(sm),
+                "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 def measured_peak():
@@ -144,6 +191,7 @@ def main():
     ap.add_argument("--block-columns", type=int, default=0)
     ap.add_argument("--warps", type=int, default=0)
     ap.add_argument("--cap", type=int, default=0)
+    ap.add_argument("--clock-sampler", default="nvml", choices=["nvml", "smi", "none"])
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (experiments)")
     args = ap.parse_args()
 
@@ -271,9 +319,10 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             eng.close()
         if getattr(res, "trace", None) and rank == 0:
             sys.stderr.write("shard trace (rank 0, ms): " + ", ".join("%s %.3f" % kv for kv in res.trace) + "\n")
+            sys.stderr.write("host ms (accumulated): " + ", ".join("%s %.3f" % (k, ctx.stat("hms_" + k)) for k in ("traceback", "traceback_copy", "reduce", "reduce_walk", "reduced_states")) + "\n")
         return (res.K, res.count)
 
-    sampler = ClockSampler(dev)
+    sampler = ClockSampler(dev, args.clock_sampler)
     sampler.start()
     for _ in range(args.warmup):
         info = step()

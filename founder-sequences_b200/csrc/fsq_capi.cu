@@ -7,6 +7,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <chrono>
 #include <map>
 #include <new>
 #include <string>
@@ -97,8 +98,9 @@ struct fsq_segmentation
 	uint32_t *d_a{}, *d_d{};                  // reduced states on the device, count x m
 	uint32_t *h_a{}, *h_d{};                  // pinned host copies, made on first request
 	size_t d_bytes[2]{}, h_bytes[2]{};        // sizes of those blocks in the context's workspace cache
-	std::vector <uint64_t> tb_lb, tb_rb;      // traceback before reduction
-	std::vector <uint32_t> tb_max, tb_size;
+	void *h_tb{};                             // traceback before reduction, pinned: rb u64[T], then lb, max, size u32[T] each
+	size_t h_tb_bytes{};
+	uint32_t T{};
 	std::vector <uint32_t> dp_lb, dp_max, dp_size;   // keep_dp
 };
 
@@ -150,6 +152,14 @@ struct phase
 		cudaEventRecord(e1, ctx->stream);
 		ctx->pending.push_back({name, {e0, e1}});
 	}
+};
+
+// Host-side stopwatch for the stages whose time is not kernels (statistic "hms_<name>", milliseconds, accumulated).
+struct host_watch
+{
+	fsq_ctx *ctx; char const *name; std::chrono::steady_clock::time_point t0;
+	host_watch(fsq_ctx *c, char const *n): ctx(c), name(n), t0(std::chrono::steady_clock::now()) {}
+	~host_watch() { ctx->stats[std::string("hms_") + name] += std::chrono::duration <double, std::milli>(std::chrono::steady_clock::now() - t0).count(); }
 };
 
 void flush_phases(fsq_ctx *ctx)
@@ -322,7 +332,7 @@ __global__ void gather_states_kernel(uint32_t const *src_a, uint32_t const *src_
 	}
 }
 
-// States kept by pass B (packed row | code << 16, one row of `stride` words per column) -> (a, d) at the given right
+// States kept by pass B (packed row | code << 16, one row of `stride` words per column) -> (a, d) at the given (global) right
 // bounds: the state before column rb is the one stored after column rb - 1; its codes are relative to that column's block.
 __global__ void gather_stored_states_kernel(
 	uint32_t const *states, uint64_t stride, uint64_t const *rbs, uint32_t m, uint32_t C, uint64_t col0,
@@ -332,7 +342,7 @@ __global__ void gather_stored_states_kernel(
 	uint32_t const t = blockIdx.x;                 // grid.x: up to 2^31 - 1 positions
 	uint32_t const i = blockIdx.y * blockDim.x + threadIdx.x;
 	if (i >= m) return;
-	uint64_t const k = rbs[t] - 1;                 // local column whose output state this is
+	uint64_t const k = rbs[t] - col0 - 1;          // local column whose output state this is (rbs are global right bounds)
 	uint32_t const b = (uint32_t) (k / C);
 	uint32_t const r = R[b];
 	uint32_t const w = states[k * stride + i];
@@ -610,13 +620,16 @@ struct fsq_shard
 	// traceback (replicated) and reduction
 	uint32_t T{}, K{};
 	dbuf tr_lb, tr_rb, tr_max, tr_size, lists, d_next, d_nsize;
-	std::vector <uint64_t> tb_lb_h, tb_rb_h;
-	std::vector <uint32_t> tb_max_h, tb_size_h;
+	hbuf h_tb;                                 // the traceback on the host (pinned): rb u64[T], then lb, max, size u32[T] each
 	uint32_t pos_first{}, pos_last{};          // traceback positions whose right bound this rank holds the state of
 	std::vector <uint64_t> red_lb, red_rb;
 	std::vector <uint32_t> red_size, red_pos;  // reduced segments; red_pos: index into the traceback
 	uint32_t seg_first{}, seg_last{};          // reduced segments whose state this rank holds
+	uint32_t n_reduced{};
 	dbuf red_a, red_d;                         // [seg_last - seg_first][m]
+	dbuf d_red_lb, d_red_rb, d_red_size, walk_jump, walk_info;      // the reduced segments on the device (launch_walk)
+	hbuf h_red, h_info;                        // their host staging; red_pending: copies in flight, vectors not yet filled
+	bool red_pending{false};
 
 	dp_args dp() const
 	{
@@ -818,6 +831,7 @@ int shard_dp_final(fsq_shard *P, uint32_t *overflow)
 int shard_traceback(fsq_shard *P)
 {
 	fsq_ctx *ctx = P->ctx;
+	host_watch hw(ctx, "traceback");
 	phase pt(ctx, "traceback");
 	trace_args TA;
 	memset(&TA, 0, sizeof TA);
@@ -838,9 +852,8 @@ int shard_traceback(fsq_shard *P)
 	TA.out_lb = P->tr_lb.as <uint32_t>(); TA.out_rb = P->tr_rb.as <uint64_t>(); TA.out_max = P->tr_max.as <uint32_t>(); TA.out_size = P->tr_size.as <uint32_t>();
 	CK(launch_trace_gather(TA, T, ctx->stream));
 	ctx->stats["kernel_launches"] += 1;
-	hbuf stage;
-	CK(stage.alloc(ctx, (size_t) T * 20));
-	uint64_t *h_rb = stage.as <uint64_t>();
+	CK(P->h_tb.alloc(ctx, (size_t) T * 20));
+	uint64_t *h_rb = P->h_tb.as <uint64_t>();
 	uint32_t *h_lb = (uint32_t *) (h_rb + T), *h_max = h_lb + T, *h_size = h_max + T;
 	CK(cudaMemcpyAsync(h_rb, P->tr_rb.p, (size_t) T * 8, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaMemcpyAsync(h_lb, P->tr_lb.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -848,14 +861,11 @@ int shard_traceback(fsq_shard *P)
 	CK(cudaMemcpyAsync(h_size, P->tr_size.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
 	pt.stop();
 	CK(cudaStreamSynchronize(ctx->stream));
-	P->tb_rb_h.assign(h_rb, h_rb + T);
-	P->tb_lb_h.assign(h_lb, h_lb + T);
-	P->tb_max_h.assign(h_max, h_max + T);
-	P->tb_size_h.assign(h_size, h_size + T);
-	P->K = P->tb_max_h.back();
+	(void) h_size;
+	P->K = h_max[T - 1];
 	// the traceback positions this rank holds the state of: right bounds in (c0, c1]
-	P->pos_first = (uint32_t) (std::upper_bound(P->tb_rb_h.begin(), P->tb_rb_h.end(), P->c0) - P->tb_rb_h.begin());
-	P->pos_last = (uint32_t) (std::upper_bound(P->tb_rb_h.begin(), P->tb_rb_h.end(), P->c1) - P->tb_rb_h.begin());
+	P->pos_first = (uint32_t) (std::upper_bound(h_rb, h_rb + T, P->c0) - h_rb);
+	P->pos_last = (uint32_t) (std::upper_bound(h_rb, h_rb + T, P->c1) - h_rb);
 	return FSQ_OK;
 }
 
@@ -884,9 +894,9 @@ int shard_reduce(fsq_shard *P)
 {
 	fsq_ctx *ctx = P->ctx;
 	uint32_t const T = P->T;
+	host_watch hw(ctx, "reduce");
 	phase pr(ctx, "reduce");
-	hbuf h_next;
-	CK(P->d_next.alloc(ctx, (size_t) T * 4)); CK(P->d_nsize.alloc(ctx, (size_t) T * 4)); CK(h_next.alloc(ctx, (size_t) T * 8));
+	CK(P->d_next.alloc(ctx, (size_t) T * 4)); CK(P->d_nsize.alloc(ctx, (size_t) T * 4));
 	reduce_args R;
 	memset(&R, 0, sizeof R);
 	R.T = T; R.K = P->K; R.width = P->K + 1;
@@ -895,27 +905,53 @@ int shard_reduce(fsq_shard *P)
 	R.next = P->d_next.as <uint32_t>(); R.next_size = P->d_nsize.as <uint32_t>();
 	CK(launch_reduce(R, ctx->stream));
 	ctx->stats["kernel_launches"] += 1;
-	uint32_t *nxt = h_next.as <uint32_t>(), *nsz = nxt + T;
-	CK(cudaMemcpyAsync(nxt, P->d_next.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaMemcpyAsync(nsz, P->d_nsize.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	// the walk u -> next[u] + 1 from 0, on the device; the host learns the segment count and which segments are its own
+	walk_args W;
+	memset(&W, 0, sizeof W);
+	W.T = T;
+	W.levels = 1;
+	while ((1ull << W.levels) <= T) ++W.levels;
+	W.next = P->d_next.as <uint32_t>(); W.next_size = P->d_nsize.as <uint32_t>(); W.tb_rb = P->tr_rb.as <uint64_t>();
+	CK(P->walk_jump.alloc(ctx, (size_t) W.levels * T * 4)); CK(P->walk_info.alloc(ctx, 16)); CK(P->h_info.alloc(ctx, 16));
+	CK(P->d_red_lb.alloc(ctx, (size_t) T * 8)); CK(P->d_red_rb.alloc(ctx, (size_t) T * 8)); CK(P->d_red_size.alloc(ctx, (size_t) T * 4));
+	W.jump = P->walk_jump.as <uint32_t>(); W.info = P->walk_info.as <uint32_t>();
+	W.out_lb = P->d_red_lb.as <uint64_t>(); W.out_rb = P->d_red_rb.as <uint64_t>(); W.out_size = P->d_red_size.as <uint32_t>();
+	W.c0 = P->c0; W.c1 = P->c1;
+	CK(launch_walk(W, ctx->stream));
+	ctx->stats["kernel_launches"] += W.levels + 3;
+	CK(cudaMemcpyAsync(P->h_info.p, P->walk_info.p, 12, cudaMemcpyDeviceToHost, ctx->stream));
 	pr.stop();
 	CK(cudaStreamSynchronize(ctx->stream));
-	P->red_lb.clear(); P->red_rb.clear(); P->red_size.clear(); P->red_pos.clear();
-	P->red_lb.reserve(T); P->red_rb.reserve(T); P->red_size.reserve(T); P->red_pos.reserve(T);
-	uint64_t cur_lb = 0;
-	for (uint32_t u = 0; u < T; )
+	uint32_t const n_red = P->h_info.as <uint32_t>()[0];
+	P->seg_first = P->h_info.as <uint32_t>()[1];
+	P->seg_last = P->h_info.as <uint32_t>()[2];
+	P->n_reduced = n_red;
+	// host copies of the bounds (what segmentation_container holds) travel while the states are gathered
+	CK(P->h_red.alloc(ctx, (size_t) n_red * 20));
 	{
-		uint32_t const last = nxt[u];
-		P->red_lb.push_back(cur_lb);
-		P->red_rb.push_back(P->tb_rb_h[last]);
-		P->red_size.push_back(nsz[u]);
-		P->red_pos.push_back(last);
-		cur_lb = P->tb_rb_h[last];
-		u = last + 1;
+		uint64_t *h_lb = P->h_red.as <uint64_t>(), *h_rb = h_lb + n_red;
+		uint32_t *h_sz = (uint32_t *) (h_rb + n_red);
+		CK(cudaMemcpyAsync(h_lb, P->d_red_lb.p, (size_t) n_red * 8, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_rb, P->d_red_rb.p, (size_t) n_red * 8, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_sz, P->d_red_size.p, (size_t) n_red * 4, cudaMemcpyDeviceToHost, ctx->stream));
 	}
-	// the reduced segments whose end state this rank holds
-	P->seg_first = (uint32_t) (std::upper_bound(P->red_rb.begin(), P->red_rb.end(), P->c0) - P->red_rb.begin());
-	P->seg_last = (uint32_t) (std::upper_bound(P->red_rb.begin(), P->red_rb.end(), P->c1) - P->red_rb.begin());
+	P->red_pending = true;
+	return FSQ_OK;
+}
+
+// After the stream has drained: the reduced bounds as host vectors.
+int finish_reduced(fsq_shard *P)
+{
+	fsq_ctx *ctx = P->ctx;
+	if (!P->red_pending) return FSQ_OK;
+	CK(cudaStreamSynchronize(ctx->stream));
+	uint32_t const R = P->n_reduced;
+	uint64_t const *h_lb = P->h_red.as <uint64_t>(), *h_rb = h_lb + R;
+	uint32_t const *h_sz = (uint32_t const *) (h_rb + R);
+	P->red_lb.assign(h_lb, h_lb + R);
+	P->red_rb.assign(h_rb, h_rb + R);
+	P->red_size.assign(h_sz, h_sz + R);
+	P->red_pending = false;
 	return FSQ_OK;
 }
 
@@ -926,30 +962,27 @@ int shard_reduced_states(fsq_shard *P)
 	fsq_ctx *ctx = P->ctx;
 	uint32_t const m = P->m;
 	uint32_t const cnt = P->seg_last - P->seg_first;
+	host_watch hw(ctx, "reduced_states");
 	CK(P->red_a.alloc(ctx, (size_t) std::max <uint32_t>(cnt, 1) * m * 4)); CK(P->red_d.alloc(ctx, (size_t) std::max <uint32_t>(cnt, 1) * m * 4));
-	if (0 == cnt) return FSQ_OK;
-	if (P->states.p)
+	if (cnt && P->states.p)
 	{
-		hbuf h_rb;
-		dbuf d_rb;
-		CK(h_rb.alloc(ctx, (size_t) cnt * 8)); CK(d_rb.alloc(ctx, (size_t) cnt * 8));
-		for (uint32_t i = 0; i < cnt; ++i) h_rb.as <uint64_t>()[i] = P->red_rb[P->seg_first + i] - P->c0;      // local right bounds
-		CK(cudaMemcpyAsync(d_rb.p, h_rb.p, (size_t) cnt * 8, cudaMemcpyHostToDevice, ctx->stream));
 		phase pc(ctx, "pass_c");
 		dim3 const grid(cnt, (m + 255) / 256);
-		gather_stored_states_kernel <<<grid, 256, 0, ctx->stream>>>(P->states.as <uint32_t>(), P->state_stride, d_rb.as <uint64_t>(), m, P->S.g.C, P->c0,
+		gather_stored_states_kernel <<<grid, 256, 0, ctx->stream>>>(P->states.as <uint32_t>(), P->state_stride, P->d_red_rb.as <uint64_t>() + P->seg_first, m, P->S.g.C, P->c0,
 			P->S.oldvals.as <uint32_t>(), P->S.R.as <uint32_t>(), P->red_a.as <uint32_t>(), P->red_d.as <uint32_t>());
 		CK(cudaGetLastError());
 		pc.stop();
 		ctx->stats["kernel_launches"] += 1;
-		CK(cudaStreamSynchronize(ctx->stream));
-		P->states.release();
 	}
-	else
+	int rc = finish_reduced(P);      // drains the stream
+	if (rc) return rc;
+	if (cnt && P->states.p)
+		P->states.release();
+	else if (cnt)
 	{
 		std::vector <uint64_t> cols(cnt);
 		for (uint32_t i = 0; i < cnt; ++i) cols[i] = P->red_rb[P->seg_first + i] - P->c0;
-		int const rc = dump_states(ctx, P->msa, P->S, cols, P->red_a.as <uint32_t>(), P->red_d.as <uint32_t>());
+		rc = dump_states(ctx, P->msa, P->S, cols, P->red_a.as <uint32_t>(), P->red_d.as <uint32_t>());
 		if (rc) return rc;
 	}
 	return FSQ_OK;
@@ -1306,7 +1339,7 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	struct guard { fsq_segmentation *&s; bool ok{false}; ~guard() { if (!ok) { fsq_segmentation_free(s); s = nullptr; } } } gd{seg};
 	seg->ctx = ctx; seg->m = m; seg->n = n; seg->L = L;
 	if ((rc = shard_traceback(P))) return rc;
-	seg->tb_rb = P->tb_rb_h; seg->tb_lb = P->tb_lb_h; seg->tb_max = P->tb_max_h; seg->tb_size = P->tb_size_h;
+	seg->T = P->T; seg->h_tb_bytes = P->h_tb.bytes; seg->h_tb = P->h_tb.detach();
 	seg->K = P->K;
 	if (ctx->opt("keep_dp", 0))
 	{
@@ -1346,6 +1379,7 @@ void fsq_segmentation_free(fsq_segmentation *seg)
 	fsq_ctx *ctx = seg->ctx;
 	ctx->give(false, seg->d_a, seg->d_bytes[0]);
 	ctx->give(false, seg->d_d, seg->d_bytes[1]);
+	ctx->give(true, seg->h_tb, seg->h_tb_bytes);
 	ctx->give(true, seg->h_a, seg->h_bytes[0]);
 	ctx->give(true, seg->h_d, seg->h_bytes[1]);
 	delete seg;
@@ -1406,15 +1440,23 @@ int fsq_segmentation_states_view(const fsq_segmentation *cseg, const uint32_t **
 	return FSQ_OK;
 }
 
-uint32_t fsq_segmentation_traceback_count(const fsq_segmentation *seg) { return seg ? (uint32_t) seg->tb_rb.size() : 0; }
+uint32_t fsq_segmentation_traceback_count(const fsq_segmentation *seg) { return seg ? seg->T : 0; }
+
+// rb u64[T], then lb, max, size u32[T] each (shard_traceback)
+static void copy_traceback(void const *h_tb, uint32_t T, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
+{
+	uint64_t const *h_rb = static_cast <uint64_t const *>(h_tb);
+	uint32_t const *h_lb = reinterpret_cast <uint32_t const *>(h_rb + T), *h_max = h_lb + T, *h_size = h_max + T;
+	std::copy(h_lb, h_lb + T, lb);
+	std::copy(h_rb, h_rb + T, rb);
+	std::copy(h_max, h_max + T, max_size);
+	std::copy(h_size, h_size + T, size);
+}
 
 int fsq_segmentation_traceback(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
 {
 	if (!seg || !lb || !rb || !max_size || !size) return FSQ_ERR_ARG;
-	std::copy(seg->tb_lb.begin(), seg->tb_lb.end(), lb);
-	std::copy(seg->tb_rb.begin(), seg->tb_rb.end(), rb);
-	std::copy(seg->tb_max.begin(), seg->tb_max.end(), max_size);
-	std::copy(seg->tb_size.begin(), seg->tb_size.end(), size);
+	if (seg->h_tb) copy_traceback(seg->h_tb, seg->T, lb, rb, max_size, size);
 	return FSQ_OK;
 }
 
@@ -1696,10 +1738,7 @@ int fsq_shard_traceback(fsq_shard *P, uint32_t *count, uint32_t *K)
 int fsq_shard_get_traceback(const fsq_shard *P, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
 {
 	if (!P || !lb || !rb || !max_size || !size) return FSQ_ERR_ARG;
-	std::copy(P->tb_lb_h.begin(), P->tb_lb_h.end(), lb);
-	std::copy(P->tb_rb_h.begin(), P->tb_rb_h.end(), rb);
-	std::copy(P->tb_max_h.begin(), P->tb_max_h.end(), max_size);
-	std::copy(P->tb_size_h.begin(), P->tb_size_h.end(), size);
+	if (P->h_tb.p) copy_traceback(P->h_tb.p, P->T, lb, rb, max_size, size);
 	return FSQ_OK;
 }
 

@@ -616,6 +616,74 @@ cudaError_t launch_reduce(reduce_args const &A, cudaStream_t st)
 }
 
 
+// ---- the reduced segments from next[] -----------------------------------------------------------------------------------
+__global__ void walk_init_kernel(walk_args const A)
+{
+	uint32_t const u = blockIdx.x * blockDim.x + threadIdx.x;
+	if (u >= A.T) return;
+	uint32_t const v = A.next[u] + 1;
+	A.jump[u] = v < A.T ? v : TRACE_END;
+}
+
+__global__ void walk_double_kernel(walk_args const A, uint32_t k)
+{
+	uint32_t const u = blockIdx.x * blockDim.x + threadIdx.x;
+	if (u >= A.T) return;
+	uint32_t const *prev = A.jump + (size_t) (k - 1) * A.T;
+	uint32_t const j = prev[u];
+	A.jump[(size_t) k * A.T + u] = (TRACE_END == j) ? TRACE_END : prev[j];
+}
+
+__global__ void walk_count_kernel(walk_args const A)
+{
+	uint32_t cur = 0, hops = 0;
+	for (int k = (int) A.levels - 1; k >= 0; --k)
+	{
+		uint32_t const j = A.jump[(size_t) k * A.T + cur];
+		if (TRACE_END != j) { cur = j; hops += 1u << k; }
+	}
+	A.info[0] = hops + 1;
+}
+
+__global__ void walk_gather_kernel(walk_args const A)
+{
+	uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;      // segments in text order = hops from u = 0
+	if (s >= A.info[0]) return;
+	uint32_t cur = 0;
+	for (uint32_t k = 0; k < A.levels; ++k)
+		if ((s >> k) & 1u) cur = A.jump[(size_t) k * A.T + cur];
+	A.out_lb[s] = cur ? A.tb_rb[cur - 1] : 0ull;
+	A.out_rb[s] = A.tb_rb[A.next[cur]];
+	A.out_size[s] = A.next_size[cur];
+}
+
+// upper bounds of c0 and c1 among the right bounds: the segments whose end state this rank holds
+__global__ void walk_own_kernel(walk_args const A)
+{
+	if (threadIdx.x >= 2) return;
+	uint64_t const c = threadIdx.x ? A.c1 : A.c0;
+	uint32_t lo = 0, hi = A.info[0];
+	while (lo < hi)
+	{
+		uint32_t const mid = (lo + hi) >> 1;
+		if (A.out_rb[mid] <= c) lo = mid + 1; else hi = mid;
+	}
+	A.info[1 + threadIdx.x] = lo;
+}
+
+cudaError_t launch_walk(walk_args const &A, cudaStream_t st)
+{
+	uint32_t const grid = (A.T + 255) / 256;
+	walk_init_kernel <<<grid, 256, 0, st>>>(A);
+	for (uint32_t k = 1; k < A.levels; ++k)
+		walk_double_kernel <<<grid, 256, 0, st>>>(A, k);
+	walk_count_kernel <<<1, 1, 0, st>>>(A);
+	walk_gather_kernel <<<grid, 256, 0, st>>>(A);
+	walk_own_kernel <<<1, 32, 0, st>>>(A);
+	return cudaGetLastError();
+}
+
+
 // ---- segment sets (reference: pbwt.hh:253-280, create_segment_texts_task.cc:15-35) ----------------------------------
 // Runs of the prefix array w.r.t. the segment's left bound, in PBWT order; the rows of a run in ascending order.
 __global__ void __launch_bounds__(1024) segment_sets_kernel(

@@ -176,6 +176,21 @@ struct reduce_args
 cudaError_t launch_reduce_lists(reduce_args const &A, cudaStream_t st);    // fill lists[pos_first .. pos_last)
 cudaError_t launch_reduce(reduce_args const &A, cudaStream_t st);
 
+// The walk u -> next[u] + 1 from u = 0 (segmentation_lp_context.cc:335-390 merges in exactly this order), on the
+// device by pointer doubling: the reduced segments come out as arrays without a host loop over the traceback.
+struct walk_args
+{
+	uint32_t T, levels;          // 2^levels > T
+	uint32_t const *next, *next_size;
+	uint64_t const *tb_rb;       // [T]
+	uint32_t *jump;              // [levels][T]
+	uint64_t *out_lb, *out_rb;   // [<= T]
+	uint32_t *out_size;
+	uint64_t c0, c1;             // this rank's columns: it holds the state of the segments whose right bound lies in (c0, c1]
+	uint32_t *info;              // [0] number of reduced segments  [1], [2] first and one-past-last segment held here
+};
+cudaError_t launch_walk(walk_args const &A, cudaStream_t st);
+
 cudaError_t launch_segment_sets(uint32_t const *a, uint32_t const *d, uint32_t m, uint64_t lb, uint32_t *run_off, uint32_t *ids, uint32_t *class_of_row, uint32_t *n_runs, cudaStream_t st);
 cudaError_t launch_pair_weights(uint32_t const *cls_l, uint32_t const *cls_r, uint32_t m, uint32_t runs_r, int32_t *W, cudaStream_t st);
 
