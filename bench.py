@@ -41,9 +41,8 @@ WORKLOADS = {
 
 
 class ClockSampler:
-    """SM clock and clock-event (throttle) reasons DURING the timed region (B200_PROFILING.md's clocks line).  Sampled
-    in-process through NVML every 200 ms: an `nvidia-smi -lms` process beside the run was measured to stall this
-    process's launches by ~9 ms per sample (a 10 % error on a 9 ms step); `--clock-sampler smi` keeps that variant."""
+    """SM clock and clock-event (throttle) reasons under load (B200_PROFILING.md's clocks line): `nvidia-smi -lms`
+    beside the run (`smi`), or an in-process NVML thread (`nvml`).  Both disturb the run they watch -- see run()."""
 
     REASONS = [("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20), ("sw_power_cap", 0x4)]
 
@@ -73,7 +72,7 @@ class ClockSampler:
                 self.nvml = None
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "200"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", str(int(1000 * self.period))],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read_smi, daemon=True)
             self.thread.start()
@@ -118,6 +117,12 @@ class ClockSampler:
                 continue
             names = [n for n, _ in self.REASONS]
             self.lines.append((time.perf_counter(), sm, mx, [n for n, v in zip(names, f[2:6]) if v.lower().startswith("active")]))
+
+    def wait_ready(self, timeout=5.0):
+        """nvidia-smi needs about a second before its first line."""
+        t_end = time.perf_counter() + timeout
+        while self.kind != "none" and not self.lines and time.perf_counter() < t_end:
+            time.sleep(0.01)
 
     def window(self, t0, t1):
         """Keep the samples taken inside the timed region (the sampler is started before the warm-up so that its own
@@ -182,7 +187,7 @@ def sample_columns(m, kind_ref=True):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
@@ -191,7 +196,7 @@ def main():
     ap.add_argument("--block-columns", type=int, default=0)
     ap.add_argument("--warps", type=int, default=0)
     ap.add_argument("--cap", type=int, default=0)
-    ap.add_argument("--clock-sampler", default="nvml", choices=["nvml", "smi", "none"])
+    ap.add_argument("--clock-sampler", default="smi", choices=["nvml", "smi", "none"])
     ap.add_argument("--opt", action="append", default=[], help="library option key=value (experiments)")
     args = ap.parse_args()
 
@@ -322,10 +327,33 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             sys.stderr.write("host ms (accumulated): " + ", ".join("%s %.3f" % (k, ctx.stat("hms_" + k)) for k in ("traceback", "traceback_copy", "reduce", "reduce_walk", "reduced_states")) + "\n")
         return (res.K, res.count)
 
-    sampler = ClockSampler(dev, args.clock_sampler)
-    sampler.start()
     for _ in range(args.warmup):
         info = step()
+
+    # Clocks and clock-event reasons under this very load: a pass of the same steps with the sampler beside it, right
+    # before the timed pass.  Sampling inside the timed pass itself is measurably intrusive on this box (an nvidia-smi
+    # sample stalls the process's launches for ~9 ms, an in-process NVML thread far longer: tests/micro/nvml_cost.py and
+    # profiles/README.md), which on a 9 ms step is an error of 5-80 %, so the two are kept apart and both are reported.
+    sampler = ClockSampler(dev, args.clock_sampler, period=0.1)
+    sampler.start()
+    sampler.wait_ready()
+    barrier()
+    s0 = time.perf_counter()
+    n_sampled = max(args.steps, 40) if args.clock_sampler != "none" else 0
+    for _ in range(n_sampled):
+        info = step()
+    barrier()
+    s1 = time.perf_counter()
+    sampler.window(s0, s1)
+    clocks = sampler.stop()
+    if n_sampled:
+        clocks["sampled"] = "a pass of %d identical steps immediately before the timed one, sampler beside it" % n_sampled
+        clocks["ms_per_step_while_sampling"] = 1e3 * (s1 - s0) / n_sampled
+
+    if n_sampled:
+        time.sleep(0.05)             # the sampler process is gone; two more untimed steps before the timed ones
+        for _ in range(2):
+            info = step()
     ctx.reset_stats()
     barrier()
     ctx.set_option("timer", 1)
@@ -335,8 +363,6 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
     ctx.set_option("timer", 0)
     barrier()
     t1 = time.perf_counter()
-    sampler.window(t0, t1)
-    clocks = sampler.stop()
     wall = t1 - t0
     secs = ctx.stat("ms_timer") * 1e-3        # CUDA events on the stream the kernels are launched on
     if dist is not None:

@@ -255,14 +255,21 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 		size_t smem = 2 * (size_t) g.cg * msa->col_stride + 4 * (size_t) threads * (g.blocked ? g.E + 2 * g.ns : 1) + 2 * (size_t) m + 1024;
 		if (g.chunked)
 		{
-			block_args P;
-			memset(&P, 0, sizeof P);
-			P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m;
-			P.C = (uint32_t) std::min <uint64_t>(4096, std::max <uint64_t>(64, msa->n / (ctx->prop.multiProcessorCount * 8)));
-			smem = cblock_smem_bytes(P, g.T, g.E, g.ns, true) + 1024;
+			// The histogram of pass B grows with the block length, so the footprint depends on the answer: take the largest
+			// number of resident CTAs whose own block length fits (every CTA also reserves 1 KB of shared memory).
 			per_sm = std::min <uint64_t>(per_sm, 65536 / ((uint64_t) threads * (9 == g.E ? 64 : 128)));
+			for (; per_sm > 1; --per_sm)
+			{
+				block_args P;
+				memset(&P, 0, sizeof P);
+				P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m;
+				uint64_t const res = (uint64_t) ctx->prop.multiProcessorCount * per_sm;
+				P.C = (uint32_t) std::min <uint64_t>(4096, std::max <uint64_t>(64, (msa->n + res - 1) / res));
+				if ((cblock_smem_bytes(P, g.T, g.E, g.ns, true) + 1024) * per_sm <= (size_t) ctx->prop.sharedMemPerMultiprocessor) break;
+			}
+			smem = 0;
 		}
-		per_sm = std::min <uint64_t>(per_sm, (227 * 1024) / smem);
+		if (smem) per_sm = std::min <uint64_t>(per_sm, (227 * 1024) / smem);
 		per_sm = std::max <uint64_t>(per_sm, 1);
 		uint64_t const resident = (uint64_t) ctx->prop.multiProcessorCount * per_sm;
 		C = (int64_t) ((msa->n + resident - 1) / resident);
@@ -701,7 +708,7 @@ int shard_scan(fsq_shard *P)
 	if (!P->tb_max.p)
 	{
 		CK(P->tb_max.alloc(ctx, P->dp_size * 4)); CK(P->tb_lb.alloc(ctx, P->dp_size * 4)); CK(P->tb_size.alloc(ctx, P->dp_size * 4));
-		CK(P->mk.alloc(ctx, P->dp_size * 8)); CK(P->lev.alloc(ctx, (size_t) P->n_levels * P->n_blk * 4)); CK(P->flags.alloc(ctx, 16));
+		CK(P->mk.alloc(ctx, P->dp_size * 8)); CK(P->lev.alloc(ctx, (size_t) P->n_levels * P->n_blk * 4)); CK(P->flags.alloc(ctx, 32));
 		CK(P->cnt.alloc(ctx, nl * 4)); CK(P->h0.alloc(ctx, nl * 4));
 		CK(P->chunk_level.alloc(ctx, (size_t) P->n_chunks * 8));
 		// Pass B keeps the state of every column when 4 m n bytes fit comfortably (option store_states: -1 auto, 0 never,
@@ -730,7 +737,7 @@ int shard_scan(fsq_shard *P)
 	CK(cudaMemsetAsync(P->tb_lb.p, 0, P->dp_size * 4, ctx->stream));
 	CK(cudaMemsetAsync(P->mk.p, 0xff, P->dp_size * 8, ctx->stream));
 	CK(cudaMemsetAsync(P->lev.p, 0, (size_t) P->n_levels * P->n_blk * 4, ctx->stream));
-	CK(cudaMemsetAsync(P->flags.p, 0, 16, ctx->stream));
+	CK(cudaMemsetAsync(P->flags.p, 0, 32, ctx->stream));
 	P->rounds = 0;
 	P->reach_known = 0;
 	P->single_chain = false;
@@ -776,6 +783,35 @@ int shard_dp_round(fsq_shard *P, uint32_t *changed, uint32_t *reach)
 	pd.stop();
 	CK(cudaStreamSynchronize(ctx->stream));
 	*changed = (h_flags[0] && (1 == P->rounds || h_flags[3])) ? 1u : 0u;
+	*reach = h_flags[2];
+	P->reach_known = std::max(P->reach_known, h_flags[2]);
+	ctx->stats["dp_reach"] = h_flags[2];
+	return FSQ_OK;
+}
+
+// The first two rounds queued back to back, with the guess between them, and one read-back at the end: round 1 starts
+// from nothing and can never be the last, and the guess takes the look-back from the device (flags[2]) anyway, so the
+// host has no decision to make before round 2.  Single rank only (column shards exchange their slices after every round).
+int shard_dp_first_two_rounds(fsq_shard *P, uint32_t *changed, uint32_t *reach)
+{
+	fsq_ctx *ctx = P->ctx;
+	phase pd(ctx, "dp");
+	dp_args D = P->dp();
+	CK(cudaMemsetAsync(P->flags.p, 0, 4, ctx->stream));
+	CK(cudaMemsetAsync(P->flags.as <uint32_t>() + 3, 0, 4, ctx->stream));
+	CK(launch_dp_chains(D, ctx->stream));
+	CK(launch_dp_guess(D, ctx->stream));
+	CK(cudaMemsetAsync(P->flags.p, 0, 4, ctx->stream));
+	CK(cudaMemsetAsync(P->flags.as <uint32_t>() + 3, 0, 4, ctx->stream));
+	D.bound_on_device = 1;
+	CK(launch_dp_chains(D, ctx->stream));
+	ctx->stats["kernel_launches"] += 2 + 4 + P->n_levels;
+	P->rounds += 2;
+	uint32_t h_flags[4] = {0, 0, 0, 0};
+	CK(cudaMemcpyAsync(h_flags, P->flags.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+	pd.stop();
+	CK(cudaStreamSynchronize(ctx->stream));
+	*changed = (h_flags[0] && h_flags[3]) ? 1u : 0u;
 	*reach = h_flags[2];
 	P->reach_known = std::max(P->reach_known, h_flags[2]);
 	ctx->stats["dp_reach"] = h_flags[2];
@@ -1304,7 +1340,11 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 		while (true)
 		{
 			uint32_t changed = 0, reach = 0;
-			if ((rc = shard_dp_round(P, &changed, &reach))) return rc;
+			if (0 == P->rounds && P->n_chunks > 1 && !P->single_chain && max_rounds > 2 && guess_rounds >= 1)
+			{
+				if ((rc = shard_dp_first_two_rounds(P, &changed, &reach))) return rc;
+			}
+			else if ((rc = shard_dp_round(P, &changed, &reach))) return rc;
 			if (1 == P->n_chunks || P->single_chain) break;      // a single chain is the reference's own order: exact as it stands
 			if (P->rounds > 1 && 0 == changed) break;            // nothing changed: every entry was computed from the table it is part of
 			if (P->rounds >= max_rounds)

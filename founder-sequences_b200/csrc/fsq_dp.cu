@@ -236,7 +236,10 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 	// What a later chain may have read of this one while it ran: the last reach_bound entries (the look-back seen in the
 	// rounds before).  A round in which no chain changed anything there, and no chain read below that window, has
 	// computed every entry from values that are final: flags[3] counts the chains for which this cannot be said.
-	uint32_t const tail_from = t_end > A.reach_bound ? t_end - A.reach_bound : 0u;
+	// (bound_on_device: the bound is the copy of flags[2] the guess made before this round, flags[4], so that two rounds
+	// can be queued without the host in between; the live flags[2] moves while the round runs and cannot serve)
+	uint32_t const reach_bound = A.bound_on_device ? A.flags[4] : A.reach_bound;
+	uint32_t const tail_from = t_end > reach_bound ? t_end - reach_bound : 0u;
 	uint32_t lowest = 0xffffffffu;
 	bool unsettled = false, changed = false;      // published once per warp at the end (a store per entry would pile up on one address)
 
@@ -340,7 +343,7 @@ __global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
 	if (__any_sync(FSQ_FULL, changed) && 0 == lane) A.flags[0] = 1;
 	if (0 == lane && reach) atomicMax(&A.flags[2], reach);
 	// reads below the own entries must stay inside the window the chains before this one watch
-	if (0xffffffffu != lowest && lowest < t_begin && t_begin - lowest > A.reach_bound) unsettled = true;
+	if (0xffffffffu != lowest && lowest < t_begin && t_begin - lowest > reach_bound) unsettled = true;
 	if (__any_sync(FSQ_FULL, unsettled) && 0 == lane) atomicAdd(&A.flags[3], 1u);
 }
 
@@ -405,7 +408,7 @@ __global__ void __launch_bounds__(1024) dp_level_kernel(dp_args const A)
 	__shared__ uint32_t carry;
 	__shared__ uint32_t wmax[32];
 	uint32_t const lane = lane_id(), warp = threadIdx.x >> 5;
-	if (0 == threadIdx.x) carry = 0;
+	if (0 == threadIdx.x) { carry = 0; A.flags[4] = A.flags[2]; }      // the look-back bound of the next round (no chain is running now)
 	__syncthreads();
 	for (uint32_t c0 = 0; c0 < A.n_chunks; c0 += blockDim.x)
 	{

@@ -136,7 +136,9 @@ struct dp_args
 	uint32_t *flags;            // [0] some stored value changed  [1] 1 + column whose top list was too short to be exact
 	                            // [2] the farthest any column looked back in the table (entries), over all rounds
 	                            // [3] chains of this round whose result a later chain may have read half-way (see dp_chain_kernel)
+	                            // [4] flags[2] as it stood when the last guess ran: the look-back bound of a round queued behind it
 	uint32_t reach_bound;       // the look-back known when the round starts (0 in the first round)
+	uint32_t bound_on_device;   // take the bound from flags[4] instead (see dp_chain_kernel)
 	uint32_t w_first, w_last;   // masks and rmq cells are rebuilt for entries [w_first, w_last) (w_first a multiple of 64)
 };
 
