@@ -636,7 +636,9 @@ struct fsq_shard
 	dbuf red_a, red_d;                         // [seg_last - seg_first][m]
 	dbuf d_red_lb, d_red_rb, d_red_size, walk_jump, walk_info;      // the reduced segments on the device (launch_walk)
 	hbuf h_red, h_info;                        // their host staging; red_pending: copies in flight, vectors not yet filled
-	bool red_pending{false};
+	bool red_pending{false}, red_on_host{false};
+	bool final_done{false};                    // the last DP entry was computed behind the final round already
+	uint32_t final_overflow{};
 
 	dp_args dp() const
 	{
@@ -718,7 +720,7 @@ int shard_scan(fsq_shard *P)
 		if (g.chunked && 0 != want)
 		{
 			size_t free_b = 0, total_b = 0;
-			CK(cudaMemGetInfo(&free_b, &total_b));
+			CK(cudaMemGetInfo(&free_b, &total_b));      // (a driver round trip per call; the answer decides only the first time)
 			size_t cached = 0;
 			for (auto const &blk : ctx->dev_cache) cached += blk.bytes;
 			size_t const need = (size_t) (P->state_stride * 4 * nl);
@@ -739,6 +741,7 @@ int shard_scan(fsq_shard *P)
 	CK(cudaMemsetAsync(P->lev.p, 0, (size_t) P->n_levels * P->n_blk * 4, ctx->stream));
 	CK(cudaMemsetAsync(P->flags.p, 0, 32, ctx->stream));
 	P->rounds = 0;
+	P->final_done = false;
 	P->reach_known = 0;
 	P->single_chain = false;
 	{
@@ -805,7 +808,9 @@ int shard_dp_first_two_rounds(fsq_shard *P, uint32_t *changed, uint32_t *reach)
 	CK(cudaMemsetAsync(P->flags.as <uint32_t>() + 3, 0, 4, ctx->stream));
 	D.bound_on_device = 1;
 	CK(launch_dp_chains(D, ctx->stream));
-	ctx->stats["kernel_launches"] += 2 + 4 + P->n_levels;
+	// the last entry too, behind the same read-back: it stands if round 2 turns out to have been the last one
+	CK(launch_dp_final(D, ctx->stream));
+	ctx->stats["kernel_launches"] += 3 + 5;
 	P->rounds += 2;
 	uint32_t h_flags[4] = {0, 0, 0, 0};
 	CK(cudaMemcpyAsync(h_flags, P->flags.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
@@ -815,6 +820,13 @@ int shard_dp_first_two_rounds(fsq_shard *P, uint32_t *changed, uint32_t *reach)
 	*reach = h_flags[2];
 	P->reach_known = std::max(P->reach_known, h_flags[2]);
 	ctx->stats["dp_reach"] = h_flags[2];
+	if (0 == *changed)
+	{
+		P->final_done = true;
+		P->final_overflow = h_flags[1];
+		ctx->stats["dp_rounds"] += P->rounds;
+		ctx->stats["dp_chunks"] = P->n_chunks;
+	}
 	return FSQ_OK;
 }
 
@@ -829,16 +841,15 @@ int shard_dp_sync(fsq_shard *P, int guess, uint32_t reach)
 	{
 		CK(cudaMemcpyAsync(P->flags.as <uint32_t>() + 2, &reach, 4, cudaMemcpyHostToDevice, ctx->stream));
 		CK(launch_dp_guess(D, ctx->stream));
-		ctx->stats["kernel_launches"] += 4 + P->n_levels;
+		ctx->stats["kernel_launches"] += 5;
 	}
 	else
 	{
 		CK(launch_dp_rebuild(D, ctx->stream));
-		ctx->stats["kernel_launches"] += 1 + P->n_levels;
+		ctx->stats["kernel_launches"] += 2;
 	}
 	pd.stop();
-	CK(cudaStreamSynchronize(ctx->stream));      // reach is a stack variable of the caller's frame
-	return FSQ_OK;
+	return FSQ_OK;        // (a copy from pageable host memory has left the source when cudaMemcpyAsync returns)
 }
 
 // The last entry (segmentation_lp_context.cc:165-185), on the rank that holds the last column; and this rank's
@@ -879,7 +890,7 @@ int shard_traceback(fsq_shard *P)
 	CK(jump.alloc(ctx, (size_t) TA.levels * P->dp_size * 4)); CK(count.alloc(ctx, 4));
 	TA.jump = jump.as <uint32_t>(); TA.count = count.as <uint32_t>();
 	CK(launch_trace_tables(TA, ctx->stream));
-	ctx->stats["kernel_launches"] += TA.levels + 1;
+	ctx->stats["kernel_launches"] += 1;
 	uint32_t T = 0;
 	CK(cudaMemcpyAsync(&T, count.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaStreamSynchronize(ctx->stream));
@@ -925,8 +936,10 @@ int shard_reduce_lists(fsq_shard *P)
 	return FSQ_OK;
 }
 
+int start_reduced_copy(fsq_shard *P);
+
 // Greedy reduction (segmentation_lp_context.cc:335-390) from the complete lists; every rank does the same.
-int shard_reduce(fsq_shard *P)
+int shard_reduce(fsq_shard *P, bool want_host_bounds)
 {
 	fsq_ctx *ctx = P->ctx;
 	uint32_t const T = P->T;
@@ -954,7 +967,7 @@ int shard_reduce(fsq_shard *P)
 	W.out_lb = P->d_red_lb.as <uint64_t>(); W.out_rb = P->d_red_rb.as <uint64_t>(); W.out_size = P->d_red_size.as <uint32_t>();
 	W.c0 = P->c0; W.c1 = P->c1;
 	CK(launch_walk(W, ctx->stream));
-	ctx->stats["kernel_launches"] += W.levels + 3;
+	ctx->stats["kernel_launches"] += 1;
 	CK(cudaMemcpyAsync(P->h_info.p, P->walk_info.p, 12, cudaMemcpyDeviceToHost, ctx->stream));
 	pr.stop();
 	CK(cudaStreamSynchronize(ctx->stream));
@@ -962,8 +975,18 @@ int shard_reduce(fsq_shard *P)
 	P->seg_first = P->h_info.as <uint32_t>()[1];
 	P->seg_last = P->h_info.as <uint32_t>()[2];
 	P->n_reduced = n_red;
-	// host copies of the bounds (what segmentation_container holds) travel while the states are gathered
-	CK(P->h_red.alloc(ctx, (size_t) n_red * 20));
+	P->red_lb.clear(); P->red_rb.clear(); P->red_size.clear();
+	P->red_on_host = false;
+	if (!want_host_bounds) return FSQ_OK;      // column shards fetch them on request (fsq_shard_bounds): they are replicated
+	return start_reduced_copy(P);
+}
+
+// Host copies of the reduced bounds (what segmentation_container holds): started here, completed by finish_reduced().
+int start_reduced_copy(fsq_shard *P)
+{
+	fsq_ctx *ctx = P->ctx;
+	uint32_t const n_red = P->n_reduced;
+	CK(P->h_red.alloc(ctx, (size_t) std::max <uint32_t>(n_red, 1) * 20));
 	{
 		uint64_t *h_lb = P->h_red.as <uint64_t>(), *h_rb = h_lb + n_red;
 		uint32_t *h_sz = (uint32_t *) (h_rb + n_red);
@@ -979,7 +1002,12 @@ int shard_reduce(fsq_shard *P)
 int finish_reduced(fsq_shard *P)
 {
 	fsq_ctx *ctx = P->ctx;
-	if (!P->red_pending) return FSQ_OK;
+	if (P->red_on_host) return FSQ_OK;
+	if (!P->red_pending)
+	{
+		int const rc = start_reduced_copy(P);
+		if (rc) return rc;
+	}
 	CK(cudaStreamSynchronize(ctx->stream));
 	uint32_t const R = P->n_reduced;
 	uint64_t const *h_lb = P->h_red.as <uint64_t>(), *h_rb = h_lb + R;
@@ -988,6 +1016,7 @@ int finish_reduced(fsq_shard *P)
 	P->red_rb.assign(h_rb, h_rb + R);
 	P->red_size.assign(h_sz, h_sz + R);
 	P->red_pending = false;
+	P->red_on_host = true;
 	return FSQ_OK;
 }
 
@@ -1010,8 +1039,13 @@ int shard_reduced_states(fsq_shard *P)
 		pc.stop();
 		ctx->stats["kernel_launches"] += 1;
 	}
-	int rc = finish_reduced(P);      // drains the stream
-	if (rc) return rc;
+	int rc = FSQ_OK;
+	if (P->red_pending || (cnt && !P->states.p))
+	{
+		if ((rc = finish_reduced(P))) return rc;      // drains the stream
+	}
+	else
+		CK(cudaStreamSynchronize(ctx->stream));
 	if (cnt && P->states.p)
 		P->states.release();
 	else if (cnt)
@@ -1359,7 +1393,8 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 			}
 		}
 		uint32_t ovf = 0;
-		if ((rc = shard_dp_final(P, &ovf))) return rc;
+		if (P->final_done) ovf = P->final_overflow;
+		else if ((rc = shard_dp_final(P, &ovf))) return rc;
 		if (0 == ovf) break;
 		if (P->cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list at column %u with cap = m", ovf - 1);
 		P->cap = (uint32_t) std::min <uint64_t>(m, (uint64_t) P->cap * 4);
@@ -1401,7 +1436,7 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	// ---- greedy reduction (segmentation_lp_context.cc:335-390), then the states at the reduced right bounds
 	//      (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35) ----
 	if ((rc = shard_reduce_lists(P))) return rc;
-	if ((rc = shard_reduce(P))) return rc;
+	if ((rc = shard_reduce(P, true))) return rc;
 	if ((rc = shard_reduced_states(P))) return rc;
 	seg->lb = P->red_lb; seg->rb = P->red_rb; seg->size = P->red_size;
 	seg->d_bytes[0] = P->red_a.bytes; seg->d_bytes[1] = P->red_d.bytes;
@@ -1803,11 +1838,11 @@ int fsq_shard_reduce(fsq_shard *P, uint32_t *count, uint32_t *own_first, uint32_
 	if (!P || !count || !own_first || !own_last) return FSQ_ERR_ARG;
 	fsq_ctx *ctx = P->ctx;
 	CK(cudaSetDevice(ctx->device));
-	int rc = shard_reduce(P);
+	int rc = shard_reduce(P, false);
 	if (rc) return rc;
 	if ((rc = shard_reduced_states(P))) return rc;
 	CK(cudaStreamSynchronize(ctx->stream));
-	*count = (uint32_t) P->red_lb.size();
+	*count = P->n_reduced;
 	*own_first = P->seg_first;
 	*own_last = P->seg_last;
 	ctx->stats["cap"] = P->cap;
@@ -1816,9 +1851,15 @@ int fsq_shard_reduce(fsq_shard *P, uint32_t *count, uint32_t *own_first, uint32_
 	return FSQ_OK;
 }
 
-int fsq_shard_bounds(const fsq_shard *P, uint64_t *lb, uint64_t *rb, uint32_t *size)
+int fsq_shard_bounds(const fsq_shard *cP, uint64_t *lb, uint64_t *rb, uint32_t *size)
 {
+	fsq_shard *P = const_cast <fsq_shard *>(cP);
 	if (!P || !lb || !rb || !size) return FSQ_ERR_ARG;
+	CK_(P->ctx, cudaSetDevice(P->ctx->device));
+	{
+		int const rc = finish_reduced(P);
+		if (rc) return rc;
+	}
 	std::copy(P->red_lb.begin(), P->red_lb.end(), lb);
 	std::copy(P->red_rb.begin(), P->red_rb.end(), rb);
 	std::copy(P->red_size.begin(), P->red_size.end(), size);

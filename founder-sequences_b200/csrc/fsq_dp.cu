@@ -2,6 +2,8 @@
 // the segment-set / edge-weight kernels (sm_100a).
 #include "fsq_internal.h"
 #include "fsq_common.cuh"
+#include <cooperative_groups.h>
+#include <algorithm>
 
 namespace fsq {
 
@@ -477,6 +479,24 @@ cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st)
 
 // Masks and rmq tables as a function of the table as it stands (no levelling): what a rank does after it has received the
 // other ranks' entries.
+// All levels of the rmq tables in one launch: level p of cell i needs level p - 1 of the same cell only, so the levels
+// of a cell are computed by one thread, in order, without any barrier.
+__global__ void dp_levels_all_kernel(dp_args const A)
+{
+	uint32_t const i = A.w_first / 64 + blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t const n_complete = A.w_last / 64;
+	uint32_t prev = 0;
+	for (uint32_t p = 0; p < A.n_levels; ++p)
+	{
+		uint64_t const b = (uint64_t) i + (1ull << p) - 1;       // the block whose completion defines lev[p][i]
+		if (b >= n_complete) return;
+		uint32_t const smp0 = 64 * (uint32_t) b + (uint32_t) __ffsll((long long) A.mk[64 * b + 63]) - 1u;
+		uint32_t const res = (0 == p) ? smp0 : ((A.tb_max[smp0] < A.tb_max[prev]) ? smp0 : prev);
+		A.lev[(size_t) p * A.n_blk + i] = res;
+		prev = res;
+	}
+}
+
 cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st)
 {
 	if (A.w_first >= A.w_last) return cudaSuccess;
@@ -484,8 +504,8 @@ cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st)
 	dp_masks_kernel <<<(span + 7) / 8, 256, 0, st>>>(A);
 	uint32_t const n_complete = A.w_last / 64;
 	uint32_t const first_blk = A.w_first / 64;
-	for (uint32_t p = 0; p < A.n_levels && (1ull << p) <= n_complete && first_blk < n_complete; ++p)
-		dp_levels_kernel <<<(n_complete - first_blk + 255) / 256, 256, 0, st>>>(A, p);
+	if (first_blk < n_complete)
+		dp_levels_all_kernel <<<(n_complete - first_blk + 255) / 256, 256, 0, st>>>(A);
 	return cudaGetLastError();
 }
 
@@ -535,8 +555,69 @@ __global__ void trace_gather_kernel(trace_args const A, uint32_t count)
 	A.out_size[o] = A.tb_size[cur];
 }
 
+// Level-by-level phases (pointer doubling, rmq levels) are a dozen or two launches of kernels that each run for a few
+// microseconds: the launch rate of the host, not the device, sets their time, and on a busy host it varies by the
+// millisecond.  They run instead as ONE cooperative launch with a grid-wide barrier between levels; the grid is what is
+// resident at once.  (The one-launch-per-level forms stay as the fallback.)
+template <typename K, typename A>
+static bool launch_cooperative(K kernel, A const &args, uint32_t threads, uint64_t work_items, cudaStream_t st, cudaError_t *err)
+{
+	static int coop = -1, sms = 0;
+	if (coop < 0)
+	{
+		int dev = 0;
+		cudaGetDevice(&dev);
+		cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+		cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+	}
+	if (coop <= 0) return false;
+	int per_sm = 0;
+	if (cudaSuccess != cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, (int) threads, 0) || per_sm <= 0) { cudaGetLastError(); return false; }
+	uint64_t const want = (work_items + threads - 1) / threads;
+	uint32_t const grid = (uint32_t) std::max <uint64_t>(1, std::min <uint64_t>(want, (uint64_t) per_sm * sms));
+	A a = args;
+	void *params[] = {&a};
+	*err = cudaLaunchCooperativeKernel((void const *) kernel, dim3(grid), dim3(threads), params, 0, st);
+	return true;
+}
+
+__global__ void __launch_bounds__(256) trace_tables_coop_kernel(trace_args const A)
+{
+	cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+	uint32_t const stride = gridDim.x * blockDim.x, first = blockIdx.x * blockDim.x + threadIdx.x;
+	for (uint32_t t = first; t < A.dp_size; t += stride)
+	{
+		uint32_t const lb = A.tb_lb[t];
+		A.jump[t] = lb ? lb - A.L : TRACE_END;
+	}
+	for (uint32_t k = 1; k < A.levels; ++k)
+	{
+		grid.sync();
+		uint32_t const *prev = A.jump + (size_t) (k - 1) * A.dp_size;
+		uint32_t *cur = A.jump + (size_t) k * A.dp_size;
+		for (uint32_t t = first; t < A.dp_size; t += stride)
+		{
+			uint32_t const j = prev[t];
+			cur[t] = (TRACE_END == j) ? TRACE_END : prev[j];
+		}
+	}
+	grid.sync();
+	if (0 == first)
+	{
+		uint32_t cur = A.dp_size - 1, hops = 0;
+		for (int k = (int) A.levels - 1; k >= 0; --k)
+		{
+			uint32_t const j = A.jump[(size_t) k * A.dp_size + cur];
+			if (TRACE_END != j) { cur = j; hops += 1u << k; }
+		}
+		*A.count = hops + 1;
+	}
+}
+
 cudaError_t launch_trace_tables(trace_args const &A, cudaStream_t st)
 {
+	cudaError_t err = cudaSuccess;
+	if (launch_cooperative(trace_tables_coop_kernel, A, 256, A.dp_size, st, &err)) return err;
 	uint32_t const grid = (A.dp_size + 255) / 256;
 	trace_init_kernel <<<grid, 256, 0, st>>>(A);
 	for (uint32_t k = 1; k < A.levels; ++k)
@@ -674,8 +755,66 @@ __global__ void walk_own_kernel(walk_args const A)
 	A.info[1 + threadIdx.x] = lo;
 }
 
+__global__ void __launch_bounds__(256) walk_coop_kernel(walk_args const A)
+{
+	cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+	uint32_t const stride = gridDim.x * blockDim.x, first = blockIdx.x * blockDim.x + threadIdx.x;
+	for (uint32_t u = first; u < A.T; u += stride)
+	{
+		uint32_t const v = A.next[u] + 1;
+		A.jump[u] = v < A.T ? v : TRACE_END;
+	}
+	for (uint32_t k = 1; k < A.levels; ++k)
+	{
+		grid.sync();
+		uint32_t const *prev = A.jump + (size_t) (k - 1) * A.T;
+		uint32_t *cur = A.jump + (size_t) k * A.T;
+		for (uint32_t u = first; u < A.T; u += stride)
+		{
+			uint32_t const j = prev[u];
+			cur[u] = (TRACE_END == j) ? TRACE_END : prev[j];
+		}
+	}
+	grid.sync();
+	if (0 == first)
+	{
+		uint32_t cur = 0, hops = 0;
+		for (int k = (int) A.levels - 1; k >= 0; --k)
+		{
+			uint32_t const j = A.jump[(size_t) k * A.T + cur];
+			if (TRACE_END != j) { cur = j; hops += 1u << k; }
+		}
+		A.info[0] = hops + 1;
+	}
+	grid.sync();
+	uint32_t const count = A.info[0];
+	for (uint32_t s = first; s < count; s += stride)
+	{
+		uint32_t cur = 0;
+		for (uint32_t k = 0; k < A.levels; ++k)
+			if ((s >> k) & 1u) cur = A.jump[(size_t) k * A.T + cur];
+		A.out_lb[s] = cur ? A.tb_rb[cur - 1] : 0ull;
+		A.out_rb[s] = A.tb_rb[A.next[cur]];
+		A.out_size[s] = A.next_size[cur];
+	}
+	grid.sync();
+	if (first < 2)
+	{
+		uint64_t const c = first ? A.c1 : A.c0;
+		uint32_t lo = 0, hi = count;
+		while (lo < hi)
+		{
+			uint32_t const mid = (lo + hi) >> 1;
+			if (A.out_rb[mid] <= c) lo = mid + 1; else hi = mid;
+		}
+		A.info[1 + first] = lo;
+	}
+}
+
 cudaError_t launch_walk(walk_args const &A, cudaStream_t st)
 {
+	cudaError_t err = cudaSuccess;
+	if (launch_cooperative(walk_coop_kernel, A, 256, A.T, st, &err)) return err;
 	uint32_t const grid = (A.T + 255) / 256;
 	walk_init_kernel <<<grid, 256, 0, st>>>(A);
 	for (uint32_t k = 1; k < A.levels; ++k)
