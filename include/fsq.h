@@ -45,9 +45,11 @@ void fsq_destroy(fsq_ctx *ctx);
 const char *fsq_last_error(const fsq_ctx *ctx);     /* ctx may be NULL: returns the message of a failed fsq_create */
 const char *fsq_version(void);
 
-/* Tuning knobs (all have defaults): "block_columns" (columns per scan block), "cap" (initial bound on the
- * per-column top list; grown automatically when the DP proves it too small), "keep_dp" (retain the full DP
- * table for fsq_segmentation_dp_table), "keep_traceback_states". */
+/* Tuning knobs (all have defaults; unknown keys are an error): "block_columns" (columns per scan block), "cap"
+ * (initial bound on the per-column top list; grown automatically when the DP proves it too small), "keep_dp"
+ * (retain the full DP table for fsq_segmentation_dp_table), "store_states" (-1 auto, 0 re-scan for the boundary
+ * states, 1 keep every column's state in pass B), "dp_chunks", "dp_max_rounds", "dp_guess_rounds" (DP chaining),
+ * "kernel", "chunk", "warps", "stitch_sort", "stitch_group" (kernel selection, used by the parity tests). */
 int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value);
 int fsq_get_stat(const fsq_ctx *ctx, const char *key, double *value);   /* e.g. "ms_pack", "ms_pass_a", "ms_dp", "kernel_launches" */
 
