@@ -322,8 +322,8 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             res = sharded.segment_sharded(eng, comm, want_states=False, want_traceback=False, want_bounds=False)
         finally:
             eng.close()
-        if getattr(res, "trace", None) and rank == 0:
-            sys.stderr.write("shard trace (rank 0, ms): " + ", ".join("%s %.3f" % kv for kv in res.trace) + "\n")
+        if getattr(res, "trace", None) and rank in (0, world - 1):
+            sys.stderr.write("shard trace (rank %d, ms): " % rank + ", ".join("%s %.3f" % kv for kv in res.trace) + "\n")
             sys.stderr.write("host ms (accumulated): " + ", ".join("%s %.3f" % (k, ctx.stat("hms_" + k)) for k in ("traceback", "traceback_copy", "reduce", "reduce_walk", "reduced_states")) + "\n")
         return (res.K, res.count)
 

@@ -46,6 +46,16 @@ class TorchComm:
         self.dist.all_gather(out, tensor, group=self.group)
         return out
 
+    def all_gather_flat(self, tensor):
+        """[size, len] tensor of every rank's 1-D tensor (same length everywhere)."""
+        out = torch.empty((self.size, tensor.numel()), dtype=tensor.dtype, device=tensor.device)
+        if tensor.is_cuda:
+            self.dist.all_gather_into_tensor(out.view(-1), tensor, group=self.group)
+        else:
+            parts = [out[r] for r in range(self.size)]
+            self.dist.all_gather(parts, tensor, group=self.group)
+        return out
+
     def fence(self, device):
         """The engine launches on its own stream: what a collective wrote must have landed before the next stage."""
         if getattr(device, "type", "cpu") == "cuda":
@@ -114,6 +124,9 @@ class ThreadComm:
             torch.cuda.synchronize(tensor.device)
         self.sh.barrier.wait()
         return out
+
+    def all_gather_flat(self, tensor):
+        return torch.stack(self.all_gather(tensor))
 
     def fence(self, device):
         pass        # broadcast / all_gather above synchronise the device themselves
@@ -272,23 +285,35 @@ class ShardedResult:
         self.cap_retries = 0
 
 
-def _exchange_slices(comm, tensors, ranges):
-    """Every rank sends its own slice [first, last) of each tensor to all others (ranges: per rank).  One all-gather
-    per tensor over slices padded to the longest one -- a broadcast per rank costs a collective launch per rank and
-    adds up the ranks' skew -- then the received slices are copied into place."""
+def _exchange_slices(comm, tensors, ranges, extras=None):
+    """Every rank sends its own slice [first, last) of each tensor to all others (ranges: per rank).  ONE all-gather for
+    all tensors (same dtype), the slices padded to the longest one and laid side by side -- a broadcast per rank costs a
+    collective launch per rank and adds up the ranks' skew -- then the received slices are copied into place.
+    extras: a few non-negative integers that ride along; returns their element-wise maximum over the ranks (one
+    read-back instead of a second collective)."""
     width = max(l - f for f, l in ranges)
-    if width == 0:
-        return
-    for t in tensors:
-        f, l = ranges[comm.rank]
-        send = torch.zeros(width, dtype=t.dtype, device=t.device)
-        send[: l - f] = t[f:l]
-        got = comm.all_gather(send)
-        for src, (f, l) in enumerate(ranges):
-            if src != comm.rank and l > f:
-                t[f:l] = got[src][: l - f]
-    if tensors:
-        comm.fence(tensors[0].device)
+    extras = [int(v) for v in (extras or [])]
+    if not tensors:
+        return comm.max_many(extras, torch.device("cpu")) if extras else []
+    t0 = tensors[0]
+    k, e = len(tensors), len(extras)
+    send = torch.zeros(k * width + e, dtype=t0.dtype, device=t0.device)
+    f, l = ranges[comm.rank]
+    for i, t in enumerate(tensors):
+        send[i * width: i * width + (l - f)] = t[f:l]
+    if e:
+        send[k * width:] = torch.tensor(extras, dtype=t0.dtype)
+    got = comm.all_gather_flat(send)                    # [size, k * width + e]
+    for src, (f, l) in enumerate(ranges):
+        if src != comm.rank and l > f:
+            for i, t in enumerate(tensors):
+                t[f:l] = got[src, i * width: i * width + (l - f)]
+    if e:
+        out = [int(v) for v in got[:, k * width:].max(dim=0).values.tolist()]      # the read-back also drains the copies above
+    else:
+        out = []
+    comm.fence(t0.device)
+    return out
 
 
 def entry_range(c0, c1, n, L):
@@ -352,10 +377,8 @@ def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=Tru
             changed, reach = engine.dp_round()
             mark("dp_round")
             rounds += 1
-            _exchange_slices(comm, tabs[:1], ranges)
-            mark("dp exchange")
-            changed, reach = comm.max_many((changed, reach), dev)
-            mark("dp flags")
+            changed, reach = _exchange_slices(comm, tabs[:1], ranges, extras=(changed, reach))
+            mark("dp exchange + flags")
             if comm.size == 1 and rounds > 1 and not changed:
                 break
             if rounds > 1 and not changed:
@@ -369,8 +392,7 @@ def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=Tru
             mark("dp_sync")
         overflow = engine.dp_final()
         mark("dp_final")
-        _exchange_slices(comm, tabs, ranges)
-        overflow = comm.max(overflow, dev)
+        overflow, = _exchange_slices(comm, tabs, ranges, extras=(overflow,))
         mark("table exchange")
         res.dp_rounds += rounds
         if not overflow:
