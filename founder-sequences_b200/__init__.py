@@ -33,7 +33,7 @@ EXPORTS = [
     "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights",
     "fsq_msa_set_first_column", "fsq_shard_create", "fsq_shard_free", "fsq_shard_local_summary", "fsq_shard_set_start",
     "fsq_shard_scan", "fsq_shard_dp_table", "fsq_shard_dp_round", "fsq_shard_dp_sync", "fsq_shard_dp_single_chain",
-    "fsq_shard_dp_final", "fsq_shard_grow_cap", "fsq_shard_traceback", "fsq_shard_get_traceback",
+    "fsq_shard_dp_final", "fsq_shard_grow_cap", "fsq_shard_traceback", "fsq_shard_get_traceback", "fsq_shard_position_range",
     "fsq_shard_reduce_lists", "fsq_shard_reduce", "fsq_shard_bounds", "fsq_shard_states",
 ]
 
@@ -107,6 +107,7 @@ def load_library():
     proto("fsq_shard_grow_cap", ci, [vp])
     proto("fsq_shard_traceback", ci, [vp, pu32, pu32])
     proto("fsq_shard_get_traceback", ci, [vp, vp, vp, vp, vp])
+    proto("fsq_shard_position_range", ci, [vp, u64, u64, pu32, pu32])
     proto("fsq_shard_reduce_lists", ci, [vp, pp, pu32, pu32, pu32])
     proto("fsq_shard_reduce", ci, [vp, pu32, pu32, pu32])
     proto("fsq_shard_bounds", ci, [vp, vp, vp, vp])

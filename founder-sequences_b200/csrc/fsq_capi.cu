@@ -1817,6 +1817,16 @@ int fsq_shard_get_traceback(const fsq_shard *P, uint64_t *lb, uint64_t *rb, uint
 	return FSQ_OK;
 }
 
+int fsq_shard_position_range(const fsq_shard *P, uint64_t c0, uint64_t c1, uint32_t *first, uint32_t *last)
+{
+	if (!P || !first || !last) return FSQ_ERR_ARG;
+	if (!P->h_tb.p) return fail(P->ctx, FSQ_ERR_ARG, "fsq_shard_traceback has not run");
+	uint64_t const *h_rb = P->h_tb.as <uint64_t>();
+	*first = (uint32_t) (std::upper_bound(h_rb, h_rb + P->T, c0) - h_rb);
+	*last = (uint32_t) (std::upper_bound(h_rb, h_rb + P->T, c1) - h_rb);
+	return FSQ_OK;
+}
+
 int fsq_shard_reduce_lists(fsq_shard *P, uint32_t **d_lists, uint32_t *width, uint32_t *own_first, uint32_t *own_last)
 {
 	if (!P || !d_lists || !width || !own_first || !own_last) return FSQ_ERR_ARG;

@@ -239,6 +239,11 @@ class GpuShard:
         self.ctx.check(self.lib.fsq_shard_get_traceback(self.h, p(lb), p(rb), p(mx), p(sz)))
         return lb, rb, mx, sz
 
+    def position_range(self, c0, c1):
+        f, l = C.c_uint32(), C.c_uint32()
+        self.ctx.check(self.lib.fsq_shard_position_range(self.h, int(c0), int(c1), C.byref(f), C.byref(l)))
+        return f.value, l.value
+
     def reduce_lists(self, count):
         pl = C.c_void_p()
         w, f, l = C.c_uint32(), C.c_uint32(), C.c_uint32()
@@ -411,7 +416,9 @@ def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=Tru
         raise NotReducible("the maximum segment size %d is equal to the number of input sequences" % K)
     lists, row, own_pos = engine.reduce_lists(T)
     mark("reduce_lists")
-    pos_ranges = comm.gather_ints(own_pos, dev)
+    # the traceback is replicated: every rank can tell which rows every other rank fills
+    pos_ranges = [engine.position_range(int(c[0]), int(c[1])) for c in cols]
+    assert tuple(pos_ranges[comm.rank]) == tuple(own_pos), (pos_ranges[comm.rank], own_pos)
     _exchange_slices(comm, [lists], [(f * row, l * row) for f, l in pos_ranges])
     mark("lists exchange")
     count, own_seg = engine.reduce()

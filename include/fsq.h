@@ -174,6 +174,9 @@ int fsq_shard_dp_final(fsq_shard *s, uint32_t *overflow);
 int fsq_shard_grow_cap(fsq_shard *s);
 int fsq_shard_traceback(fsq_shard *s, uint32_t *count, uint32_t *max_segment_size);
 int fsq_shard_get_traceback(const fsq_shard *s, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size);
+/* The traceback positions whose right bound lies in (c0, c1]: the rows of the reduction lists that the rank holding
+ * columns [c0, c1) fills.  The traceback is replicated, so every rank can answer this for every other rank. */
+int fsq_shard_position_range(const fsq_shard *s, uint64_t c0, uint64_t c1, uint32_t *first, uint32_t *last);
 /* Device array [count][width] of (v, #{d > v}) pairs (2 uint32 each) and the rows [own_first, own_last) this rank filled. */
 int fsq_shard_reduce_lists(fsq_shard *s, uint32_t **d_lists, uint32_t *width, uint32_t *own_first, uint32_t *own_last);
 /* Reduced segments: their number and the range [own_first, own_last) whose states this rank holds. */

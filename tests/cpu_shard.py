@@ -180,6 +180,10 @@ class CpuShard:
     def get_traceback(self, count):
         return self.tb
 
+    def position_range(self, c0, c1):
+        rbs = self.tb[1]
+        return int(np.searchsorted(rbs, c0, side="right")), int(np.searchsorted(rbs, c1, side="right"))
+
     def reduce_lists(self, count):
         from founder_sequences_b200.sharded import NotReducible
         if not self.K < self.m:
