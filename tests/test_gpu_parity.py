@@ -169,6 +169,34 @@ def test_segmentation_matches_oracle(ctx, oracle, synth, m, n, L, C, founders):
     assert res is not None
 
 
+@pytest.mark.parametrize("m,n,L,founders,seed", [(1500, 8000, 20, 16, 7), (2500, 6000, 50, 24, 4), (5000, 4000, 50, 32, 3), (8000, 1500, 30, 40, 9)])
+def test_dp_table_with_several_warps_per_block(ctx, oracle, synth, m, n, L, founders, seed):
+    """More rows than one warp's chunks hold: the scan CTA has several warps, and only the last one emits the top
+    lists.  (A missing barrier between that emission and the next step's histogram moves once put single DP entries off
+    by one here while every smaller case passed.)  The whole DP table, K > cap included, against the oracle, twice."""
+    rows = synth.synth_rows(m, n, seed=seed, founders=founders, gaps=True)
+    with oracle.open(rows) as o:
+        assert o.segment(L) == 0
+        odp = o.dp()
+        olb, orb, _, osz = o.reduced()
+        oa, od = o.reduced_states()
+        K = o.K()
+    ctx.set_option("keep_dp", 1)
+    try:
+        for _ in range(2):
+            with ctx.msa_from_rows(rows) as msa, ctx.segment(msa, L) as seg:
+                assert seg.max_segment_size == K
+                for name, x, y in zip(("lb", "rb", "max", "size"), seg.dp_table(n - L + 1), odp):
+                    assert np.array_equal(x, y), "dp %s differs first at entry %d" % (name, int(np.nonzero(x != y)[0][0]))
+                lb, rb, sz = seg.reduced_traceback()
+                assert np.array_equal(lb, olb) and np.array_equal(rb, orb) and np.array_equal(sz, osz)
+                a, d = seg.reduced_pbwt_samples()
+                assert np.array_equal(a, oa) and np.array_equal(d, od)
+        assert ctx.stat("warps") > 1
+    finally:
+        ctx.set_option("keep_dp", 0)
+
+
 @pytest.mark.parametrize("store,kernel", [(0, 0), (1, 0), (-1, 2), (-1, 1)])
 @pytest.mark.parametrize("m,n,L,C", [(200, 3000, 20, 100), (1000, 1500, 20, 128), (1101, 900, 8, 77)])
 def test_segmentation_stored_states_and_rescan(ctx, oracle, synth, store, kernel, m, n, L, C):
