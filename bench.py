@@ -37,6 +37,8 @@ WORKLOADS = {
     "c2s": (1000, 200_000, 20, 16, True, 2, "synthetic 1,000 x 200k (1/5 of config 2), sigma=5, L=20"),
     "c3s": (5000, 1_000_000, 50, 32, True, 3, "synthetic 5,000 x 1M (1/10 of config 3), sigma=5, L=50"),
     "c4s": (2500, 1_000_000, 50, 24, True, 4, "synthetic 2,500 x 1M (1/5 of config 4), L=50"),
+    "c3": (5000, 1_250_000, 50, 32, True, 3, "synthetic 5,000 x 1.25M per GPU (config 3 = 5,000 x 10M at 8 GPUs), sigma=5, L=50"),
+    "c5s": (20000, 250_000, 100, 64, True, 5, "synthetic 20,000 x 250k (1/200 of config 5), L=100"),
 }
 
 

@@ -221,15 +221,26 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 	uint32_t threads = g.n_warps * 32, regs = 64;
 	if (g.chunked)
 	{
-		int64_t e = ctx->opt("chunk", 0);
-		if (9 != e && 17 != e && 33 != e)
-			e = m <= 32 * 9 ? 9 : (m <= 32 * 17 ? 17 : 33);
-		uint32_t const tmax = 9 == e ? 1024 : 512;
-		if ((uint64_t) tmax * e < m) e = 33;
-		g.E = (uint32_t) e;
-		g.T = ((m + g.E - 1) / g.E + 31) / 32 * 32;
+		// Chunk length: a thread's column costs about (14 + E) element times (scans across the chunk summaries, unpacking and
+		// the carry-in fix-up are per thread), and the padding up to whole warps is worked on like real rows.
+		static uint32_t const lengths[] = {
+#define FSQ_LIST(E) E,
+			FSQ_CHUNK_LENGTHS(FSQ_LIST)
+#undef FSQ_LIST
+		};
+		int64_t const want = ctx->opt("chunk", 0);
+		uint64_t best = ~0ull;
+		for (int pass = 0; pass < 2 && ~0ull == best; ++pass)
+			for (uint32_t e : lengths)
+			{
+				if (0 == pass && 0 != want && want != (int64_t) e) continue;
+				uint64_t const t = ((m + e - 1) / e + 31) / 32 * 32;
+				if (t > cblock_thread_limit(e)) continue;
+				uint64_t const cost = t * (14 + e);
+				if (cost < best) { best = cost; g.E = e; g.T = (uint32_t) t; }
+			}
 		threads = g.T;
-		regs = 9 == g.E ? 64 : 128;
+		regs = g.E <= 9 ? 64 : 128;
 	}
 	else if (g.blocked)
 	{
@@ -257,7 +268,7 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 		{
 			// The histogram of pass B grows with the block length, so the footprint depends on the answer: take the largest
 			// number of resident CTAs whose own block length fits (every CTA also reserves 1 KB of shared memory).
-			per_sm = std::min <uint64_t>(per_sm, 65536 / ((uint64_t) threads * (9 == g.E ? 64 : 128)));
+			per_sm = std::min <uint64_t>(per_sm, 65536 / ((uint64_t) threads * regs));
 			for (; per_sm > 1; --per_sm)
 			{
 				block_args P;
@@ -291,9 +302,10 @@ cudaError_t launch_scan(block_args const &A, uint32_t n_blocks, geometry const &
 	{
 		switch (g.E)
 		{
-			case 9: return launch_cblock_e9(A, n_blocks, g.T, g.ns, hist, st);
-			case 17: return launch_cblock_e17(A, n_blocks, g.T, g.ns, hist, st);
-			default: return launch_cblock_e33(A, n_blocks, g.T, g.ns, hist, st);
+#define FSQ_CASE(E) case E: return launch_cblock_e##E(A, n_blocks, g.T, g.ns, hist, st);
+			FSQ_CHUNK_LENGTHS(FSQ_CASE)
+#undef FSQ_CASE
+			default: return cudaErrorInvalidConfiguration;
 		}
 	}
 	if (!g.blocked) return launch_block(A, n_blocks, g.n_warps, g.tpw, hist, st);
@@ -1858,6 +1870,9 @@ int fsq_shard_reduce(fsq_shard *P, uint32_t *count, uint32_t *own_first, uint32_
 	ctx->stats["cap"] = P->cap;
 	ctx->stats["block_columns"] = P->S.g.C;
 	ctx->stats["blocks"] = P->S.g.B;
+	ctx->stats["warps"] = (P->S.g.blocked || P->S.g.chunked) ? P->S.g.T / 32 : P->S.g.n_warps;
+	ctx->stats["chunk"] = (P->S.g.blocked || P->S.g.chunked) ? P->S.g.E : 0;
+	ctx->stats["kernel"] = P->S.g.chunked ? 3 : (P->S.g.blocked ? 2 : 1);
 	return FSQ_OK;
 }
 

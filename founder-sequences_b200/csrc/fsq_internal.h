@@ -88,9 +88,12 @@ inline size_t cblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uin
 	if (hist) t += r16(sizeof(uint32_t) * ((size_t) A.m + A.C + 8));
 	return t;
 }
-cudaError_t launch_cblock_e9(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
-cudaError_t launch_cblock_e17(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
-cudaError_t launch_cblock_e33(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
+// One translation unit per chunk length (fsq_cscan_e*.cu).
+#define FSQ_CHUNK_LENGTHS(X) X(9) X(13) X(17) X(21) X(25) X(27) X(29) X(31) X(33)
+#define FSQ_DECLARE_CBLOCK(E) cudaError_t launch_cblock_e##E(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
+FSQ_CHUNK_LENGTHS(FSQ_DECLARE_CBLOCK)
+#undef FSQ_DECLARE_CBLOCK
+inline uint32_t cblock_thread_limit(uint32_t E) { return E <= 9 ? 1024 : 512; }       // cblock_max_threads(), fsq_cscan.inc
 cudaError_t launch_prep(uint32_t const *st_d, uint32_t m, uint16_t *code, uint32_t *oldvals, uint32_t *R, uint32_t first_block, uint32_t n_blocks, cudaStream_t st);
 
 struct stitch_item

@@ -8,7 +8,7 @@ import oraclelib
 fsq, synth = load_package(), load_synth()
 orc = oraclelib.oracle()
 ctx = fsq.Context(0)
-for (m, n, L, F, seed) in [(2500, 6000, 5, 24, 4), (2500, 6000, 50, 24, 4), (5000, 4000, 50, 32, 3), (1500, 8000, 20, 16, 7), (8000, 1500, 30, 40, 9)]:
+for (m, n, L, F, seed) in [(2500, 6000, 5, 24, 4), (2500, 6000, 50, 24, 4), (5000, 4000, 50, 32, 3), (1500, 8000, 20, 16, 7), (8000, 1500, 30, 40, 9), (2500, 3000, 50, 24, 5), (20000, 1200, 100, 64, 11)]:
     rows = synth.synth_rows(m, n, seed=seed, founders=F, gaps=True)
     with orc.open(rows) as o:
         assert o.segment(L) == 0

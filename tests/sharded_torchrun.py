@@ -24,7 +24,7 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     fsq, sh, synth = load_package(), load_sharded(), load_synth()
     comm = sh.TorchComm()
-    for m, n, L, C in [(64, 4000, 10, 96), (1000, 6000, 20, 0), (300, 2500, 7, 50)]:
+    for m, n, L, C in [(64, 4000, 10, 96), (1000, 6000, 20, 0), (300, 2500, 7, 50), (2500, 4000, 30, 0), (5000, 3200, 50, 0)]:
         rows = synth.synth_rows(m, n, seed=m + L, founders=8, gaps=True)
         c0, c1 = sh.split_columns(n, world)[rank]
         ctx = fsq.Context(local)

@@ -89,7 +89,7 @@ def check_against_oracle(oracle, rows, L, results):
 
 
 @pytest.mark.parametrize("parts", [1, 2, 3, 5])
-@pytest.mark.parametrize("m,n,L,C", [(48, 3000, 10, 96), (200, 2600, 20, 100), (1000, 1800, 8, 0)])
+@pytest.mark.parametrize("m,n,L,C", [(48, 3000, 10, 96), (200, 2600, 20, 100), (1000, 1800, 8, 0), (2500, 1500, 30, 0)])
 def test_sharded_matches_oracle(fsq, oracle, synth, parts, m, n, L, C):
     rows = synth.synth_rows(m, n, seed=m + L + parts, founders=7, gaps=True)
     opts = {"block_columns": C} if C else {}
