@@ -216,7 +216,7 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 	g.sym0 = lo;
 	g.ns = hi - lo + 1;
 	int64_t const kern = ctx->opt("kernel", 0);        // 0 auto, 1 striped, 2 blocked, 3 chunked
-	g.chunked = (0 == kern || 3 == kern) && g.ns <= 8 && m <= 512u * 33u;
+	g.chunked = (0 == kern || 3 == kern) && g.ns <= 8 && m <= cblock_thread_limit(53) * 53u;
 	g.blocked = !g.chunked && (1 != kern) && g.ns <= 8 && m <= 448u * 33u;
 	uint32_t threads = g.n_warps * 32, regs = 64;
 	if (g.chunked)
@@ -236,11 +236,13 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 				if (0 == pass && 0 != want && want != (int64_t) e) continue;
 				uint64_t const t = ((m + e - 1) / e + 31) / 32 * 32;
 				if (t > cblock_thread_limit(e)) continue;
-				uint64_t const cost = t * (14 + e);
+				// E = 53 exists for row counts the others cannot hold: 168 registers with a few spills and a loop body beyond the
+				// instruction cache make it ~1.4 times slower per element than the model says (5,000 rows, measured)
+				uint64_t const cost = t * (14 + e) * (e > 33 ? 3 : 2);
 				if (cost < best) { best = cost; g.E = e; g.T = (uint32_t) t; }
 			}
 		threads = g.T;
-		regs = g.E <= 9 ? 64 : 128;
+		regs = cblock_registers(g.E);
 	}
 	else if (g.blocked)
 	{
@@ -286,6 +288,16 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 		C = (int64_t) ((msa->n + resident - 1) / resident);
 		C = std::max <int64_t>(C, 64);
 		C = std::min <int64_t>(C, 4096);
+		if (g.chunked)
+		{
+			// one CTA per SM and still too large (many rows): the histogram has one counter per row and per column of the block
+			block_args P;
+			memset(&P, 0, sizeof P);
+			P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m; P.C = 0;
+			size_t const fixed = cblock_smem_bytes(P, g.T, g.E, g.ns, true) + 1024;
+			size_t const room = (size_t) ctx->prop.sharedMemPerBlockOptin > fixed ? ((size_t) ctx->prop.sharedMemPerBlockOptin - fixed) / 4 : 0;
+			if ((size_t) C > room) C = (int64_t) std::max <size_t>(room, 1);
+		}
 	}
 	C = std::min <int64_t>(C, 65534 - (int64_t) m - 2);
 	C = std::max <int64_t>(C, 1);
@@ -1378,8 +1390,14 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 	geometry const &g = P->S.g;
 
 	// ---- pass B + DP; the top-list bound grows until the DP proves the result exact ----
-	int64_t const max_rounds = std::max <int64_t>(2, ctx->opt("dp_max_rounds", 16));
-	int64_t const guess_rounds = ctx->opt("dp_guess_rounds", 8);      // after these the table is left to settle by itself
+	// A round costs one chain's length of sequential work, the single-chain fallback as much as n_chunks rounds (and round r
+	// leaves the first r chains exact, so n_chunks rounds always suffice): give up on the rounds only after half of that.
+	// Slowly rising levels (thousands of distinct rows per segment) take 15-20 rounds where config 2 takes two.
+	int64_t max_rounds = ctx->opt("dp_max_rounds", 0);
+	if (max_rounds <= 0) max_rounds = std::max <int64_t>(16, P->n_chunks / 2);
+	max_rounds = std::max <int64_t>(2, max_rounds);
+	int64_t guess_rounds = ctx->opt("dp_guess_rounds", -1);           // after these the table is left to settle by itself
+	if (guess_rounds < 0) guess_rounds = max_rounds;
 	while (true)
 	{
 		if ((rc = shard_scan(P))) return rc;

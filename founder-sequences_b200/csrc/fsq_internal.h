@@ -89,11 +89,14 @@ inline size_t cblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uin
 	return t;
 }
 // One translation unit per chunk length (fsq_cscan_e*.cu).
-#define FSQ_CHUNK_LENGTHS(X) X(9) X(13) X(17) X(21) X(25) X(27) X(29) X(31) X(33)
+#define FSQ_CHUNK_LENGTHS(X) X(9) X(13) X(17) X(21) X(25) X(27) X(29) X(31) X(33) X(53)
 #define FSQ_DECLARE_CBLOCK(E) cudaError_t launch_cblock_e##E(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
 FSQ_CHUNK_LENGTHS(FSQ_DECLARE_CBLOCK)
 #undef FSQ_DECLARE_CBLOCK
-inline uint32_t cblock_thread_limit(uint32_t E) { return E <= 9 ? 1024 : 512; }       // cblock_max_threads(), fsq_cscan.inc
+// Threads per CTA are bounded so that the unrolled chunk (2 E registers and the running maxima) fits the register file:
+// 64 registers per thread up to E = 9, 128 up to 33, 168 at 53 (which reaches 20,352 rows).
+constexpr uint32_t cblock_thread_limit(uint32_t E) { return E <= 9 ? 1024 : (E <= 33 ? 512 : 384); }
+constexpr uint32_t cblock_registers(uint32_t E) { return E <= 9 ? 64 : (E <= 33 ? 128 : 168); }
 cudaError_t launch_prep(uint32_t const *st_d, uint32_t m, uint16_t *code, uint32_t *oldvals, uint32_t *R, uint32_t first_block, uint32_t n_blocks, cudaStream_t st);
 
 struct stitch_item

@@ -330,10 +330,12 @@ def entry_range(c0, c1, n, L):
     return first, last
 
 
-def segment_sharded(engine, comm, max_rounds=16, guess_rounds=8, want_states=True, want_traceback=True, want_bounds=True):
+def segment_sharded(engine, comm, max_rounds=64, guess_rounds=None, want_states=True, want_traceback=True, want_bounds=True):
     """Run the long path over the column shards held by the ranks of `comm`; `engine` is this rank's shard.
     Raises NotReducible when K == m (generate_context.cc:192-200)."""
     res = ShardedResult()
+    if guess_rounds is None:
+        guess_rounds = max_rounds           # a round is cheap, the take-turns fallback is not (fsq_segment's rule)
     dev = getattr(engine, "device", torch.device("cpu"))
     trace = [] if os.environ.get("FSQ_SHARD_TRACE") else None
     t_prev = [time.perf_counter()]

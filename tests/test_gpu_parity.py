@@ -169,7 +169,8 @@ def test_segmentation_matches_oracle(ctx, oracle, synth, m, n, L, C, founders):
     assert res is not None
 
 
-@pytest.mark.parametrize("m,n,L,founders,seed", [(1500, 8000, 20, 16, 7), (2500, 6000, 50, 24, 4), (5000, 4000, 50, 32, 3), (8000, 1500, 30, 40, 9)])
+@pytest.mark.parametrize("m,n,L,founders,seed", [(1500, 8000, 20, 16, 7), (2500, 6000, 50, 24, 4), (5000, 4000, 50, 32, 3), (8000, 1500, 30, 40, 9),
+                                                    (20000, 1200, 100, 64, 11)])
 def test_dp_table_with_several_warps_per_block(ctx, oracle, synth, m, n, L, founders, seed):
     """More rows than one warp's chunks hold: the scan CTA has several warps, and only the last one emits the top
     lists.  (A missing barrier between that emission and the next step's histogram moves once put single DP entries off
