@@ -38,6 +38,10 @@ WORKLOADS = {
     "c3s": (5000, 1_000_000, 50, 32, True, 3, "synthetic 5,000 x 1M (1/10 of config 3), sigma=5, L=50"),
     "c4s": (2500, 1_000_000, 50, 24, True, 4, "synthetic 2,500 x 1M (1/5 of config 4), L=50"),
     "c3": (5000, 1_250_000, 50, 32, True, 3, "synthetic 5,000 x 1.25M per GPU (config 3 = 5,000 x 10M at 8 GPUs), sigma=5, L=50"),
+    "c4": (2500, 5_000_000, 50, 24, True, 4, "synthetic 2,500 x 5M (config 4), L=50"),
+    "c4_L5": (2500, 5_000_000, 5, 24, True, 4, "synthetic 2,500 x 5M (config 4), L=5"),
+    "c4_L10": (2500, 5_000_000, 10, 24, True, 4, "synthetic 2,500 x 5M (config 4), L=10"),
+    "c4_L200": (2500, 5_000_000, 200, 24, True, 4, "synthetic 2,500 x 5M (config 4), L=200"),
     "c5s": (20000, 250_000, 100, 64, True, 5, "synthetic 20,000 x 250k (1/200 of config 5), L=100"),
 }
 

@@ -287,7 +287,7 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 		uint64_t const resident = (uint64_t) ctx->prop.multiProcessorCount * per_sm;
 		C = (int64_t) ((msa->n + resident - 1) / resident);
 		C = std::max <int64_t>(C, 64);
-		C = std::min <int64_t>(C, 4096);
+		int64_t c_max = std::min <int64_t>(4096, 65534 - (int64_t) m - 2);
 		if (g.chunked)
 		{
 			// one CTA per SM and still too large (many rows): the histogram has one counter per row and per column of the block
@@ -296,7 +296,17 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 			P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m; P.C = 0;
 			size_t const fixed = cblock_smem_bytes(P, g.T, g.E, g.ns, true) + 1024;
 			size_t const room = (size_t) ctx->prop.sharedMemPerBlockOptin > fixed ? ((size_t) ctx->prop.sharedMemPerBlockOptin - fixed) / 4 : 0;
-			if ((size_t) C > room) C = (int64_t) std::max <size_t>(room, 1);
+			c_max = std::min <int64_t>(c_max, (int64_t) std::max <size_t>(room, 1));
+		}
+		if (C > c_max)
+		{
+			// More columns than one resident wave of the longest blocks holds: whole waves of equal blocks, not blocks of
+			// the maximal length whose last wave fills a part of the SMs (2,500 x 5M: 1,221 blocks of 4,096 columns on 740
+			// resident CTAs = 1.65 waves; 1,480 blocks of 3,379 columns are two full ones).
+			c_max = std::max <int64_t>(c_max, 1);
+			uint64_t const waves = (msa->n + resident * (uint64_t) c_max - 1) / (resident * (uint64_t) c_max);
+			C = (int64_t) ((msa->n + waves * resident - 1) / (waves * resident));
+			if (0 != ctx->opt("whole_waves", 1)) C = std::min <int64_t>(C, c_max); else C = c_max;
 		}
 	}
 	C = std::min <int64_t>(C, 65534 - (int64_t) m - 2);
@@ -1183,7 +1193,7 @@ int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
 		}
 		return FSQ_OK;
 	}
-	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", nullptr};
+	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", "whole_waves", nullptr};
 	for (char const **k = known; *k; ++k)
 		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }
 	return fail(ctx, FSQ_ERR_ARG, "unknown option '%s'", key);

@@ -42,9 +42,8 @@ def _digest(seg):
     return (seg.max_segment_size, lb.tobytes(), rb.tobytes(), sz.tobytes(), zlib.crc32(a.tobytes()), zlib.crc32(d.tobytes()))
 
 
-def test_config2_full_size(ctx, oracle, synth):
-    m, n, L, F, seed = 1000, 1000000, 20, 16, 2
-    P = 30000                                   # prefix the oracle runs
+def _full_size_case(ctx, oracle, synth, m, n, L, F, seed, P, variants):
+    """P = length of the prefix the oracle runs; variants = option sets whose result must have the same bytes."""
     msa = ctx.msa_synth(m, n, seed, F, True)
     try:
         ctx.set_option("keep_dp", 1)
@@ -79,8 +78,9 @@ def test_config2_full_size(ctx, oracle, synth):
                 cnt = P - 2 * L + 1                                      # entries whose column lies inside the prefix
                 assert np.array_equal(dlb[:cnt], olb[:cnt]) and np.array_equal(drb[:cnt], orb[:cnt])
                 assert np.array_equal(dmx[:cnt], omx[:cnt]) and np.array_equal(dsz[:cnt], osz[:cnt])
-                oa, od = o.scan_dump(2000, hist=False)
-            cols = np.array([1, 2, 451, 452, 999, 2000], np.uint64)
+                n_dump = min(2000, P)
+                oa, od = o.scan_dump(n_dump, hist=False)
+            cols = np.array([c for c in (1, 2, 451, 452, 999, 2000) if c <= n_dump], np.uint64)
             ga, gd = ctx.pbwt_states(msa, cols)
             for i, c in enumerate(cols):
                 assert np.array_equal(ga[i], oa[int(c) - 1]) and np.array_equal(gd[i], od[int(c) - 1])
@@ -88,7 +88,7 @@ def test_config2_full_size(ctx, oracle, synth):
             seg.free()
 
         # ---- invariance under the decomposition ----
-        for opts in ({"block_columns": 1000}, {"dp_chunks": 37}, {"store_states": 0}, {"stitch_sort": 0, "block_columns": 333}):
+        for opts in variants:
             for k, v in opts.items():
                 ctx.set_option(k, v)
             try:
@@ -99,3 +99,30 @@ def test_config2_full_size(ctx, oracle, synth):
                     ctx.set_option(k, {"block_columns": 0, "dp_chunks": 0, "store_states": -1, "stitch_sort": 1}[k])
     finally:
         msa.free()
+
+
+def test_config2_full_size(ctx, oracle, synth):
+    _full_size_case(ctx, oracle, synth, 1000, 1000000, 20, 16, 2, 30000,
+                    ({"block_columns": 1000}, {"dp_chunks": 37}, {"store_states": 0}, {"stitch_sort": 0, "block_columns": 333}))
+
+
+# Config 4 (BASELINE.json: segment-length-bound sweep on 2,500 x 5M; SURVEY.md section 8d: F = 24, seed 4): L = 50 and
+# 200 at the full 5M columns; L = 5 and 10 at 1M columns, where the reduced states the test reads back (segments x m x
+# 8 B on the host) stay below 4 GB.  Three warps per scan CTA (chunk length 27), DP wavefronts of 5 .. 16 columns.
+@pytest.mark.parametrize("n,L", [(5_000_000, 50), (5_000_000, 200), (1_000_000, 5), (1_000_000, 10)])
+def test_config4_length_bound_sweep(ctx, oracle, synth, n, L):
+    _full_size_case(ctx, oracle, synth, 2500, n, L, 24, 4, 12000,
+                    ({"block_columns": 700}, {"dp_chunks": 37}, {"store_states": 0}))
+
+
+# Config 3's share of one GPU at 8 GPUs (5,000 x 1.25M, L = 50; the column-sharded whole is tests/sharded_torchrun.py)
+def test_config3_one_gpu_share(ctx, oracle, synth):
+    _full_size_case(ctx, oracle, synth, 5000, 1_250_000, 50, 32, 3, 6000,
+                    ({"block_columns": 900}, {"dp_chunks": 37}, {"store_states": 0}))
+
+
+# Config 5's rows (20,000, L = 100, F = 64, seed 5) on a 250k-column slice: chunk length 53, one CTA per SM, K in the
+# thousands (cap 8,128) and about 15 DP rounds.  The full 50M columns are open.
+def test_config5_rows_slice(ctx, oracle, synth):
+    _full_size_case(ctx, oracle, synth, 20000, 250_000, 100, 64, 5, 3000,
+                    ({"dp_chunks": 37}, {"store_states": 0}))
