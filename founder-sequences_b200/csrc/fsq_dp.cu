@@ -221,7 +221,10 @@ __device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list
 // few hundred entries at most on real data; anything older is read from global memory), every result is written
 // through to global memory for the other chains and the later stages, and the head of the next wavefront's top lists
 // is loaded while the current one is computed.  One warp per column of the wavefront.
-__global__ void __launch_bounds__(512) dp_chain_kernel(dp_args const A)
+#ifndef FSQ_DP_MIN_CTAS
+#define FSQ_DP_MIN_CTAS 2
+#endif
+__global__ void __launch_bounds__(512, FSQ_DP_MIN_CTAS) dp_chain_kernel(dp_args const A)
 {
 	__shared__ uint32_t sM[DP_RING];
 	__shared__ unsigned long long smk[DP_RING];
