@@ -81,6 +81,7 @@ struct fsq_msa
 {
 	fsq_ctx *ctx{};
 	uint8_t *cols{};
+	size_t cols_bytes{};       // 0: from cudaMalloc; else the size of the block taken from the context's cache
 	uint64_t col_stride{};
 	uint32_t m{}, nsym{};
 	uint32_t sym_mask{};       // bit c set: comp value c occurs in some row
@@ -1101,6 +1102,8 @@ int check_shape(fsq_ctx *ctx, fsq_msa const *msa)
 	return FSQ_OK;
 }
 
+constexpr unsigned long long FSQ_MSA_CACHE_LIMIT = 4ull << 30;
+
 int new_msa(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint32_t nsym, fsq_msa **out)
 {
 	if (!ctx || !out) return fail(ctx, FSQ_ERR_ARG, "null argument");
@@ -1110,12 +1113,24 @@ int new_msa(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint32_t nsym, 
 	msa->ctx = ctx; msa->m = m; msa->n = n; msa->col0 = col0; msa->nsym = nsym;
 	msa->col_stride = (((uint64_t) m + 1) / 2 + 15) & ~15ull;
 	unsigned long long const bytes = msa->col_stride * n;
-	cudaError_t e = cudaMalloc(&msa->cols, bytes);
-	if (cudaErrorMemoryAllocation == e)
+	// Alignments of a few GB come from (and return to) the context's cache, so that a caller that uploads one alignment
+	// after another pays no cudaMalloc / cudaFree (each synchronises the device) per call; larger ones are not kept.
+	cudaError_t e;
+	if (bytes <= FSQ_MSA_CACHE_LIMIT)
 	{
-		cudaGetLastError();
-		ctx->trim(false);        // give the workspace cache back and try once more
+		void *p = nullptr;
+		e = ctx->take(false, bytes, &p, &msa->cols_bytes);        // trims the cache and retries when memory is short
+		msa->cols = static_cast <uint8_t *>(p);
+	}
+	else
+	{
 		e = cudaMalloc(&msa->cols, bytes);
+		if (cudaErrorMemoryAllocation == e)
+		{
+			cudaGetLastError();
+			ctx->trim(false);        // give the workspace cache back and try once more
+			e = cudaMalloc(&msa->cols, bytes);
+		}
 	}
 	if (cudaSuccess != e)
 	{
@@ -1337,7 +1352,10 @@ void fsq_msa_free(fsq_msa *msa)
 {
 	if (!msa) return;
 	if (msa->ctx) cudaSetDevice(msa->ctx->device);
-	cudaFree(msa->cols);
+	if (msa->cols_bytes && msa->ctx)
+		msa->ctx->give(false, msa->cols, msa->cols_bytes);      // work that reads it is ordered before any reuse: one stream
+	else
+		cudaFree(msa->cols);
 	delete msa;
 }
 
