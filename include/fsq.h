@@ -72,6 +72,8 @@ int fsq_msa_synth(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint64_t 
 /* The same cells as ASCII rows (row-major m × n) into a device buffer, for end-to-end runs that start from host rows. */
 int fsq_synth_rows_device(fsq_ctx *ctx, uint8_t *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps);
 
+/* Must run before fsq_destroy() of the context that made the alignment: packed alignments of up to 4 GB return to the
+ * context's buffer cache (reused by the next upload on that context, released by fsq_destroy or when memory runs short). */
 void fsq_msa_free(fsq_msa *msa);
 uint32_t fsq_msa_rows(const fsq_msa *msa);
 uint64_t fsq_msa_columns(const fsq_msa *msa);
