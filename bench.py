@@ -38,6 +38,9 @@ WORKLOADS = {
     "c3s": (5000, 1_000_000, 50, 32, True, 3, "synthetic 5,000 x 1M (1/10 of config 3), sigma=5, L=50"),
     "c4s": (2500, 1_000_000, 50, 24, True, 4, "synthetic 2,500 x 1M (1/5 of config 4), L=50"),
     "c3": (5000, 1_250_000, 50, 32, True, 3, "synthetic 5,000 x 1.25M per GPU (config 3 = 5,000 x 10M at 8 GPUs), sigma=5, L=50"),
+    "c3_n4": (5000, 2_500_000, 50, 32, True, 3, "synthetic 5,000 x 2.5M per GPU (config 3 = 5,000 x 10M at 4 GPUs), sigma=5, L=50"),
+    "c3_n2": (5000, 5_000_000, 50, 32, True, 3, "synthetic 5,000 x 5M per GPU (config 3 = 5,000 x 10M at 2 GPUs), sigma=5, L=50"),
+    "c3_whole": (5000, 10_000_000, 50, 32, True, 3, "synthetic 5,000 x 10M (config 3 whole on one GPU), sigma=5, L=50"),
     "c4": (2500, 5_000_000, 50, 24, True, 4, "synthetic 2,500 x 5M (config 4), L=50"),
     "c4_L5": (2500, 5_000_000, 5, 24, True, 4, "synthetic 2,500 x 5M (config 4), L=5"),
     "c4_L10": (2500, 5_000_000, 10, 24, True, 4, "synthetic 2,500 x 5M (config 4), L=10"),
