@@ -1455,7 +1455,17 @@ int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation *
 		else if ((rc = shard_dp_final(P, &ovf))) return rc;
 		if (0 == ovf) break;
 		if (P->cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list at column %u with cap = m", ovf - 1);
-		P->cap = (uint32_t) std::min <uint64_t>(m, (uint64_t) P->cap * 4);
+		uint64_t next = std::min <uint64_t>(m, (uint64_t) P->cap * 4);
+		{
+			// four times the refused bound unless the lists of that length do not fit: then twice (config 3 whole on one
+			// GPU: 127 -> 508 -> 2,032 would be 163 GB of lists next to 25 GB of alignment; 1,016 is enough and fits)
+			size_t free_b = 0, total_b = 0;
+			CK(cudaMemGetInfo(&free_b, &total_b));
+			size_t avail = free_b + P->toplist.bytes;
+			for (auto const &blk : ctx->dev_cache) avail += blk.bytes;
+			while (next / 2 > P->cap && (size_t) n * (next + 1) * sizeof(uint2) + ((size_t) 1 << 30) > avail) next /= 2;
+		}
+		P->cap = (uint32_t) next;
 		ctx->opts["cap"] = P->cap;          // later calls on this context start from the bound that worked
 		ctx->stats["cap_retries"] += 1;
 	}
