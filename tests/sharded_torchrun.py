@@ -14,6 +14,9 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
+CASES = [(64, 4000, 10, 96), (1000, 6000, 20, 0), (300, 2500, 7, 50), (2500, 4000, 30, 0), (5000, 3200, 50, 0)]
+
+
 def main():
     import torch
     import torch.distributed as dist
@@ -24,7 +27,7 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     fsq, sh, synth = load_package(), load_sharded(), load_synth()
     comm = sh.TorchComm()
-    for m, n, L, C in [(64, 4000, 10, 96), (1000, 6000, 20, 0), (300, 2500, 7, 50), (2500, 4000, 30, 0), (5000, 3200, 50, 0)]:
+    for m, n, L, C in CASES:
         rows = synth.synth_rows(m, n, seed=m + L, founders=8, gaps=True)
         c0, c1 = sh.split_columns(n, world)[rank]
         ctx = fsq.Context(local)
@@ -51,6 +54,8 @@ def main():
         assert owns[0][0] == 0 and owns[-1][1] == len(olb) and all(owns[i][1] == owns[i + 1][0] for i in range(world - 1))
         if rank == 0:
             print("sharded ok: %d x %d, L = %d over %d ranks: K = %d, %d segments, %d DP rounds" % (m, n, L, world, res.K, len(olb), res.dp_rounds))
+    if rank == 0:
+        print("sharded all ok %d" % len(CASES))
     dist.destroy_process_group()
 
 

@@ -131,4 +131,7 @@ def test_sharded_under_torchrun_nccl():
            "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(here, "sharded_torchrun.py")]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:]
-    assert r.stdout.count("sharded ok") == 3, r.stdout[-3000:]
+    sys.path.insert(0, here)
+    from sharded_torchrun import CASES
+    assert r.stdout.count("sharded ok:") == len(CASES), r.stdout[-3000:]
+    assert "sharded all ok %d" % len(CASES) in r.stdout, r.stdout[-3000:]
