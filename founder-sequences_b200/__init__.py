@@ -31,10 +31,9 @@ EXPORTS = [
     "fsq_segmentation_count", "fsq_segmentation_max_segment_size", "fsq_segmentation_bounds",
     "fsq_segmentation_states", "fsq_segmentation_states_view", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
     "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights",
-    "fsq_msa_set_first_column", "fsq_shard_create", "fsq_shard_free", "fsq_shard_local_summary", "fsq_shard_set_start",
-    "fsq_shard_scan", "fsq_shard_dp_table", "fsq_shard_dp_round", "fsq_shard_dp_sync", "fsq_shard_dp_single_chain",
-    "fsq_shard_dp_final", "fsq_shard_grow_cap", "fsq_shard_traceback", "fsq_shard_get_traceback", "fsq_shard_position_range",
-    "fsq_shard_reduce_lists", "fsq_shard_reduce", "fsq_shard_bounds", "fsq_shard_states",
+    "fsq_msa_set_first_column", "fsq_shard_columns", "fsq_comm_unique_id", "fsq_comm_create", "fsq_comm_adopt_nccl",
+    "fsq_local_group_create", "fsq_local_group_free", "fsq_comm_create_local", "fsq_comm_free", "fsq_comm_rank", "fsq_comm_size",
+    "fsq_segment_sharded", "fsq_segmentation_own_range",
 ]
 
 
@@ -94,24 +93,18 @@ def load_library():
     proto("fsq_pair_weights", ci, [vp, vp, u32, vp, C.POINTER(u32), C.POINTER(u32)])
     pu32, pu64 = C.POINTER(u32), C.POINTER(u64)
     proto("fsq_msa_set_first_column", ci, [vp, u64])
-    proto("fsq_shard_create", ci, [vp, vp, u64, u64, pp])
-    proto("fsq_shard_free", None, [vp])
-    proto("fsq_shard_local_summary", ci, [vp, pp, pp])
-    proto("fsq_shard_set_start", ci, [vp, vp, vp, vp, u32])
-    proto("fsq_shard_scan", ci, [vp])
-    proto("fsq_shard_dp_table", ci, [vp, pp, pp, pp, pu64, pu64, pu64])
-    proto("fsq_shard_dp_round", ci, [vp, pu32, pu32])
-    proto("fsq_shard_dp_sync", ci, [vp, ci, u32])
-    proto("fsq_shard_dp_single_chain", ci, [vp])
-    proto("fsq_shard_dp_final", ci, [vp, pu32])
-    proto("fsq_shard_grow_cap", ci, [vp])
-    proto("fsq_shard_traceback", ci, [vp, pu32, pu32])
-    proto("fsq_shard_get_traceback", ci, [vp, vp, vp, vp, vp])
-    proto("fsq_shard_position_range", ci, [vp, u64, u64, pu32, pu32])
-    proto("fsq_shard_reduce_lists", ci, [vp, pp, pu32, pu32, pu32])
-    proto("fsq_shard_reduce", ci, [vp, pu32, pu32, pu32])
-    proto("fsq_shard_bounds", ci, [vp, vp, vp, vp])
-    proto("fsq_shard_states", ci, [vp, vp, vp])
+    proto("fsq_shard_columns", ci, [u64, ci, ci, pu64, pu64])
+    proto("fsq_comm_unique_id", ci, [vp])
+    proto("fsq_comm_create", ci, [vp, vp, ci, ci, pp])
+    proto("fsq_comm_adopt_nccl", ci, [vp, vp, ci, ci, pp])
+    proto("fsq_local_group_create", ci, [ci, pp])
+    proto("fsq_local_group_free", None, [vp])
+    proto("fsq_comm_create_local", ci, [vp, vp, ci, pp])
+    proto("fsq_comm_free", None, [vp])
+    proto("fsq_comm_rank", ci, [vp])
+    proto("fsq_comm_size", ci, [vp])
+    proto("fsq_segment_sharded", ci, [vp, vp, vp, u64, u64, pp])
+    proto("fsq_segmentation_own_range", ci, [vp, pu32, pu32])
     _lib = lib
     return lib
 
@@ -194,9 +187,14 @@ class Context:
         self.check(self.lib.fsq_pbwt_states(self.h, msa.h, _p(cols), len(cols), _p(a), _p(d)))
         return a, d
 
-    def segment(self, msa, segment_length_bound):
+    def segment(self, msa, segment_length_bound, comm=None, n_total=None):
+        """The long path.  With a communicator (sharded.Comm): msa holds this rank's columns of an alignment of n_total
+        columns (fsq_segment_sharded); every rank of the communicator makes the same call."""
         h = C.c_void_p()
-        rc = self.lib.fsq_segment(self.h, msa.h, segment_length_bound, C.byref(h))
+        if comm is None:
+            rc = self.lib.fsq_segment(self.h, msa.h, segment_length_bound, C.byref(h))
+        else:
+            rc = self.lib.fsq_segment_sharded(self.h, msa.h, comm.h, n_total, segment_length_bound, C.byref(h))
         if rc == ERR_NOT_REDUCIBLE and h:
             seg = Segmentation(self, h, msa.m)
             err = FsqError(rc, self.lib.fsq_last_error(self.h).decode())
@@ -237,6 +235,9 @@ class Segmentation:
         lib = ctx.lib
         self.max_segment_size = lib.fsq_segmentation_max_segment_size(h)
         self.count = lib.fsq_segmentation_count(h)
+        f, l = C.c_uint32(), C.c_uint32()
+        lib.fsq_segmentation_own_range(h, C.byref(f), C.byref(l))
+        self.own = (f.value, l.value)       # the reduced segments whose states this handle holds (all, on one GPU)
 
     def free(self):
         if self.h:
@@ -257,8 +258,9 @@ class Segmentation:
         return lb, rb, sz
 
     def reduced_pbwt_samples(self):
-        a = np.zeros((self.count, self.m), np.uint32)
-        d = np.zeros((self.count, self.m), np.uint32)
+        cnt = self.own[1] - self.own[0]
+        a = np.zeros((cnt, self.m), np.uint32)
+        d = np.zeros((cnt, self.m), np.uint32)
         self.ctx.check(self.ctx.lib.fsq_segmentation_states(self.h, _p(a), _p(d)))
         return a, d
 
@@ -266,7 +268,9 @@ class Segmentation:
         """Zero-copy views of the handle's pinned host buffers (valid until free())."""
         pa, pd = C.c_void_p(), C.c_void_p()
         self.ctx.check(self.ctx.lib.fsq_segmentation_states_view(self.h, C.byref(pa), C.byref(pd)))
-        shape = (self.count, self.m)
+        shape = (self.own[1] - self.own[0], self.m)
+        if 0 == shape[0]:
+            return np.zeros(shape, np.uint32), np.zeros(shape, np.uint32)
         a = np.ctypeslib.as_array(C.cast(pa, C.POINTER(C.c_uint32)), shape)
         d = np.ctypeslib.as_array(C.cast(pd, C.POINTER(C.c_uint32)), shape)
         return a, d

@@ -2,6 +2,7 @@
 // There is no CPU fallback anywhere in this file: every compute entry point launches the CUDA kernels or fails.
 #include "../../include/fsq.h"
 #include "fsq_internal.h"
+#include "fsq_comm.h"
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
@@ -9,8 +10,10 @@
 #include <cstring>
 #include <chrono>
 #include <map>
+#include <memory>
 #include <new>
 #include <string>
+#include <tuple>
 #include <vector>
 
 using namespace fsq;
@@ -34,6 +37,14 @@ struct fsq_ctx
 	std::vector <std::pair <std::string, std::pair <cudaEvent_t, cudaEvent_t>>> pending;   // phase timers
 	cudaEvent_t timer_ev[2]{nullptr, nullptr};   // option "timer": 1 records the start, 0 the stop, on the context's stream ("ms_timer")
 	cudaEvent_t call_start{nullptr};       // recorded at the entry of fsq_segment: phases report their offset from it ("at_<phase>")
+
+	// what calls on a shape (m, n, L) have learned: the top-list bound that proved exact.  The option "cap" stays the caller's.
+	std::map <std::tuple <uint32_t, uint64_t, uint64_t>, uint32_t> learned_cap;
+
+	// ... and the memory plan agreed for (m, n, L, bound, ranks, local columns, blocks, block length, option store_states):
+	// {one window, states kept, blocks per window}
+	struct mem_plan { bool whole, keep; uint32_t per_window; };
+	std::map <std::tuple <uint32_t, uint64_t, uint64_t, uint32_t, int, uint64_t, uint32_t, uint32_t, int64_t>, mem_plan> plans;
 
 	int64_t opt(char const *k, int64_t dflt) const { auto it = opts.find(k); return opts.end() == it ? dflt : it->second; }
 
@@ -88,19 +99,40 @@ struct fsq_msa
 	uint64_t n{}, col0{};
 };
 
+// RAII workspace buffers (device / pinned host) out of the context's cache
+template <bool HOST>
+struct wbuf
+{
+	void *p{nullptr};
+	size_t bytes{0};
+	fsq_ctx *owner{nullptr};
+	wbuf() = default;
+	wbuf(wbuf const &) = delete;
+	wbuf &operator=(wbuf const &) = delete;
+	~wbuf() { release(); }
+	void release() { if (p) owner->give(HOST, p, bytes); p = nullptr; }
+	cudaError_t alloc(fsq_ctx *ctx, size_t want) { release(); owner = ctx; return ctx->take(HOST, want, &p, &bytes); }
+	void *detach() { void *q = p; p = nullptr; return q; }
+	void adopt(wbuf &o) { release(); p = o.p; bytes = o.bytes; owner = o.owner; o.p = nullptr; }
+	template <typename T> T *as() const { return static_cast <T *>(p); }
+};
+typedef wbuf <false> dbuf;
+typedef wbuf <true> hbuf;
+
+
 struct fsq_segmentation
 {
 	fsq_ctx *ctx{};
 	uint32_t m{};
 	uint64_t n{}, L{};
 	uint32_t K{};
-	std::vector <uint64_t> lb, rb;            // reduced
+	std::vector <uint64_t> lb, rb;            // reduced (every rank holds all of them)
 	std::vector <uint32_t> size;
-	uint32_t *d_a{}, *d_d{};                  // reduced states on the device, count x m
-	uint32_t *h_a{}, *h_d{};                  // pinned host copies, made on first request
-	size_t d_bytes[2]{}, h_bytes[2]{};        // sizes of those blocks in the context's workspace cache
-	void *h_tb{};                             // traceback before reduction, pinned: rb u64[T], then lb, max, size u32[T] each
-	size_t h_tb_bytes{};
+	uint32_t own_first{}, own_last{};         // the reduced segments whose state this rank holds (all of them on one GPU)
+	dbuf red_a, red_d;                        // their states on the device, (own_last - own_first) x m
+	hbuf h_a, h_d;                            // pinned host copies, made on first request
+	dbuf tr_lb, tr_rb, tr_max, tr_size;       // traceback before reduction, on the device: T entries
+	hbuf h_tb;                                // ... and on the host once asked for: rb u64[T], then lb, max, size u32[T] each
 	uint32_t T{};
 	std::vector <uint32_t> dp_lb, dp_max, dp_size;   // keep_dp
 };
@@ -120,25 +152,6 @@ int fail(fsq_ctx *ctx, int code, char const *fmt, ...)
 
 #define CK_(ctx, call) do { cudaError_t e_ = (call); if (cudaSuccess != e_) return fail(ctx, FSQ_ERR_CUDA, "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while (0)
 #define CK(call) do { cudaError_t e_ = (call); if (cudaSuccess != e_) return fail(ctx, FSQ_ERR_CUDA, "%s:%d: %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); } while (0)
-
-// RAII workspace buffers (device / pinned host) out of the context's cache
-template <bool HOST>
-struct wbuf
-{
-	void *p{nullptr};
-	size_t bytes{0};
-	fsq_ctx *owner{nullptr};
-	wbuf() = default;
-	wbuf(wbuf const &) = delete;
-	wbuf &operator=(wbuf const &) = delete;
-	~wbuf() { release(); }
-	void release() { if (p) owner->give(HOST, p, bytes); p = nullptr; }
-	cudaError_t alloc(fsq_ctx *ctx, size_t want) { release(); owner = ctx; return ctx->take(HOST, want, &p, &bytes); }
-	void *detach() { void *q = p; p = nullptr; return q; }
-	template <typename T> T *as() const { return static_cast <T *>(p); }
-};
-typedef wbuf <false> dbuf;
-typedef wbuf <true> hbuf;
 
 struct phase
 {
@@ -187,9 +200,8 @@ void flush_phases(fsq_ctx *ctx)
 struct geometry
 {
 	uint32_t n_tiles, n_warps, tpw, C, cg, B;
-	// blocked column step (fsq_bstep.cuh): E elements per thread, T threads, symbols sym0 .. sym0 + ns - 1
-	bool blocked;
-	bool chunked;          // fsq_cstep.cuh (the default where it applies); otherwise blocked = fsq_bstep.cuh, else striped
+	// chunked column step (fsq_cstep.cuh): E elements per thread, T threads, symbols sym0 .. sym0 + ns - 1
+	bool chunked;          // the default where it applies; otherwise the striped kernel (fsq_step.cuh)
 	uint32_t E, T, ns, sym0;
 };
 
@@ -209,16 +221,15 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 	g.tpw = (g.n_tiles + g.n_warps - 1) / g.n_warps;
 	while (g.tpw > 32 && g.n_warps < 32) { g.n_warps *= 2; g.tpw = (g.n_tiles + g.n_warps - 1) / g.n_warps; }
 
-	// The blocked step walks E consecutive positions per thread; it needs the symbols that occur to span at most 8 values.
+	// The chunked step walks E consecutive positions per thread; it needs the symbols that occur to span at most 8 values.
 	uint32_t const mask = msa->sym_mask ? msa->sym_mask : ((1u << msa->nsym) - 1u);
 	uint32_t lo = 0, hi = 31;
 	while (!((mask >> lo) & 1u)) ++lo;
 	while (!((mask >> hi) & 1u)) --hi;
 	g.sym0 = lo;
 	g.ns = hi - lo + 1;
-	int64_t const kern = ctx->opt("kernel", 0);        // 0 auto, 1 striped, 2 blocked, 3 chunked
+	int64_t const kern = ctx->opt("kernel", 0);        // 0 auto, 1 striped, 3 chunked
 	g.chunked = (0 == kern || 3 == kern) && g.ns <= 8 && m <= cblock_thread_limit(53) * 53u;
-	g.blocked = !g.chunked && (1 != kern) && g.ns <= 8 && m <= 448u * 33u;
 	uint32_t threads = g.n_warps * 32, regs = 64;
 	if (g.chunked)
 	{
@@ -245,18 +256,6 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 		threads = g.T;
 		regs = cblock_registers(g.E);
 	}
-	else if (g.blocked)
-	{
-		int64_t e = ctx->opt("chunk", 0);
-		if (9 != e && 17 != e && 33 != e)
-			e = m <= 32 * 9 ? 9 : (m <= 32 * 17 ? 17 : 33);
-		uint32_t const tmax = 9 == e ? 1024 : (17 == e ? 512 : 448);
-		if ((uint64_t) tmax * e < m) e = 33;
-		g.E = (uint32_t) e;
-		g.T = ((m + g.E - 1) / g.E + 31) / 32 * 32;
-		threads = g.T;
-		regs = 9 == g.E ? 64 : 128;
-	}
 
 	g.cg = (uint32_t) std::max <uint64_t>(1, (g.chunked ? 512 : 2048) / msa->col_stride);
 	int64_t C = ctx->opt("block_columns", 0);
@@ -266,7 +265,7 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 		// footprint decides), but long enough to amortise the two extra passes' fixed costs
 		uint64_t per_sm = std::min <uint64_t>(32, 2048 / threads);
 		per_sm = std::min <uint64_t>(per_sm, 65536 / ((uint64_t) threads * regs));
-		size_t smem = 2 * (size_t) g.cg * msa->col_stride + 4 * (size_t) threads * (g.blocked ? g.E + 2 * g.ns : 1) + 2 * (size_t) m + 1024;
+		size_t smem = 2 * (size_t) g.cg * msa->col_stride + 4 * (size_t) threads + 2 * (size_t) m + 1024;
 		if (g.chunked)
 		{
 			// The histogram of pass B grows with the block length, so the footprint depends on the answer: take the largest
@@ -331,13 +330,7 @@ cudaError_t launch_scan(block_args const &A, uint32_t n_blocks, geometry const &
 			default: return cudaErrorInvalidConfiguration;
 		}
 	}
-	if (!g.blocked) return launch_block(A, n_blocks, g.n_warps, g.tpw, hist, st);
-	switch (g.E)
-	{
-		case 9: return launch_bblock_e9(A, n_blocks, g.T, g.ns, hist, st);
-		case 17: return launch_bblock_e17(A, n_blocks, g.T, g.ns, hist, st);
-		default: return launch_bblock_e33(A, n_blocks, g.T, g.ns, hist, st);
-	}
+	return launch_block(A, n_blocks, g.n_warps, g.tpw, hist, st);
 }
 
 void fill_common(block_args &A, fsq_msa const *msa, geometry const &g)
@@ -377,14 +370,16 @@ __global__ void gather_states_kernel(uint32_t const *src_a, uint32_t const *src_
 // States kept by pass B (packed row | code << 16, one row of `stride` words per column) -> (a, d) at the given (global) right
 // bounds: the state before column rb is the one stored after column rb - 1; its codes are relative to that column's block.
 __global__ void gather_stored_states_kernel(
-	uint32_t const *states, uint64_t stride, uint64_t const *rbs, uint32_t m, uint32_t C, uint64_t col0,
+	uint32_t const *states, uint64_t stride, uint64_t const *rbs, uint32_t const *ctl, uint32_t m, uint32_t C, uint64_t col0,
 	uint32_t const *oldvals, uint32_t const *R, uint32_t *dst_a, uint32_t *dst_d
 )
 {
+	// rbs: the right bounds of all reduced segments; this rank's are [ctl[I_SEG_FIRST], ctl[I_SEG_LAST]) (the grid may be larger)
 	uint32_t const t = blockIdx.x;                 // grid.x: up to 2^31 - 1 positions
+	if (ctl[I_SEG_FIRST] + t >= ctl[I_SEG_LAST]) return;
 	uint32_t const i = blockIdx.y * blockDim.x + threadIdx.x;
 	if (i >= m) return;
-	uint64_t const k = rbs[t] - col0 - 1;          // local column whose output state this is (rbs are global right bounds)
+	uint64_t const k = rbs[ctl[I_SEG_FIRST] + t] - col0 - 1;          // local column whose output state this is (rbs are global right bounds)
 	uint32_t const b = (uint32_t) (k / C);
 	uint32_t const r = R[b];
 	uint32_t const w = states[k * stride + i];
@@ -400,8 +395,11 @@ struct scan_state
 	geometry g;
 	dbuf sum_a, sum_d;          // [B][m]: block summaries (pass A); after the up-sweep, summaries of aligned spans
 	dbuf st_a, st_d;            // [B + 1][m]: state at every block start (slot B: at the end of the last block)
-	dbuf code, oldvals, R, items, item_begin;
-	hbuf h_items, h_begin;
+	dbuf code, oldvals, R;
+	// stitch plans: device copies and their pinned staging, one pair per plan, alive until the run ends (no plan waits
+	// for the copies of the one before it)
+	std::vector <std::unique_ptr <dbuf>> plan_dev;
+	std::vector <std::unique_ptr <hbuf>> plan_host;
 	bool relative{false};      // st_* are still relative to the identity state at the first local column
 };
 
@@ -416,15 +414,21 @@ struct stitch_plan
 int run_stitch_plan(fsq_ctx *ctx, scan_state &S, stitch_plan const &plan, uint32_t m, std::vector <std::vector <std::pair <uint32_t *, uint32_t const *>>> const &copies)
 {
 	size_t const n = plan.items.size();
+	stitch_item *d_items = nullptr;
+	uint32_t *d_begin = nullptr;
 	if (n)
 	{
 		// pinned staging lives in the scan state: it is released only after the caller's final synchronisation
-		CK(S.h_items.alloc(ctx, n * sizeof(stitch_item))); CK(S.h_begin.alloc(ctx, (n + 1) * 4));
-		memcpy(S.h_items.p, plan.items.data(), n * sizeof(stitch_item));
-		for (size_t i = 0; i <= n; ++i) S.h_begin.as <uint32_t>()[i] = (uint32_t) i;
-		CK(S.items.alloc(ctx, n * sizeof(stitch_item))); CK(S.item_begin.alloc(ctx, (n + 1) * 4));
-		CK(cudaMemcpyAsync(S.items.p, S.h_items.p, n * sizeof(stitch_item), cudaMemcpyHostToDevice, ctx->stream));
-		CK(cudaMemcpyAsync(S.item_begin.p, S.h_begin.p, (n + 1) * 4, cudaMemcpyHostToDevice, ctx->stream));
+		size_t const ib = n * sizeof(stitch_item), bb = (n + 1) * 4, ib_al = (ib + 15) & ~size_t(15);
+		S.plan_host.emplace_back(new hbuf); S.plan_dev.emplace_back(new dbuf);
+		hbuf &h = *S.plan_host.back(); dbuf &d = *S.plan_dev.back();
+		CK(h.alloc(ctx, ib_al + bb)); CK(d.alloc(ctx, ib_al + bb));
+		memcpy(h.p, plan.items.data(), ib);
+		uint32_t *hb = (uint32_t *) (h.as <uint8_t>() + ib_al);
+		for (size_t i = 0; i <= n; ++i) hb[i] = (uint32_t) i;
+		CK(cudaMemcpyAsync(d.p, h.p, ib_al + bb, cudaMemcpyHostToDevice, ctx->stream));
+		d_items = d.as <stitch_item>();
+		d_begin = (uint32_t *) (d.as <uint8_t>() + ib_al);
 	}
 	for (size_t l = 0; l + 1 < plan.level_begin.size(); ++l)
 	{
@@ -434,8 +438,8 @@ int run_stitch_plan(fsq_ctx *ctx, scan_state &S, stitch_plan const &plan, uint32
 		size_t const first = plan.level_begin[l], count = plan.level_begin[l + 1] - first;
 		if (0 == count) continue;
 		stitch_args SA;
-		SA.items = S.items.as <stitch_item>();
-		SA.item_begin = S.item_begin.as <uint32_t>() + first;
+		SA.items = d_items;
+		SA.item_begin = d_begin + first;
 		SA.n_ctas = (uint32_t) count;
 		SA.m = m;
 		SA.n_tiles = S.g.n_tiles;
@@ -561,7 +565,6 @@ int apply_start_state(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S, uint32_t 
 		plan.items.push_back(it);
 	}
 	plan.end_level();
-	CK(cudaStreamSynchronize(ctx->stream));      // the staging buffers of the scan state are about to be rewritten
 	int const rc = run_stitch_plan(ctx, S, plan, m, {});
 	if (rc) return rc;
 	CK(cudaMemcpyAsync(st_a, d_a, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
@@ -637,461 +640,661 @@ int dump_states(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S, std::vector <ui
 
 } // namespace
 
-// One run of the long path over the columns one rank holds (all of them on a single GPU), cut into the stages between
-// which column-sharded ranks exchange data.  fsq_segment() runs the stages back to back; fsq_shard_*() exposes them.
-struct fsq_shard
+// One run of the long path over the columns one rank holds (all of them on a single GPU).  Every stage is enqueued on
+// the context's stream behind the one before it; what a stage decides (another DP round? lists long enough? how many
+// traceback entries?) stays in the control words on the device, where the next stage reads it, and the host looks at
+// them once per batch of stages.  With several ranks the exchanges are all-gathers enqueued on the same stream.
+struct fsq_run
 {
 	fsq_ctx *ctx{};
 	fsq_msa const *msa{};
+	fsq_comm *comm{};
+	int rank{0}, size{1};
 	uint32_t m{};
 	uint64_t n{};               // columns of the whole alignment
 	uint64_t L{};
 	uint64_t c0{}, c1{};        // this rank's columns [c0, c1)
+	uint64_t n_per{};           // columns per rank (the last rank may hold fewer)
 	scan_state S;
-	bool started{false};        // block start states are true and compressed
 
-	// DP: the table is global (every rank holds all of it), the top lists are local
-	uint64_t dp_size{};
+	// DP.  The table is global (every rank holds all of it) and indexed by the column an entry is computed at: entry t
+	// lives at tbx[t + L - 1], so that rank r's slice is tbx[r n_per, (r + 1) n_per) and the exchange is an in-place all-gather.
+	uint64_t dp_size{}, tb_len{};
 	uint32_t n_entries{}, n_blk{}, n_levels{}, t_first{}, t_last{};
-	uint32_t chunk{}, n_chunks{}, cap{}, rounds{};
-	uint32_t reach_known{};     // the farthest look-back any rank has seen in the rounds so far
+	uint32_t chunk{}, n_chunks{}, cap{};
+	uint32_t back_bound{1u << 16};     // masks and rmq cells are rebuilt this far below the rank's first entry
 	bool single_chain{false};
-	dbuf tb_max, tb_lb, tb_size, mk, lev, flags, chunk_level, cnt, h0, toplist, states;
+	dbuf tbx_max, tbx_lb, tbx_size, mk, lev, ctl, chunk_level, cnt, h0, toplist, states, xflags, sums;
 	uint64_t state_stride{};
+	struct window { uint32_t b0, b1; uint64_t col0, col1; };      // blocks [b0, b1) = local columns [col0, col1)
+	std::vector <window> windows;
+	bool whole{true};           // every rank keeps the top lists of all its columns at once (one window each)
+	hbuf h_x;
 
-	// traceback (replicated) and reduction
-	uint32_t T{}, K{};
-	dbuf tr_lb, tr_rb, tr_max, tr_size, lists, d_next, d_nsize;
-	hbuf h_tb;                                 // the traceback on the host (pinned): rb u64[T], then lb, max, size u32[T] each
-	uint32_t pos_first{}, pos_last{};          // traceback positions whose right bound this rank holds the state of
-	std::vector <uint64_t> red_lb, red_rb;
-	std::vector <uint32_t> red_size, red_pos;  // reduced segments; red_pos: index into the traceback
-	uint32_t seg_first{}, seg_last{};          // reduced segments whose state this rank holds
-	uint32_t n_reduced{};
-	dbuf red_a, red_d;                         // [seg_last - seg_first][m]
-	dbuf d_red_lb, d_red_rb, d_red_size, walk_jump, walk_info;      // the reduced segments on the device (launch_walk)
-	hbuf h_red, h_info;                        // their host staging; red_pending: copies in flight, vectors not yet filled
-	bool red_pending{false}, red_on_host{false};
-	bool final_done{false};                    // the last DP entry was computed behind the final round already
-	uint32_t final_overflow{};
+	// traceback (replicated), reduction (own positions + halo), reduced segments (replicated) and their states (own)
+	uint32_t t_bound{}, rows_bound{}, width{}, halo{16};
+	dbuf tr_lb, tr_rb, tr_max, tr_size, jump, rows, rows_a, halo_rows, pos_all, next_own, nsize_own, next_all, nsize_all, next, nsize;
+	dbuf walk_jump, red_lb, red_rb, red_size, red_pos, red_a, red_d;
+	hbuf h_ctl, h_red;
+	uint32_t h[N_CONTROL]{};    // the control words as last read
 
-	dp_args dp() const
-	{
-		dp_args D;
-		memset(&D, 0, sizeof D);
-		D.m = m; D.n = n; D.L = L; D.col_base = c0; D.t_first = t_first; D.t_last = t_last;
-		D.toplist = toplist.as <uint2>(); D.cap = cap; D.cnt = cnt.as <uint32_t>(); D.h0 = h0.as <uint32_t>();
-		D.tb_max = tb_max.as <uint32_t>(); D.tb_lb = tb_lb.as <uint32_t>(); D.tb_size = tb_size.as <uint32_t>();
-		D.mk = mk.as <uint64_t>();
-		D.lev = lev.as <uint32_t>(); D.n_blk = n_blk; D.n_levels = n_levels;
-		D.n_entries = n_entries;
-		D.chunk = single_chain ? (n_entries + 63) / 64 * 64 : chunk;
-		D.n_chunks = single_chain ? 1 : n_chunks;
-		D.chunk_level = chunk_level.as <uint32_t>();
-		D.flags = flags.as <uint32_t>();
-		D.reach_bound = reach_known;
-		{
-			// what this rank's chains can read: its own entries and the look-back before them (twice the bound, for slack)
-			uint64_t const back = 2 * (uint64_t) reach_known + 128;
-			D.w_first = (uint32_t) ((t_first > back ? t_first - back : 0) & ~63ull);
-			D.w_last = n_entries;
-			if (c1 != n) D.w_last = (uint32_t) std::min <uint64_t>(n_entries, t_last);      // nothing this rank reads lies past its own entries
-		}
-		return D;
-	}
+	uint32_t *tb_max() const { return tbx_max.as <uint32_t>() + (L - 1); }
+	uint32_t *tb_lb() const { return tbx_lb.as <uint32_t>() + (L - 1); }
+	uint32_t *tb_size() const { return tbx_size.as <uint32_t>() + (L - 1); }
+	uint32_t *control() const { return ctl.as <uint32_t>(); }
 };
 
 namespace {
 
-int shard_init(fsq_shard *P, fsq_ctx *ctx, fsq_msa const *msa, uint64_t n_total, uint64_t L)
+uint64_t columns_per_rank(uint64_t n, int size)
 {
-	P->ctx = ctx; P->msa = msa; P->m = msa->m; P->n = n_total; P->L = L;
-	P->c0 = msa->col0; P->c1 = msa->col0 + msa->n;
+	if (size <= 1) return n;
+	uint64_t const per = (n + size - 1) / size;
+	return (per + 31) / 32 * 32;
+}
+
+// Device memory a run may plan with: what is free plus what the context's cache holds (option mem_limit, a test knob,
+// stands in for the answer).
+size_t plannable_bytes(fsq_ctx *ctx)
+{
+	int64_t const lim = ctx->opt("mem_limit", 0);
+	if (lim > 0) return (size_t) lim;
+	size_t free_b = 0, total_b = 0;
+	if (cudaSuccess != cudaMemGetInfo(&free_b, &total_b)) { cudaGetLastError(); return 0; }
+	size_t cached = 0;
+	for (auto const &blk : ctx->dev_cache) cached += blk.bytes;
+	return free_b + cached;
+}
+
+int run_init(fsq_run *R, fsq_ctx *ctx, fsq_msa const *msa, fsq_comm *comm, uint64_t n_total, uint64_t L)
+{
+	R->ctx = ctx; R->msa = msa; R->comm = comm; R->m = msa->m; R->n = n_total; R->L = L;
+	R->rank = comm ? comm->rank : 0;
+	R->size = comm ? comm->size : 1;
+	R->n_per = columns_per_rank(n_total, R->size);
+	R->c0 = msa->col0; R->c1 = msa->col0 + msa->n;
+	if (R->size > 1)
+	{
+		uint64_t const want0 = (uint64_t) R->rank * R->n_per, want1 = std::min <uint64_t>(n_total, want0 + R->n_per);
+		if (want0 >= n_total)
+			return fail(ctx, FSQ_ERR_ARG, "%d ranks are too many for %llu columns: rank %d would hold none (fsq_shard_columns)", R->size, (unsigned long long) n_total, R->rank);
+		if (R->c0 != want0 || R->c1 != want1)
+			return fail(ctx, FSQ_ERR_ARG, "rank %d of %d must hold columns [%llu, %llu) (fsq_shard_columns), the alignment handed in holds [%llu, %llu)", R->rank, R->size,
+				(unsigned long long) want0, (unsigned long long) want1, (unsigned long long) R->c0, (unsigned long long) R->c1);
+	}
+	else if (0 != R->c0 || R->c1 != n_total)
+		return fail(ctx, FSQ_ERR_ARG, "a single rank holds the whole alignment: columns [0, %llu)", (unsigned long long) n_total);
 	uint64_t const n = n_total;
-	P->dp_size = n - L + 1;
-	P->n_entries = (uint32_t) (n - 2 * L + 1);
-	P->n_blk = (uint32_t) (P->dp_size / 64 + 1);
-	P->n_levels = 1;
-	while ((1ull << P->n_levels) <= P->n_blk) ++P->n_levels;
+	R->dp_size = n - L + 1;
+	R->tb_len = std::max <uint64_t>(n, (uint64_t) R->size * R->n_per) + 64;
+	R->n_entries = (uint32_t) (n - 2 * L + 1);
+	R->n_blk = (uint32_t) (R->dp_size / 64 + 1);
+	R->n_levels = 1;
+	while ((1ull << R->n_levels) <= R->n_blk) ++R->n_levels;
 	// entry t is computed at column t + L - 1
-	uint64_t const lo = P->c0 + 1 > L ? P->c0 + 1 - L : 0, hi = P->c1 + 1 > L ? P->c1 + 1 - L : 0;
-	P->t_first = (uint32_t) std::min <uint64_t>(lo, P->n_entries);
-	P->t_last = (uint32_t) std::min <uint64_t>(hi, P->n_entries);
+	uint64_t const lo = R->c0 + 1 > L ? R->c0 + 1 - L : 0, hi = R->c1 + 1 > L ? R->c1 + 1 - L : 0;
+	R->t_first = (uint32_t) std::min <uint64_t>(lo, R->n_entries);
+	R->t_last = (uint32_t) std::min <uint64_t>(hi, R->n_entries);
 	// chains: enough to fill the device a few times over, each a whole number of 64-entry rmq blocks, on a global grid
 	{
 		int64_t want = ctx->opt("dp_chunks", 0);
-		if (want <= 0) want = (int64_t) ctx->prop.multiProcessorCount * (2048 / (32 * (int64_t) std::min <uint64_t>(L, 16)) > 8 ? 8 : 2048 / (32 * (int64_t) std::min <uint64_t>(L, 16)));      // one resident wave of chains
-		uint64_t const own = std::max <uint64_t>(1, P->t_last - P->t_first);
+		if (want <= 0)
+		{
+			int64_t const per_sm = 2048 / (32 * (int64_t) std::min <uint64_t>(L, 16));
+			want = (int64_t) ctx->prop.multiProcessorCount * std::min <int64_t>(per_sm, 8);      // one resident wave of chains
+		}
+		uint64_t const own = std::max <uint64_t>(1, R->t_last - R->t_first);
 		uint64_t c = (own + (uint64_t) want - 1) / (uint64_t) want;
 		c = std::max <uint64_t>(c, std::max <uint64_t>(256, 8 * L));
-		if (1 == want) c = P->n_entries;
+		if (1 == want) c = R->n_entries;
 		c = (c + 63) / 64 * 64;
-		P->chunk = (uint32_t) std::min <uint64_t>(c, 0xffffffc0ull);
-		P->n_chunks = (P->n_entries + P->chunk - 1) / P->chunk;
+		R->chunk = (uint32_t) std::min <uint64_t>(c, 0xffffffc0ull);
+		R->n_chunks = (R->n_entries + R->chunk - 1) / R->chunk;
 	}
-	P->cap = (uint32_t) std::min <int64_t>(P->m, std::max <int64_t>(1, ctx->opt("cap", 127)));
-	P->state_stride = ((uint64_t) P->m + 3) & ~3ull;
+	// the bound a call on this shape has worked with before, else the option, else 127
+	{
+		auto it = ctx->learned_cap.find(std::make_tuple(R->m, R->n, R->L));
+		int64_t const start = ctx->learned_cap.end() != it ? (int64_t) it->second : ctx->opt("cap", 127);
+		R->cap = (uint32_t) std::min <int64_t>(R->m, std::max <int64_t>(1, start));
+	}
+	R->state_stride = ((uint64_t) R->m + 3) & ~3ull;
+	R->t_bound = (uint32_t) (R->dp_size / L + 2);
+	R->rows_bound = 1 == R->size ? R->t_bound : (uint32_t) (R->n_per / L + 2);
+	R->halo = (uint32_t) std::max <int64_t>(1, ctx->opt("halo", 16));
 	return FSQ_OK;
 }
 
-// Pass B over this rank's columns with the current top-list bound; resets the DP table.
-int shard_scan(fsq_shard *P)
+// ---- pass A and the true start states ---------------------------------------------------------------------------------
+int run_prepare(fsq_run *R)
 {
-	fsq_ctx *ctx = P->ctx;
-	fsq_msa const *msa = P->msa;
-	geometry const &g = P->S.g;
-	uint32_t const m = P->m;
-	uint64_t const nl = msa->n;
-	if (!P->tb_max.p)
+	fsq_ctx *ctx = R->ctx;
+	uint32_t const m = R->m;
+	int rc = local_scan(ctx, R->msa, R->S);
+	if (rc) return rc;
+	if (R->size > 1)
 	{
-		CK(P->tb_max.alloc(ctx, P->dp_size * 4)); CK(P->tb_lb.alloc(ctx, P->dp_size * 4)); CK(P->tb_size.alloc(ctx, P->dp_size * 4));
-		CK(P->mk.alloc(ctx, P->dp_size * 8)); CK(P->lev.alloc(ctx, (size_t) P->n_levels * P->n_blk * 4)); CK(P->flags.alloc(ctx, 32));
-		CK(P->cnt.alloc(ctx, nl * 4)); CK(P->h0.alloc(ctx, nl * 4));
-		CK(P->chunk_level.alloc(ctx, (size_t) P->n_chunks * 8));
-		// Pass B keeps the state of every column when 4 m n bytes fit comfortably (option store_states: -1 auto, 0 never,
-		// 1 always); the states at the segment boundaries are then a gather instead of a third scan.
-		int64_t const want = ctx->opt("store_states", -1);
-		bool keep = false;
-		if (g.chunked && 0 != want)
+		// this rank's summary = the state at the end of its last block relative to the identity state at c0; every rank
+		// receives all of them and composes the ones before it (composition is associative: SURVEY.md A.10)
+		geometry const &g = R->S.g;
+		CK(R->sums.alloc(ctx, ((size_t) R->size + 3) * 2 * m * 4));
+		uint32_t *all = R->sums.as <uint32_t>();
+		uint32_t *mine = all + (size_t) R->rank * 2 * m;
+		CK(cudaMemcpyAsync(mine, R->S.st_a.as <uint32_t>() + (size_t) g.B * m, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+		CK(cudaMemcpyAsync(mine + m, R->S.st_d.as <uint32_t>() + (size_t) g.B * m, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+		phase px(ctx, "exchange");
+		CK(R->comm->all_gather(mine, all, (size_t) 2 * m * 4, ctx->stream));
+		px.stop();
+		if (R->rank > 0)
 		{
-			size_t free_b = 0, total_b = 0;
-			CK(cudaMemGetInfo(&free_b, &total_b));      // (a driver round trip per call; the answer decides only the first time)
-			size_t cached = 0;
-			for (auto const &blk : ctx->dev_cache) cached += blk.bytes;
-			size_t const need = (size_t) (P->state_stride * 4 * nl);
-			size_t const other = (size_t) nl * (P->cap + 1) * 8 + (size_t) nl * 64 + ((size_t) 1 << 30);
-			keep = (1 == want) || need + other < free_b + cached;
-			if (keep && cudaSuccess != P->states.alloc(ctx, need)) { cudaGetLastError(); keep = false; }
+			uint32_t *tmp = all + (size_t) R->size * 2 * m;          // two scratch states behind the summaries
+			uint32_t const *cur = all;
+			phase ps(ctx, "stitch");
+			for (int i = 1; i < R->rank; ++i)
+			{
+				stitch_plan plan;
+				stitch_item it;
+				memset(&it, 0, sizeof it);
+				uint32_t *out = tmp + (size_t) (i & 1) * 2 * m;
+				it.in_a = cur; it.in_d = cur + m;
+				it.pi = all + (size_t) i * 2 * m; it.delta = it.pi + m;
+				it.out_a = out; it.out_d = out + m;
+				it.s_mark = (uint32_t) ((uint64_t) i * R->n_per);
+				plan.items.push_back(it);
+				plan.end_level();
+				if ((rc = run_stitch_plan(ctx, R->S, plan, m, {}))) return rc;
+				cur = out;
+			}
+			ps.stop();
+			if ((rc = apply_start_state(ctx, R->msa, R->S, cur, cur + m))) return rc;
 		}
-		ctx->stats["store_states"] = keep ? 1 : 0;
+		R->S.relative = false;
 	}
-	CK(P->toplist.alloc(ctx, (size_t) nl * (P->cap + 1) * sizeof(uint2)));
-	// entries the per-column DP writes start from 0 (the first round's stand-in for "nothing known"); the ones the
-	// reference never writes keep its defaults; masks and rmq cells start from values that index inside the table
-	CK(cudaMemsetAsync(P->tb_max.p, 0xff, P->dp_size * 4, ctx->stream));
-	CK(cudaMemsetAsync(P->tb_max.p, 0, (size_t) P->n_entries * 4, ctx->stream));
-	CK(cudaMemsetAsync(P->tb_size.p, 0xff, P->dp_size * 4, ctx->stream));
-	CK(cudaMemsetAsync(P->tb_lb.p, 0, P->dp_size * 4, ctx->stream));
-	CK(cudaMemsetAsync(P->mk.p, 0xff, P->dp_size * 8, ctx->stream));
-	CK(cudaMemsetAsync(P->lev.p, 0, (size_t) P->n_levels * P->n_blk * 4, ctx->stream));
-	CK(cudaMemsetAsync(P->flags.p, 0, 32, ctx->stream));
-	P->rounds = 0;
-	P->final_done = false;
-	P->reach_known = 0;
-	P->single_chain = false;
-	{
-		phase pb(ctx, "pass_b");
-		block_args A;
-		fill_common(A, msa, g);
-		A.mode = MODE_EXACT;
-		A.st_a = P->S.st_a.as <uint32_t>();
-		A.code = P->S.code.as <uint16_t>();
-		A.oldvals = P->S.oldvals.as <uint32_t>();
-		A.R = P->S.R.as <uint32_t>();
-		A.toplist = P->toplist.as <uint2>();
-		A.cap = P->cap;
-		A.cnt = P->cnt.as <uint32_t>();
-		A.h0 = P->h0.as <uint32_t>();
-		A.states = P->states.as <uint32_t>();
-		A.state_stride = P->state_stride;
-		CK(launch_scan(A, g.B, g, true, ctx->stream));
-		pb.stop();
-		ctx->stats["kernel_launches"] += 1;
-	}
-	return FSQ_OK;
+	else if (R->S.relative)
+		return fail(ctx, FSQ_ERR_ARG, "this entry point needs an alignment that starts at column 0");
+	return compress_starts(ctx, R->msa, R->S);
 }
 
-// One DP round: every own chain once against the table as it stands.  changed: another round is needed -- in the first
-// round, some stored value changed; later, some value changed that a chain after its owner may have read while it was
-// still the old one (dp_chain_kernel: the last reach_known entries of a chain, or any rmq cell), or a chain read
-// further back than that.  A round without such a change has computed every entry from final values.
-// reach: the farthest any column has looked back so far (entries).
-int shard_dp_round(fsq_shard *P, uint32_t *changed, uint32_t *reach)
+// ---- memory plan: the top lists of all columns at once, or windows of blocks over one reused buffer ---------------------
+// Bitwise AND of a word over the ranks (a host round trip: used once per shape, the answer is cached in the context).
+int run_agree_and(fsq_run *R, uint32_t *bits)
 {
-	fsq_ctx *ctx = P->ctx;
-	phase pd(ctx, "dp");
-	dp_args const D = P->dp();
-	CK(cudaMemsetAsync(P->flags.p, 0, 4, ctx->stream));
-	CK(cudaMemsetAsync(P->flags.as <uint32_t>() + 3, 0, 4, ctx->stream));
-	CK(launch_dp_chains(D, ctx->stream));
-	ctx->stats["kernel_launches"] += 1;
-	++P->rounds;
-	uint32_t h_flags[4] = {0, 0, 0, 0};
-	CK(cudaMemcpyAsync(h_flags, P->flags.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
-	pd.stop();
+	fsq_ctx *ctx = R->ctx;
+	if (R->size <= 1) return FSQ_OK;
+	CK(R->xflags.alloc(ctx, ((size_t) R->size + 1) * 16));
+	CK(R->h_x.alloc(ctx, ((size_t) R->size + 1) * 16));
+	uint32_t *xs = R->xflags.as <uint32_t>(), *hx = R->h_x.as <uint32_t>();
+	hx[0] = *bits; hx[1] = hx[2] = hx[3] = 0;
+	CK(cudaMemcpyAsync(xs + 4 * (size_t) R->rank, hx, 16, cudaMemcpyHostToDevice, ctx->stream));
+	if (cudaSuccess != R->comm->all_gather(xs + 4 * (size_t) R->rank, xs, 16, ctx->stream))
+		return fail(ctx, FSQ_ERR_CUDA, "exchange of the memory plans failed: %s", R->comm->error.c_str());
+	CK(cudaMemcpyAsync(hx, xs, (size_t) R->size * 16, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaStreamSynchronize(ctx->stream));
-	*changed = (h_flags[0] && (1 == P->rounds || h_flags[3])) ? 1u : 0u;
-	*reach = h_flags[2];
-	P->reach_known = std::max(P->reach_known, h_flags[2]);
-	ctx->stats["dp_reach"] = h_flags[2];
+	ctx->stats["host_syncs"] += 1;
+	uint32_t v = 0xffffffffu;
+	for (int r = 0; r < R->size; ++r) v &= hx[4 * r];
+	*bits = v;
 	return FSQ_OK;
 }
 
-// The first two rounds queued back to back, with the guess between them, and one read-back at the end: round 1 starts
-// from nothing and can never be the last, and the guess takes the look-back from the device (flags[2]) anyway, so the
-// host has no decision to make before round 2.  Single rank only (column shards exchange their slices after every round).
-int shard_dp_first_two_rounds(fsq_shard *P, uint32_t *changed, uint32_t *reach)
+int run_plan(fsq_run *R)
 {
-	fsq_ctx *ctx = P->ctx;
-	phase pd(ctx, "dp");
-	dp_args D = P->dp();
-	CK(cudaMemsetAsync(P->flags.p, 0, 4, ctx->stream));
-	CK(cudaMemsetAsync(P->flags.as <uint32_t>() + 3, 0, 4, ctx->stream));
-	CK(launch_dp_chains(D, ctx->stream));
-	CK(launch_dp_guess(D, ctx->stream));
-	CK(cudaMemsetAsync(P->flags.p, 0, 4, ctx->stream));
-	CK(cudaMemsetAsync(P->flags.as <uint32_t>() + 3, 0, 4, ctx->stream));
-	D.bound_on_device = 1;
-	CK(launch_dp_chains(D, ctx->stream));
-	// the last entry too, behind the same read-back: it stands if round 2 turns out to have been the last one
-	CK(launch_dp_final(D, ctx->stream));
-	ctx->stats["kernel_launches"] += 3 + 5;
-	P->rounds += 2;
-	uint32_t h_flags[4] = {0, 0, 0, 0};
-	CK(cudaMemcpyAsync(h_flags, P->flags.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
-	pd.stop();
-	CK(cudaStreamSynchronize(ctx->stream));
-	*changed = (h_flags[0] && h_flags[3]) ? 1u : 0u;
-	*reach = h_flags[2];
-	P->reach_known = std::max(P->reach_known, h_flags[2]);
-	ctx->stats["dp_reach"] = h_flags[2];
-	if (0 == *changed)
-	{
-		P->final_done = true;
-		P->final_overflow = h_flags[1];
-		ctx->stats["dp_rounds"] += P->rounds;
-		ctx->stats["dp_chunks"] = P->n_chunks;
-	}
-	return FSQ_OK;
-}
-
-// Between rounds: with guess, level the table (fsq_dp.cu) using the given look-back; rebuild masks and rmq tables.
-int shard_dp_sync(fsq_shard *P, int guess, uint32_t reach)
-{
-	fsq_ctx *ctx = P->ctx;
-	phase pd(ctx, "dp");
-	dp_args const D = P->dp();
-	P->reach_known = std::max(P->reach_known, reach);
-	if (guess)
-	{
-		CK(cudaMemcpyAsync(P->flags.as <uint32_t>() + 2, &reach, 4, cudaMemcpyHostToDevice, ctx->stream));
-		CK(launch_dp_guess(D, ctx->stream));
-		ctx->stats["kernel_launches"] += 5;
-	}
+	fsq_ctx *ctx = R->ctx;
+	geometry const &g = R->S.g;
+	uint64_t const nl = R->msa->n;
+	size_t const per_col = ((size_t) R->cap + 1) * sizeof(uint2);
+	auto const key = std::make_tuple(R->m, R->n, R->L, R->cap, R->size, nl, g.B, g.C, ctx->opt("store_states", -1));
+	auto it = ctx->plans.find(key);
+	fsq_ctx::mem_plan plan;
+	if (ctx->plans.end() != it && 0 == ctx->opt("mem_limit", 0) && 0 == ctx->opt("window_blocks", 0)) plan = it->second;
 	else
 	{
-		CK(launch_dp_rebuild(D, ctx->stream));
-		ctx->stats["kernel_launches"] += 2;
+		size_t const avail = plannable_bytes(ctx);
+		size_t const other = (size_t) nl * 64 + (size_t) R->tb_len * 32 + ((size_t) 1 << 30);
+		size_t const states = (size_t) (R->state_stride * 4 * nl);
+		int64_t const want_states = ctx->opt("store_states", -1);
+		int64_t const forced = ctx->opt("window_blocks", 0);
+		plan.per_window = g.B;
+		if (forced > 0) plan.per_window = (uint32_t) std::min <int64_t>(forced, g.B);
+		else if ((size_t) nl * per_col + other > avail)
+		{
+			size_t const room = avail > other ? avail - other : 0;
+			uint64_t blocks = room / per_col / g.C;
+			// whole resident waves when more than one fits
+			uint64_t const wave = std::max <uint64_t>(1, (uint64_t) ctx->prop.multiProcessorCount);
+			if (blocks > wave) blocks = blocks / wave * wave;
+			if (0 == blocks)
+				return fail(ctx, FSQ_ERR_NOMEM, "the top lists of one block of %u columns (%zu bytes per column at bound %u) do not fit the %zu bytes available", g.C, per_col, R->cap, room);
+			plan.per_window = (uint32_t) std::min <uint64_t>(blocks, g.B);
+		}
+		plan.whole = plan.per_window >= g.B;
+		// Pass B keeps the state of every column when 4 m n bytes fit comfortably (option store_states: -1 auto, 0 never,
+		// 1 always); the states at the segment boundaries are then a gather instead of a third scan.
+		plan.keep = g.chunked && 0 != want_states && plan.whole && ((1 == want_states) || states + (size_t) nl * per_col + other < avail);
+		// the ranks' collectives must line up: they all take the cheaper path only if every one of them can
+		uint32_t bits = (plan.whole ? 1u : 0u) | (plan.keep ? 2u : 0u);
+		int const rc = run_agree_and(R, &bits);
+		if (rc) return rc;
+		plan.whole = 0 != (bits & 1u);
+		plan.keep = plan.whole && 0 != (bits & 2u);
+		ctx->plans[key] = plan;
 	}
-	pd.stop();
-	return FSQ_OK;        // (a copy from pageable host memory has left the source when cudaMemcpyAsync returns)
-}
-
-// The last entry (segmentation_lp_context.cc:165-185), on the rank that holds the last column; and this rank's
-// "top list too short" flag (1 + column, 0 = none).
-int shard_dp_final(fsq_shard *P, uint32_t *overflow)
-{
-	fsq_ctx *ctx = P->ctx;
-	phase pd(ctx, "dp");
-	if (P->c1 == P->n)
+	R->whole = plan.whole;
+	R->windows.clear();
+	for (uint32_t b = 0; b < g.B; b += plan.per_window)
 	{
-		CK(launch_dp_final(P->dp(), ctx->stream));
-		ctx->stats["kernel_launches"] += 1;
+		fsq_run::window w;
+		w.b0 = b; w.b1 = std::min(g.B, b + plan.per_window);
+		w.col0 = (uint64_t) w.b0 * g.C; w.col1 = std::min <uint64_t>(nl, (uint64_t) w.b1 * g.C);
+		R->windows.push_back(w);
 	}
-	uint32_t h_flags[2] = {0, 0};
-	CK(cudaMemcpyAsync(h_flags, P->flags.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-	pd.stop();
-	CK(cudaStreamSynchronize(ctx->stream));
-	*overflow = h_flags[1];
-	ctx->stats["dp_rounds"] += P->rounds;
-	ctx->stats["dp_chunks"] = P->n_chunks;
+	bool keep = plan.keep;
+	if (keep && !R->states.p && cudaSuccess != R->states.alloc(ctx, (size_t) (R->state_stride * 4 * nl)))
+	{
+		cudaGetLastError();
+		if (R->size > 1) return fail(ctx, FSQ_ERR_NOMEM, "the states of %llu columns no longer fit (the plan the ranks agreed on keeps them)", (unsigned long long) nl);
+		keep = false;
+	}
+	if (!keep) R->states.release();
+	ctx->stats["store_states"] = keep ? 1 : 0;
+	ctx->stats["windows"] = (double) R->windows.size();
+	uint64_t widest = 0;
+	for (auto const &w : R->windows) widest = std::max(widest, w.col1 - w.col0);
+	if (cudaSuccess != R->toplist.alloc(ctx, (size_t) widest * per_col))
+	{
+		cudaGetLastError();
+		return fail(ctx, FSQ_ERR_NOMEM, "%zu bytes of top lists (%llu columns at bound %u) do not fit", (size_t) widest * per_col, (unsigned long long) widest, R->cap);
+	}
 	return FSQ_OK;
 }
 
-// Traceback over the (complete, global) table -- segmentation_lp_context.cc:191-224 -- on the device by pointer doubling;
-// every rank does the same.  Leaves the traceback on the device (text order) and on the host.
-int shard_traceback(fsq_shard *P)
+// Tables and control words as they stand before the first round.
+int run_reset_tables(fsq_run *R)
 {
-	fsq_ctx *ctx = P->ctx;
-	host_watch hw(ctx, "traceback");
+	fsq_ctx *ctx = R->ctx;
+	uint64_t const nl = R->msa->n;
+	if (!R->tbx_max.p)
+	{
+		CK(R->tbx_max.alloc(ctx, R->tb_len * 4)); CK(R->tbx_lb.alloc(ctx, R->tb_len * 4)); CK(R->tbx_size.alloc(ctx, R->tb_len * 4));
+		CK(R->mk.alloc(ctx, R->dp_size * 8)); CK(R->lev.alloc(ctx, (size_t) R->n_levels * R->n_blk * 4)); CK(R->ctl.alloc(ctx, N_CONTROL * 4));
+		CK(R->cnt.alloc(ctx, nl * 4)); CK(R->h0.alloc(ctx, nl * 4));
+		CK(R->chunk_level.alloc(ctx, (size_t) R->n_chunks * 8));
+		if (!R->xflags.p) CK(R->xflags.alloc(ctx, ((size_t) R->size + 1) * 16));
+		CK(R->h_ctl.alloc(ctx, N_CONTROL * 4));
+	}
+	// entries the per-column DP writes start from 0 (the first round's stand-in for "nothing known"); the ones the
+	// reference never writes keep its defaults; masks and rmq cells start from values that index inside the table
+	CK(cudaMemsetAsync(R->tbx_max.p, 0xff, R->tb_len * 4, ctx->stream));
+	CK(cudaMemsetAsync(R->tb_max(), 0, (size_t) R->n_entries * 4, ctx->stream));
+	CK(cudaMemsetAsync(R->tbx_size.p, 0xff, R->tb_len * 4, ctx->stream));
+	CK(cudaMemsetAsync(R->tbx_lb.p, 0, R->tb_len * 4, ctx->stream));
+	CK(cudaMemsetAsync(R->mk.p, 0xff, R->dp_size * 8, ctx->stream));
+	CK(cudaMemsetAsync(R->lev.p, 0, (size_t) R->n_levels * R->n_blk * 4, ctx->stream));
+	CK(cudaMemsetAsync(R->ctl.p, 0, N_CONTROL * 4, ctx->stream));
+	R->single_chain = false;
+	return FSQ_OK;
+}
+
+// Pass B over the blocks of one window with the current top-list bound.
+int run_scan_window(fsq_run *R, fsq_run::window const &w)
+{
+	fsq_ctx *ctx = R->ctx;
+	geometry const &g = R->S.g;
+	phase pb(ctx, "pass_b");
+	block_args A;
+	fill_common(A, R->msa, g);
+	A.mode = MODE_EXACT;
+	A.first_block = w.b0;
+	A.st_a = R->S.st_a.as <uint32_t>();
+	A.code = R->S.code.as <uint16_t>();
+	A.oldvals = R->S.oldvals.as <uint32_t>();
+	A.R = R->S.R.as <uint32_t>();
+	A.toplist = R->toplist.as <uint2>();
+	A.list_col0 = w.col0;
+	A.cap = R->cap;
+	A.cnt = R->cnt.as <uint32_t>();
+	A.h0 = R->h0.as <uint32_t>();
+	A.states = R->states.as <uint32_t>();
+	A.state_stride = R->state_stride;
+	CK(launch_scan(A, w.b1 - w.b0, g, true, ctx->stream));
+	pb.stop();
+	ctx->stats["kernel_launches"] += 1;
+	return FSQ_OK;
+}
+
+// The DP arguments for the entries computed at the local columns [col0, col1) of this rank (a window), or all of them.
+dp_args run_dp_args(fsq_run const *R, fsq_run::window const *w)
+{
+	dp_args D;
+	memset(&D, 0, sizeof D);
+	uint64_t const L = R->L;
+	D.m = R->m; D.n = R->n; D.L = L; D.col_base = R->c0;
+	D.t_first = R->t_first; D.t_last = R->t_last;
+	D.list_base = R->c0;
+	if (w)
+	{
+		uint64_t const g0 = R->c0 + w->col0, g1 = R->c0 + w->col1;
+		uint64_t const lo = g0 + 1 > L ? g0 + 1 - L : 0, hi = g1 + 1 > L ? g1 + 1 - L : 0;
+		D.t_first = (uint32_t) std::min <uint64_t>(lo, R->n_entries);
+		D.t_last = (uint32_t) std::min <uint64_t>(hi, R->n_entries);
+		D.list_base = g0;
+	}
+	D.toplist = R->toplist.as <uint2>(); D.cap = R->cap; D.cnt = R->cnt.as <uint32_t>(); D.h0 = R->h0.as <uint32_t>();
+	D.tb_max = R->tb_max(); D.tb_lb = R->tb_lb(); D.tb_size = R->tb_size();
+	D.mk = R->mk.as <uint64_t>();
+	D.lev = R->lev.as <uint32_t>(); D.n_blk = R->n_blk; D.n_levels = R->n_levels;
+	D.n_entries = R->n_entries;
+	D.chunk = R->single_chain ? (R->n_entries + 63) / 64 * 64 : R->chunk;
+	D.n_chunks = R->single_chain ? 1 : R->n_chunks;
+	D.chunk_level = R->chunk_level.as <uint32_t>();
+	D.flags = R->control();
+	D.bound_on_device = 1;
+	D.skip_when_done = 1;
+	// what this launch's chains can read: their own entries and the look-back before them
+	uint64_t const back = R->back_bound;
+	D.w_first = (uint32_t) ((D.t_first > back ? D.t_first - back : 0) & ~63ull);
+	D.w_last = (R->c1 == R->n && (!w || R->c0 + w->col1 == R->n)) ? R->n_entries : D.t_last;
+	// the guess levels what no round has made final: everything while several ranks iterate together, the window's
+	// entries when a single rank walks its windows in order
+	D.lvl_first = 0; D.lvl_last = R->n_entries;
+	if (1 == R->size && w) { D.lvl_first = D.t_first; D.lvl_last = D.t_last; }
+	return D;
+}
+
+// One DP round over the given windows: between rounds the guess (or only the rebuild), then every chain once against
+// the table as it stands, then the ranks' slices and flags travel and the decision is merged on the device.
+int run_enqueue_round(fsq_run *R, uint32_t round_no, size_t w_begin, size_t w_end, bool guess, bool rescan)
+{
+	fsq_ctx *ctx = R->ctx;
+	uint32_t *ctl = R->control();
+	int rc;
+	uint32_t chains = 0;
+	for (size_t wi = w_begin; wi < w_end; ++wi)
+	{
+		fsq_run::window const &w = R->windows[wi];
+		bool const whole = 1 == R->windows.size();      // (of this rank: the lists of all its columns are in the buffer)
+		dp_args D = run_dp_args(R, whole ? nullptr : &w);
+		if (round_no > 1 && (whole || 1 == R->size || wi == w_begin))
+		{
+			// several ranks with windows: one guess over the whole table per round, before the first window
+			dp_args G = (whole || 1 == R->size) ? D : run_dp_args(R, nullptr);
+			phase pd(ctx, "dp");
+			if (guess) { CK(launch_dp_guess(G, ctx->stream)); ctx->stats["kernel_launches"] += 5; }
+			else { CK(launch_dp_rebuild(G, ctx->stream)); ctx->stats["kernel_launches"] += 2; }
+			pd.stop();
+		}
+		if (rescan && (rc = run_scan_window(R, w))) return rc;
+		phase pd(ctx, "dp");
+		if (1 == round_no) { D.bound_on_device = 0; D.reach_bound = 0; }
+		if (D.t_first < D.t_last) chains += (D.t_last - 1) / D.chunk - D.t_first / D.chunk + 1;
+		CK(launch_dp_chains(D, ctx->stream));
+		pd.stop();
+		ctx->stats["kernel_launches"] += 1;
+	}
+	uint32_t *xs = R->xflags.as <uint32_t>();
+	uint32_t *mine = xs + 4 * (size_t) R->rank;
+	{
+		phase pd(ctx, "dp");
+		CK(launch_dp_round_end(ctl, 1 == round_no ? 1u : 0u, mine, ctx->stream));
+		pd.stop();
+	}
+	if (R->size > 1)
+	{
+		phase px(ctx, "exchange");
+		R->comm->group_begin();
+		cudaError_t e1 = R->comm->all_gather(R->tbx_max.as <uint32_t>() + (size_t) R->rank * R->n_per, R->tbx_max.p, (size_t) R->n_per * 4, ctx->stream);
+		cudaError_t e2 = R->comm->all_gather(mine, xs, 16, ctx->stream);
+		cudaError_t e3 = R->comm->group_end();
+		if (cudaSuccess != e1 || cudaSuccess != e2 || cudaSuccess != e3)
+			return fail(ctx, FSQ_ERR_CUDA, "exchange of the DP table slices failed: %s", R->comm->error.empty() ? "CUDA error" : R->comm->error.c_str());
+		px.stop();
+	}
+	phase pd(ctx, "dp");
+	CK(launch_dp_round_merge(ctl, xs, (uint32_t) R->size, round_no, R->back_bound, (1 == R->size && chains <= 1) ? 1u : 0u, ctx->stream));
+	pd.stop();
+	ctx->stats["kernel_launches"] += 2;
+	return FSQ_OK;
+}
+
+// The last entry (segmentation_lp_context.cc:165-185), on the rank that holds the last column; then every rank learns
+// whether any list was too short, and (several ranks) receives the rest of the table.
+int run_enqueue_final(fsq_run *R, bool rescan_last_window)
+{
+	fsq_ctx *ctx = R->ctx;
+	uint32_t *ctl = R->control();
+	if (R->c1 == R->n)
+	{
+		if (rescan_last_window)
+		{
+			int const rc = run_scan_window(R, R->windows.back());
+			if (rc) return rc;
+		}
+		phase pd(ctx, "dp");
+		dp_args D = run_dp_args(R, 1 == R->windows.size() ? nullptr : &R->windows.back());
+		CK(launch_dp_final(D, ctx->stream));
+		pd.stop();
+		ctx->stats["kernel_launches"] += 1;
+	}
+	if (R->size > 1)
+	{
+		uint32_t *xs = R->xflags.as <uint32_t>();
+		uint32_t *mine = xs + 4 * (size_t) R->rank;
+		CK(launch_dp_round_end(ctl, 0, mine, ctx->stream));
+		phase px(ctx, "exchange");
+		R->comm->group_begin();
+		size_t const off = (size_t) R->rank * R->n_per, bytes = (size_t) R->n_per * 4;
+		cudaError_t e = R->comm->all_gather(R->tbx_max.as <uint32_t>() + off, R->tbx_max.p, bytes, ctx->stream);
+		if (cudaSuccess == e) e = R->comm->all_gather(R->tbx_lb.as <uint32_t>() + off, R->tbx_lb.p, bytes, ctx->stream);
+		if (cudaSuccess == e) e = R->comm->all_gather(R->tbx_size.as <uint32_t>() + off, R->tbx_size.p, bytes, ctx->stream);
+		if (cudaSuccess == e) e = R->comm->all_gather(mine, xs, 16, ctx->stream);
+		cudaError_t const e2 = R->comm->group_end();
+		if (cudaSuccess != e || cudaSuccess != e2)
+			return fail(ctx, FSQ_ERR_CUDA, "exchange of the DP table failed: %s", R->comm->error.empty() ? "CUDA error" : R->comm->error.c_str());
+		px.stop();
+		CK(launch_dp_overflow_merge(ctl, xs, (uint32_t) R->size, ctx->stream));
+		ctx->stats["kernel_launches"] += 2;
+	}
+	return FSQ_OK;
+}
+
+// The control words to the host (blocking).
+int run_read_control(fsq_run *R)
+{
+	fsq_ctx *ctx = R->ctx;
+	CK(cudaMemcpyAsync(R->h_ctl.p, R->ctl.p, N_CONTROL * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	ctx->stats["host_syncs"] += 1;
+	memcpy(R->h, R->h_ctl.p, N_CONTROL * 4);
+	if (R->comm && !R->comm->error.empty()) return fail(ctx, FSQ_ERR_CUDA, "%s", R->comm->error.c_str());
+	return FSQ_OK;
+}
+
+// ---- traceback, reduction, reduced segments, their states: everything behind the DP that needs no host decision ----------
+int run_alloc_tail(fsq_run *R)
+{
+	fsq_ctx *ctx = R->ctx;
+	if (R->tr_lb.p) return FSQ_OK;
+	uint32_t const tb = R->t_bound, rb = R->rows_bound;
+	uint32_t levels = 1;
+	while ((1ull << levels) <= R->dp_size / R->L + 1) ++levels;
+	CK(R->jump.alloc(ctx, (size_t) levels * R->dp_size * 4));
+	CK(R->tr_lb.alloc(ctx, (size_t) tb * 4)); CK(R->tr_rb.alloc(ctx, (size_t) tb * 8)); CK(R->tr_max.alloc(ctx, (size_t) tb * 4)); CK(R->tr_size.alloc(ctx, (size_t) tb * 4));
+	CK(R->next_own.alloc(ctx, ((size_t) rb + 1) * 4)); CK(R->nsize_own.alloc(ctx, ((size_t) rb + 1) * 4));
+	if (R->size > 1)
+	{
+		CK(R->pos_all.alloc(ctx, ((size_t) R->size + 1) * 4));
+		CK(R->next_all.alloc(ctx, (size_t) R->size * (rb + 1) * 4)); CK(R->nsize_all.alloc(ctx, (size_t) R->size * (rb + 1) * 4));
+		CK(R->next.alloc(ctx, (size_t) tb * 4)); CK(R->nsize.alloc(ctx, (size_t) tb * 4));
+	}
+	uint32_t wl = 1;
+	while ((1ull << wl) <= tb) ++wl;
+	CK(R->walk_jump.alloc(ctx, (size_t) wl * tb * 4));
+	CK(R->red_lb.alloc(ctx, (size_t) tb * 8)); CK(R->red_rb.alloc(ctx, (size_t) tb * 8)); CK(R->red_size.alloc(ctx, (size_t) tb * 4)); CK(R->red_pos.alloc(ctx, (size_t) tb * 4));
+	return FSQ_OK;
+}
+
+int run_enqueue_traceback(fsq_run *R)
+{
+	fsq_ctx *ctx = R->ctx;
+	int rc = run_alloc_tail(R);
+	if (rc) return rc;
 	phase pt(ctx, "traceback");
 	trace_args TA;
 	memset(&TA, 0, sizeof TA);
-	TA.tb_lb = P->tb_lb.as <uint32_t>(); TA.tb_max = P->tb_max.as <uint32_t>(); TA.tb_size = P->tb_size.as <uint32_t>();
-	TA.L = (uint32_t) P->L; TA.dp_size = (uint32_t) P->dp_size;
+	TA.tb_lb = R->tb_lb(); TA.tb_max = R->tb_max(); TA.tb_size = R->tb_size();
+	TA.L = (uint32_t) R->L; TA.dp_size = (uint32_t) R->dp_size;
 	TA.levels = 1;
-	while ((1ull << TA.levels) <= P->dp_size / P->L + 1) ++TA.levels;
-	dbuf jump, count;
-	CK(jump.alloc(ctx, (size_t) TA.levels * P->dp_size * 4)); CK(count.alloc(ctx, 4));
-	TA.jump = jump.as <uint32_t>(); TA.count = count.as <uint32_t>();
+	while ((1ull << TA.levels) <= R->dp_size / R->L + 1) ++TA.levels;
+	TA.jump = R->jump.as <uint32_t>(); TA.ctl = R->control();
+	TA.t_bound = R->t_bound;
+	TA.out_lb = R->tr_lb.as <uint32_t>(); TA.out_rb = R->tr_rb.as <uint64_t>(); TA.out_max = R->tr_max.as <uint32_t>(); TA.out_size = R->tr_size.as <uint32_t>();
+	TA.c0 = R->c0; TA.c1 = R->c1;
 	CK(launch_trace_tables(TA, ctx->stream));
-	ctx->stats["kernel_launches"] += 1;
-	uint32_t T = 0;
-	CK(cudaMemcpyAsync(&T, count.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
-	P->T = T;
-	CK(P->tr_lb.alloc(ctx, (size_t) T * 4)); CK(P->tr_rb.alloc(ctx, (size_t) T * 8)); CK(P->tr_max.alloc(ctx, (size_t) T * 4)); CK(P->tr_size.alloc(ctx, (size_t) T * 4));
-	TA.out_lb = P->tr_lb.as <uint32_t>(); TA.out_rb = P->tr_rb.as <uint64_t>(); TA.out_max = P->tr_max.as <uint32_t>(); TA.out_size = P->tr_size.as <uint32_t>();
-	CK(launch_trace_gather(TA, T, ctx->stream));
-	ctx->stats["kernel_launches"] += 1;
-	CK(P->h_tb.alloc(ctx, (size_t) T * 20));
-	uint64_t *h_rb = P->h_tb.as <uint64_t>();
-	uint32_t *h_lb = (uint32_t *) (h_rb + T), *h_max = h_lb + T, *h_size = h_max + T;
-	CK(cudaMemcpyAsync(h_rb, P->tr_rb.p, (size_t) T * 8, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaMemcpyAsync(h_lb, P->tr_lb.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaMemcpyAsync(h_max, P->tr_max.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaMemcpyAsync(h_size, P->tr_size.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(launch_trace_gather(TA, ctx->stream));
+	ctx->stats["kernel_launches"] += 3;
 	pt.stop();
-	CK(cudaStreamSynchronize(ctx->stream));
-	(void) h_size;
-	P->K = h_max[T - 1];
-	// the traceback positions this rank holds the state of: right bounds in (c0, c1]
-	P->pos_first = (uint32_t) (std::upper_bound(h_rb, h_rb + T, P->c0) - h_rb);
-	P->pos_last = (uint32_t) (std::upper_bound(h_rb, h_rb + T, P->c1) - h_rb);
 	return FSQ_OK;
 }
 
-// The rows of the reduction's count lists for the traceback positions this rank owns (the others arrive by exchange).
-int shard_reduce_lists(fsq_shard *P)
+// Greedy reduction (segmentation_lp_context.cc:335-390) for the own traceback positions, from rows that are either list
+// rows (filled here from the top lists) or divergence rows (filled by the caller from a re-scan); then the walk.
+int run_enqueue_reduce(fsq_run *R, uint32_t row_kind)
 {
-	fsq_ctx *ctx = P->ctx;
-	uint32_t const width = P->K + 1;
-	CK(P->lists.alloc(ctx, (size_t) P->T * width * sizeof(uint2)));
+	fsq_ctx *ctx = R->ctx;
+	uint32_t const m = R->m;
 	phase pr(ctx, "reduce");
-	reduce_args R;
-	memset(&R, 0, sizeof R);
-	R.T = P->T; R.K = P->K; R.width = width;
-	R.tb_rb = P->tr_rb.as <uint64_t>(); R.tb_size = P->tr_size.as <uint32_t>();
-	R.lists = P->lists.as <uint2>();
-	R.toplist = P->toplist.as <uint2>(); R.cap = P->cap; R.cnt = P->cnt.as <uint32_t>(); R.col_base = P->c0;
-	R.pos_first = P->pos_first; R.pos_last = P->pos_last;
-	CK(launch_reduce_lists(R, ctx->stream));
-	ctx->stats["kernel_launches"] += 1;
-	pr.stop();
-	return FSQ_OK;
-}
-
-int start_reduced_copy(fsq_shard *P);
-
-// Greedy reduction (segmentation_lp_context.cc:335-390) from the complete lists; every rank does the same.
-int shard_reduce(fsq_shard *P, bool want_host_bounds)
-{
-	fsq_ctx *ctx = P->ctx;
-	uint32_t const T = P->T;
-	host_watch hw(ctx, "reduce");
-	phase pr(ctx, "reduce");
-	CK(P->d_next.alloc(ctx, (size_t) T * 4)); CK(P->d_nsize.alloc(ctx, (size_t) T * 4));
-	reduce_args R;
-	memset(&R, 0, sizeof R);
-	R.T = T; R.K = P->K; R.width = P->K + 1;
-	R.tb_rb = P->tr_rb.as <uint64_t>(); R.tb_size = P->tr_size.as <uint32_t>();
-	R.lists = P->lists.as <uint2>();
-	R.next = P->d_next.as <uint32_t>(); R.next_size = P->d_nsize.as <uint32_t>();
-	CK(launch_reduce(R, ctx->stream));
-	ctx->stats["kernel_launches"] += 1;
-	// the walk u -> next[u] + 1 from 0, on the device; the host learns the segment count and which segments are its own
-	walk_args W;
-	memset(&W, 0, sizeof W);
-	W.T = T;
-	W.levels = 1;
-	while ((1ull << W.levels) <= T) ++W.levels;
-	W.next = P->d_next.as <uint32_t>(); W.next_size = P->d_nsize.as <uint32_t>(); W.tb_rb = P->tr_rb.as <uint64_t>();
-	CK(P->walk_jump.alloc(ctx, (size_t) W.levels * T * 4)); CK(P->walk_info.alloc(ctx, 16)); CK(P->h_info.alloc(ctx, 16));
-	CK(P->d_red_lb.alloc(ctx, (size_t) T * 8)); CK(P->d_red_rb.alloc(ctx, (size_t) T * 8)); CK(P->d_red_size.alloc(ctx, (size_t) T * 4));
-	W.jump = P->walk_jump.as <uint32_t>(); W.info = P->walk_info.as <uint32_t>();
-	W.out_lb = P->d_red_lb.as <uint64_t>(); W.out_rb = P->d_red_rb.as <uint64_t>(); W.out_size = P->d_red_size.as <uint32_t>();
-	W.c0 = P->c0; W.c1 = P->c1;
-	CK(launch_walk(W, ctx->stream));
-	ctx->stats["kernel_launches"] += 1;
-	CK(cudaMemcpyAsync(P->h_info.p, P->walk_info.p, 12, cudaMemcpyDeviceToHost, ctx->stream));
-	pr.stop();
-	CK(cudaStreamSynchronize(ctx->stream));
-	uint32_t const n_red = P->h_info.as <uint32_t>()[0];
-	P->seg_first = P->h_info.as <uint32_t>()[1];
-	P->seg_last = P->h_info.as <uint32_t>()[2];
-	P->n_reduced = n_red;
-	P->red_lb.clear(); P->red_rb.clear(); P->red_size.clear();
-	P->red_on_host = false;
-	if (!want_host_bounds) return FSQ_OK;      // column shards fetch them on request (fsq_shard_bounds): they are replicated
-	return start_reduced_copy(P);
-}
-
-// Host copies of the reduced bounds (what segmentation_container holds): started here, completed by finish_reduced().
-int start_reduced_copy(fsq_shard *P)
-{
-	fsq_ctx *ctx = P->ctx;
-	uint32_t const n_red = P->n_reduced;
-	CK(P->h_red.alloc(ctx, (size_t) std::max <uint32_t>(n_red, 1) * 20));
+	reduce_args A;
+	memset(&A, 0, sizeof A);
+	A.ctl = R->control();
+	A.m = m; A.width = R->cap + 1; A.row_kind = row_kind;
+	A.rows_bound = R->rows_bound;
+	A.tb_rb = R->tr_rb.as <uint64_t>(); A.tb_size = R->tr_size.as <uint32_t>();
+	size_t const row_bytes = row_kind ? (size_t) m * 4 : (size_t) A.width * sizeof(uint2);
+	if (0 == row_kind)
 	{
-		uint64_t *h_lb = P->h_red.as <uint64_t>(), *h_rb = h_lb + n_red;
-		uint32_t *h_sz = (uint32_t *) (h_rb + n_red);
-		CK(cudaMemcpyAsync(h_lb, P->d_red_lb.p, (size_t) n_red * 8, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(h_rb, P->d_red_rb.p, (size_t) n_red * 8, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(h_sz, P->d_red_size.p, (size_t) n_red * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	}
-	P->red_pending = true;
-	return FSQ_OK;
-}
-
-// After the stream has drained: the reduced bounds as host vectors.
-int finish_reduced(fsq_shard *P)
-{
-	fsq_ctx *ctx = P->ctx;
-	if (P->red_on_host) return FSQ_OK;
-	if (!P->red_pending)
-	{
-		int const rc = start_reduced_copy(P);
-		if (rc) return rc;
-	}
-	CK(cudaStreamSynchronize(ctx->stream));
-	uint32_t const R = P->n_reduced;
-	uint64_t const *h_lb = P->h_red.as <uint64_t>(), *h_rb = h_lb + R;
-	uint32_t const *h_sz = (uint32_t const *) (h_rb + R);
-	P->red_lb.assign(h_lb, h_lb + R);
-	P->red_rb.assign(h_rb, h_rb + R);
-	P->red_size.assign(h_sz, h_sz + R);
-	P->red_pending = false;
-	P->red_on_host = true;
-	return FSQ_OK;
-}
-
-// (a, d) at the right bounds of this rank's reduced segments (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35):
-// a gather out of the states pass B kept, else a re-scan of the blocks that hold them (pass C).
-int shard_reduced_states(fsq_shard *P)
-{
-	fsq_ctx *ctx = P->ctx;
-	uint32_t const m = P->m;
-	uint32_t const cnt = P->seg_last - P->seg_first;
-	host_watch hw(ctx, "reduced_states");
-	CK(P->red_a.alloc(ctx, (size_t) std::max <uint32_t>(cnt, 1) * m * 4)); CK(P->red_d.alloc(ctx, (size_t) std::max <uint32_t>(cnt, 1) * m * 4));
-	if (cnt && P->states.p)
-	{
-		phase pc(ctx, "pass_c");
-		dim3 const grid(cnt, (m + 255) / 256);
-		gather_stored_states_kernel <<<grid, 256, 0, ctx->stream>>>(P->states.as <uint32_t>(), P->state_stride, P->d_red_rb.as <uint64_t>() + P->seg_first, m, P->S.g.C, P->c0,
-			P->S.oldvals.as <uint32_t>(), P->S.R.as <uint32_t>(), P->red_a.as <uint32_t>(), P->red_d.as <uint32_t>());
-		CK(cudaGetLastError());
-		pc.stop();
+		CK(R->rows.alloc(ctx, (size_t) R->rows_bound * row_bytes));
+		A.own_rows = R->rows.p;
+		A.toplist = R->toplist.as <uint2>(); A.cap = R->cap; A.cnt = R->cnt.as <uint32_t>(); A.col_base = R->c0;
+		CK(launch_reduce_lists(A, ctx->stream));
 		ctx->stats["kernel_launches"] += 1;
 	}
-	int rc = FSQ_OK;
-	if (P->red_pending || (cnt && !P->states.p))
+	A.own_rows = R->rows.p;
+	A.rank = (uint32_t) R->rank; A.size = (uint32_t) R->size;
+	if (R->size > 1)
 	{
-		if ((rc = finish_reduced(P))) return rc;      // drains the stream
+		// the first rows of every rank: where a run of this rank's last positions continues
+		A.halo = std::min(R->halo, R->rows_bound);
+		CK(R->halo_rows.alloc(ctx, (size_t) R->size * A.halo * row_bytes));
+		phase px(ctx, "exchange");
+		if (cudaSuccess != R->comm->all_gather(R->rows.p, R->halo_rows.p, (size_t) A.halo * row_bytes, ctx->stream))
+			return fail(ctx, FSQ_ERR_CUDA, "exchange of the reduction rows failed: %s", R->comm->error.c_str());
+		px.stop();
+		CK(launch_rank_positions(A.tb_rb, A.ctl, R->n_per, (uint32_t) R->size, R->pos_all.as <uint32_t>(), ctx->stream));
+		A.halo_rows = R->halo_rows.p;
+		A.pos_first_all = R->pos_all.as <uint32_t>();
+		ctx->stats["kernel_launches"] += 1;
 	}
-	else
-		CK(cudaStreamSynchronize(ctx->stream));
-	if (cnt && P->states.p)
-		P->states.release();
-	else if (cnt)
+	A.next = R->next_own.as <uint32_t>(); A.next_size = R->nsize_own.as <uint32_t>();
+	CK(launch_reduce(A, ctx->stream));
+	ctx->stats["kernel_launches"] += 1;
+	uint32_t const *next = A.next, *nsize = A.next_size;
+	if (R->size > 1)
 	{
-		std::vector <uint64_t> cols(cnt);
-		for (uint32_t i = 0; i < cnt; ++i) cols[i] = P->red_rb[P->seg_first + i] - P->c0;
-		rc = dump_states(ctx, P->msa, P->S, cols, P->red_a.as <uint32_t>(), P->red_d.as <uint32_t>());
-		if (rc) return rc;
+		phase px(ctx, "exchange");
+		R->comm->group_begin();
+		cudaError_t e = R->comm->all_gather(R->next_own.p, R->next_all.p, ((size_t) R->rows_bound + 1) * 4, ctx->stream);
+		if (cudaSuccess == e) e = R->comm->all_gather(R->nsize_own.p, R->nsize_all.p, ((size_t) R->rows_bound + 1) * 4, ctx->stream);
+		cudaError_t const e2 = R->comm->group_end();
+		if (cudaSuccess != e || cudaSuccess != e2)
+			return fail(ctx, FSQ_ERR_CUDA, "exchange of the reduction's runs failed: %s", R->comm->error.c_str());
+		px.stop();
+		CK(launch_scatter_next(R->next_all.as <uint32_t>(), R->nsize_all.as <uint32_t>(), R->pos_all.as <uint32_t>(), (uint32_t) R->size, R->rows_bound, R->t_bound,
+			R->next.as <uint32_t>(), R->nsize.as <uint32_t>(), R->control(), ctx->stream));
+		ctx->stats["kernel_launches"] += 1;
+		next = R->next.as <uint32_t>(); nsize = R->nsize.as <uint32_t>();
 	}
+	// the walk u -> next[u] + 1 from 0, on the device
+	walk_args W;
+	memset(&W, 0, sizeof W);
+	W.t_bound = R->t_bound;
+	W.levels = 1;
+	while ((1ull << W.levels) <= R->t_bound) ++W.levels;
+	W.ctl = R->control();
+	W.next = next; W.next_size = nsize; W.tb_rb = R->tr_rb.as <uint64_t>();
+	W.jump = R->walk_jump.as <uint32_t>();
+	W.out_lb = R->red_lb.as <uint64_t>(); W.out_rb = R->red_rb.as <uint64_t>(); W.out_size = R->red_size.as <uint32_t>(); W.out_pos = R->red_pos.as <uint32_t>();
+	W.c0 = R->c0; W.c1 = R->c1;
+	CK(launch_walk(W, ctx->stream));
+	ctx->stats["kernel_launches"] += 1;
+	pr.stop();
 	return FSQ_OK;
 }
+
+// (a, d) at the right bounds of this rank's reduced segments out of the states pass B kept; `bound` segments at most.
+int run_enqueue_state_gather(fsq_run *R, uint32_t bound)
+{
+	fsq_ctx *ctx = R->ctx;
+	uint32_t const m = R->m;
+	CK(R->red_a.alloc(ctx, (size_t) std::max <uint32_t>(bound, 1) * m * 4)); CK(R->red_d.alloc(ctx, (size_t) std::max <uint32_t>(bound, 1) * m * 4));
+	if (0 == bound) return FSQ_OK;
+	phase pc(ctx, "pass_c");
+	dim3 const grid(bound, (m + 255) / 256);
+	gather_stored_states_kernel <<<grid, 256, 0, ctx->stream>>>(R->states.as <uint32_t>(), R->state_stride, R->red_rb.as <uint64_t>(), R->control(), m, R->S.g.C, R->c0,
+		R->S.oldvals.as <uint32_t>(), R->S.R.as <uint32_t>(), R->red_a.as <uint32_t>(), R->red_d.as <uint32_t>());
+	CK(cudaGetLastError());
+	pc.stop();
+	ctx->stats["kernel_launches"] += 1;
+	return FSQ_OK;
+}
+
+// The reduced bounds to the host (what segmentation_container holds); `count` entries.
+int run_enqueue_bounds_copy(fsq_run *R, uint32_t count)
+{
+	fsq_ctx *ctx = R->ctx;
+	CK(R->h_red.alloc(ctx, (size_t) std::max <uint32_t>(count, 1) * 20));
+	uint64_t *h_lb = R->h_red.as <uint64_t>(), *h_rb = h_lb + count;
+	uint32_t *h_sz = (uint32_t *) (h_rb + count);
+	CK(cudaMemcpyAsync(h_lb, R->red_lb.p, (size_t) count * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(h_rb, R->red_rb.p, (size_t) count * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(h_sz, R->red_size.p, (size_t) count * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	return FSQ_OK;
+}
+
+// Single-chain fallback when the rounds do not settle: the reference's own order, exact in one pass.  Several ranks take
+// turns, each behind the complete prefix.
+int run_sequential_dp(fsq_run *R, bool rescan)
+{
+	fsq_ctx *ctx = R->ctx;
+	int rc;
+	R->single_chain = true;
+	ctx->stats["dp_fallbacks"] += 1;
+	CK(cudaMemsetAsync(R->control() + F_DONE, 0, 4, ctx->stream));
+	for (int r = 0; r < R->size; ++r)
+	{
+		dp_args G = run_dp_args(R, nullptr);
+		G.skip_when_done = 0;
+		CK(launch_dp_rebuild(G, ctx->stream));
+		if (r == R->rank)
+			for (auto const &w : R->windows)
+			{
+				if (rescan && (rc = run_scan_window(R, w))) return rc;
+				dp_args D = run_dp_args(R, 1 == R->windows.size() ? nullptr : &w);
+				D.skip_when_done = 0;
+				D.bound_on_device = 0; D.reach_bound = 0xffffffffu;
+				// one chain over the window's entries
+				D.chunk = (R->n_entries + 63) / 64 * 64; D.n_chunks = 1;
+				CK(launch_dp_chains(D, ctx->stream));
+			}
+		if (R->size > 1 && cudaSuccess != R->comm->all_gather(R->tbx_max.as <uint32_t>() + (size_t) R->rank * R->n_per, R->tbx_max.p, (size_t) R->n_per * 4, ctx->stream))
+			return fail(ctx, FSQ_ERR_CUDA, "exchange of the DP table slices failed: %s", R->comm->error.c_str());
+	}
+	// the lists were judged by the chains just run: merge the ranks' verdicts
+	CK(cudaMemsetAsync(R->control() + F_WINDOW_ERR, 0, 4, ctx->stream));
+	return FSQ_OK;
+}
+
+} // namespace
+
+namespace {
 
 int check_shape(fsq_ctx *ctx, fsq_msa const *msa)
 {
@@ -1138,6 +1341,303 @@ int new_msa(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint32_t nsym, 
 		return fail(ctx, cudaErrorMemoryAllocation == e ? FSQ_ERR_NOMEM : FSQ_ERR_CUDA, "cudaMalloc of %llu bytes for the packed alignment: %s", bytes, cudaGetErrorString(e));
 	}
 	*out = msa;
+	return FSQ_OK;
+}
+
+} // namespace
+
+
+namespace {
+
+// The tail behind a settled DP table when pass B kept every column's state and the top lists are resident: traceback,
+// reduction, walk, state gather and the copies of the results, all enqueued; nothing here waits for the host.
+int run_enqueue_fast_tail(fsq_run *R, bool with_states, bool with_bounds)
+{
+	int rc;
+	if ((rc = run_enqueue_traceback(R))) return rc;
+	if ((rc = run_enqueue_reduce(R, 0))) return rc;
+	if (with_states && (rc = run_enqueue_state_gather(R, R->rows_bound))) return rc;
+	if (with_bounds && (rc = run_enqueue_bounds_copy(R, R->t_bound))) return rc;
+	return FSQ_OK;
+}
+
+__global__ void gather_rows_kernel(uint32_t const *rows_a, uint32_t const *rows_d, uint32_t const *red_pos, uint32_t const *ctl, uint32_t m, uint32_t *dst_a, uint32_t *dst_d)
+{
+	uint32_t const s = ctl[I_SEG_FIRST] + blockIdx.x;
+	if (s >= ctl[I_SEG_LAST]) return;
+	uint32_t const i = blockIdx.y * blockDim.x + threadIdx.x;
+	if (i >= m) return;
+	size_t const from = (size_t) (red_pos[s] - ctl[I_POS_FIRST]) * m + i, to = (size_t) blockIdx.x * m + i;
+	dst_a[to] = rows_a[from];
+	dst_d[to] = rows_d[from];
+}
+
+// The whole long path for this rank's columns.  On FSQ_ERR_NOT_REDUCIBLE *out still receives the traceback.
+int run_segment(fsq_run *R, fsq_segmentation **out)
+{
+	fsq_ctx *ctx = R->ctx;
+	uint32_t const m = R->m;
+	int rc;
+	if ((rc = run_prepare(R))) return rc;
+	geometry const &g = R->S.g;
+
+	// A round costs one chain's length of sequential work, the single-chain fallback as much as n_chunks rounds (and round r
+	// leaves the first r chains exact, so n_chunks rounds always suffice): give up on the rounds only after half of that.
+	// Slowly rising levels (thousands of distinct rows per segment) take 15-20 rounds where config 2 takes two.
+	int64_t max_rounds = ctx->opt("dp_max_rounds", 0);
+	if (max_rounds <= 0) max_rounds = std::max <int64_t>(16, R->n_chunks / 2);
+	max_rounds = std::max <int64_t>(2, max_rounds);
+	int64_t guess_rounds = ctx->opt("dp_guess_rounds", -1);           // after these the table is left to settle by itself
+	if (guess_rounds < 0) guess_rounds = max_rounds;
+
+	bool tail_done = false;
+	uint32_t resume_block = 0;            // one rank, windows: everything before this block's first entry is final
+	uint32_t total_rounds = 0;
+	auto grow_cap = [&](uint32_t proven) -> int {
+		if (R->cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list with cap = m");
+		// every value computed under the short lists is an upper bound of the true one: lists that reach this far are proven
+		// to suffice for what was computed so far; a quarter more, for what follows (windows) and as slack
+		uint64_t next = std::max <uint64_t>((uint64_t) proven + proven / 4 + 8, (uint64_t) R->cap + 1);
+		next = (next + 7) & ~7ull;
+		R->cap = (uint32_t) std::min <uint64_t>(m, next - 1);
+		ctx->stats["cap_retries"] += 1;
+		R->toplist.release();
+		R->rows.release();
+		return FSQ_OK;
+	};
+
+	while (true)
+	{
+		if ((rc = run_plan(R))) return rc;
+		bool const whole = R->whole;
+		tail_done = false;
+		if (whole || R->size > 1)
+		{
+			// rounds over everything this rank holds: the one window, or (several ranks) every window in every round
+			if ((rc = run_reset_tables(R))) return rc;
+			bool const rescan = R->windows.size() > 1;
+			if (!rescan && (rc = run_scan_window(R, R->windows[0]))) return rc;
+			bool const can_fast_tail = whole && nullptr != R->states.p && (size_t) R->rows_bound * m * 8 <= ((size_t) 1 << 30) && 0 == ctx->opt("keep_dp", 0);
+			uint32_t rounds = 0, batch = (1 == R->size && 1 == R->n_chunks) ? 1 : 2;
+			bool restart = false;
+			while (true)
+			{
+				for (uint32_t i = 0; i < batch && rounds < (uint32_t) max_rounds; ++i)
+				{
+					++rounds;
+					if ((rc = run_enqueue_round(R, rounds, 0, R->windows.size(), (int64_t) rounds - 1 <= guess_rounds, rescan))) return rc;
+				}
+				if ((rc = run_enqueue_final(R, rescan))) return rc;
+				bool const with_tail = can_fast_tail && rounds <= 2;
+				if (with_tail && (rc = run_enqueue_fast_tail(R, true, (size_t) R->t_bound * 20 <= ((size_t) 4 << 20)))) return rc;
+				if ((rc = run_read_control(R))) return rc;
+				if (R->h[F_WINDOW_ERR] && R->size > 1 && 0xffffffffu != R->back_bound) { R->back_bound = 0xffffffffu; restart = true; break; }
+				if (R->h[F_DONE]) { tail_done = with_tail; break; }
+				if (rounds >= (uint32_t) max_rounds)
+				{
+					// the guesses keep failing: the chains one after the other, exact in a single pass
+					R->back_bound = 0xffffffffu;
+					if ((rc = run_sequential_dp(R, rescan))) return rc;
+					if ((rc = run_enqueue_final(R, rescan))) return rc;
+					if ((rc = run_read_control(R))) return rc;
+					++rounds;
+					break;
+				}
+				batch = std::min <uint32_t>(8, rounds);
+			}
+			total_rounds += R->h[F_DONE] ? R->h[F_ROUNDS] : rounds;
+			if (restart) continue;
+		}
+		else
+		{
+			// one rank, the columns in windows over one list buffer: a window's entries settle (behind final ones) before the
+			// next window is scanned
+			if (0 == resume_block && (rc = run_reset_tables(R))) return rc;
+			bool overflow = false;
+			for (size_t wi = 0; wi < R->windows.size() && !overflow; ++wi)
+			{
+				fsq_run::window const &w = R->windows[wi];
+				if (w.b1 <= resume_block) continue;
+				if ((rc = run_scan_window(R, w))) return rc;
+				CK(cudaMemsetAsync(R->control(), 0, 8 * 4, ctx->stream));          // the DP words; the traceback's stay
+				R->single_chain = false;
+				uint32_t rounds = 0, batch = 2;
+				while (true)
+				{
+					for (uint32_t i = 0; i < batch && rounds < (uint32_t) max_rounds; ++i)
+					{
+						++rounds;
+						if ((rc = run_enqueue_round(R, rounds, wi, wi + 1, (int64_t) rounds - 1 <= guess_rounds, false))) return rc;
+					}
+					bool const last = wi + 1 == R->windows.size();
+					if (last && (rc = run_enqueue_final(R, false))) return rc;
+					if ((rc = run_read_control(R))) return rc;
+					if (R->h[F_WINDOW_ERR] && 0xffffffffu != R->back_bound) { R->back_bound = 0xffffffffu; rounds = 0; CK(cudaMemsetAsync(R->control(), 0, 8 * 4, ctx->stream)); continue; }
+					if (R->h[F_DONE]) break;
+					if (rounds >= (uint32_t) max_rounds)
+					{
+						// the guesses keep failing: this window's entries as one chain behind the final ones
+						R->back_bound = 0xffffffffu;
+						CK(cudaMemsetAsync(R->control() + F_DONE, 0, 4, ctx->stream));
+						{
+							dp_args G = run_dp_args(R, &w);
+							G.skip_when_done = 0;
+							CK(launch_dp_rebuild(G, ctx->stream));
+							dp_args D = G;
+							D.bound_on_device = 0; D.reach_bound = 0xffffffffu;
+							D.chunk = (R->n_entries + 63) / 64 * 64; D.n_chunks = 1;
+							CK(launch_dp_chains(D, ctx->stream));
+							ctx->stats["dp_fallbacks"] += 1;
+						}
+						if (last && (rc = run_enqueue_final(R, false))) return rc;
+						if ((rc = run_read_control(R))) return rc;
+						++rounds;
+						break;
+					}
+					batch = std::min <uint32_t>(8, rounds);
+				}
+				total_rounds += rounds;
+				if (R->h[F_OVERFLOW]) { overflow = true; resume_block = w.b0; }
+			}
+			if (overflow)
+			{
+				if ((rc = grow_cap(R->h[F_OVERFLOW]))) return rc;
+				continue;
+			}
+		}
+		if (0 == R->h[F_OVERFLOW]) break;
+		if ((rc = grow_cap(R->h[F_OVERFLOW]))) return rc;
+		resume_block = 0;
+	}
+	ctx->learned_cap[std::make_tuple(R->m, R->n, R->L)] = R->cap;      // later calls on this shape start from the bound that worked
+	ctx->stats["cap"] = R->cap;
+	ctx->stats["block_columns"] = g.C;
+	ctx->stats["blocks"] = g.B;
+	ctx->stats["warps"] = g.chunked ? g.T / 32 : g.n_warps;
+	ctx->stats["chunk"] = g.chunked ? g.E : 0;
+	ctx->stats["kernel"] = g.chunked ? 3 : 1;
+	ctx->stats["dp_rounds"] += total_rounds;
+	ctx->stats["dp_chunks"] = R->n_chunks;
+	ctx->stats["dp_reach"] = R->h[F_REACH];
+
+	fsq_segmentation *seg = new (std::nothrow) fsq_segmentation;
+	if (!seg) return fail(ctx, FSQ_ERR_NOMEM, "out of host memory");
+	struct guard { fsq_segmentation *&s; bool ok{false}; ~guard() { if (!ok) { fsq_segmentation_free(s); s = nullptr; } } } gd{seg};
+	seg->ctx = ctx; seg->m = m; seg->n = R->n; seg->L = R->L;
+
+	// ---- traceback (reference: segmentation_lp_context.cc:191-224) ----
+	bool const whole = R->whole;
+	if (!tail_done)
+	{
+		if ((rc = run_enqueue_traceback(R))) return rc;
+		if (whole && (rc = run_enqueue_reduce(R, 0))) return rc;       // harmless when K == m turns out below
+		if ((rc = run_read_control(R))) return rc;
+	}
+	seg->T = R->h[I_T];
+	seg->K = R->h[I_K];
+	if (ctx->opt("keep_dp", 0))
+	{
+		uint64_t const dp_size = R->dp_size;
+		seg->dp_lb.resize(dp_size); seg->dp_max.resize(dp_size); seg->dp_size.resize(dp_size);
+		CK(cudaMemcpyAsync(seg->dp_lb.data(), R->tb_lb(), dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(seg->dp_max.data(), R->tb_max(), dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(seg->dp_size.data(), R->tb_size(), dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));
+	}
+	// the traceback stays on the device with the handle; it is copied when asked for
+	seg->tr_lb.adopt(R->tr_lb); seg->tr_rb.adopt(R->tr_rb); seg->tr_max.adopt(R->tr_max); seg->tr_size.adopt(R->tr_size);
+	if (!(seg->K < m))
+	{
+		// generate_context.cc:192-200; the traceback stays available through the handle for inspection
+		gd.ok = true;
+		*out = seg;
+		return fail(ctx, FSQ_ERR_NOT_REDUCIBLE, "the maximum segment size %u is equal to the number of input sequences", seg->K);
+	}
+
+	// ---- greedy reduction (segmentation_lp_context.cc:335-390), then the states at the reduced right bounds
+	//      (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35) ----
+	uint32_t const pos_first = R->h[I_POS_FIRST], pos_last = R->h[I_POS_LAST];
+	if (!tail_done && !whole)
+	{
+		// the lists are gone (windows): the divergence arrays at the own traceback positions, from a re-scan, serve instead
+		host_watch hw(ctx, "reduced_states");
+		uint32_t const cnt = pos_last - pos_first;
+		std::vector <uint64_t> cols(cnt);
+		if (cnt)
+		{
+			CK(cudaMemcpyAsync(cols.data(), seg->tr_rb.as <uint64_t>() + pos_first, (size_t) cnt * 8, cudaMemcpyDeviceToHost, ctx->stream));
+			CK(cudaStreamSynchronize(ctx->stream));
+		}
+		for (auto &c : cols) c -= R->c0;
+		CK(R->rows.alloc(ctx, (size_t) R->rows_bound * m * 4)); CK(R->rows_a.alloc(ctx, (size_t) std::max <uint32_t>(cnt, 1) * m * 4));
+		if (cnt && (rc = dump_states(ctx, R->msa, R->S, cols, R->rows_a.as <uint32_t>(), R->rows.as <uint32_t>()))) return rc;
+		if ((rc = run_enqueue_reduce(R, 1))) return rc;
+		if ((rc = run_read_control(R))) return rc;
+	}
+	while (R->h[I_HALO_ERR])
+	{
+		// a run of merged segments went past the rows at hand of the ranks behind this one: more rows (every rank decides alike:
+		// the flag is merged below)
+		if (R->halo >= R->rows_bound) return fail(ctx, FSQ_ERR_INTERNAL, "the reduction ran out of rows with the complete halo");
+		R->halo = std::min <uint32_t>(R->rows_bound, R->halo * 8);
+		CK(cudaMemsetAsync(R->control() + I_HALO_ERR, 0, 4, ctx->stream));
+		if ((rc = run_enqueue_reduce(R, whole ? 0 : 1))) return rc;
+		if ((rc = run_read_control(R))) return rc;
+		tail_done = false;
+	}
+	uint32_t const n_red = R->h[I_NRED], seg_first = R->h[I_SEG_FIRST], seg_last = R->h[I_SEG_LAST];
+	uint32_t const own = seg_last - seg_first;
+	if (!tail_done)
+	{
+		if (R->states.p)
+		{
+			if ((rc = run_enqueue_state_gather(R, own))) return rc;
+		}
+		else if (!whole)
+		{
+			CK(R->red_a.alloc(ctx, (size_t) std::max <uint32_t>(own, 1) * m * 4)); CK(R->red_d.alloc(ctx, (size_t) std::max <uint32_t>(own, 1) * m * 4));
+			if (own)
+			{
+				gather_rows_kernel <<<dim3(own, (m + 255) / 256), 256, 0, ctx->stream>>>(R->rows_a.as <uint32_t>(), R->rows.as <uint32_t>(), R->red_pos.as <uint32_t>(), R->control(), m,
+					R->red_a.as <uint32_t>(), R->red_d.as <uint32_t>());
+				CK(cudaGetLastError());
+				ctx->stats["kernel_launches"] += 1;
+			}
+		}
+		else
+		{
+			// the states were not kept: a re-scan of the blocks that hold the reduced right bounds (pass C)
+			host_watch hw(ctx, "reduced_states");
+			std::vector <uint64_t> cols(own);
+			if (own)
+			{
+				CK(cudaMemcpyAsync(cols.data(), R->red_rb.as <uint64_t>() + seg_first, (size_t) own * 8, cudaMemcpyDeviceToHost, ctx->stream));
+				CK(cudaStreamSynchronize(ctx->stream));
+			}
+			for (auto &c : cols) c -= R->c0;
+			CK(R->red_a.alloc(ctx, (size_t) std::max <uint32_t>(own, 1) * m * 4)); CK(R->red_d.alloc(ctx, (size_t) std::max <uint32_t>(own, 1) * m * 4));
+			if (own && (rc = dump_states(ctx, R->msa, R->S, cols, R->red_a.as <uint32_t>(), R->red_d.as <uint32_t>()))) return rc;
+		}
+	}
+	bool const bounds_copied = tail_done && (size_t) R->t_bound * 20 <= ((size_t) 4 << 20);
+	uint32_t const copied = bounds_copied ? R->t_bound : n_red;
+	if (!bounds_copied)
+	{
+		if ((rc = run_enqueue_bounds_copy(R, n_red))) return rc;
+		CK(cudaStreamSynchronize(ctx->stream));
+		ctx->stats["host_syncs"] += 1;
+	}
+	{
+		uint64_t const *h_lb = R->h_red.as <uint64_t>(), *h_rb = h_lb + copied;
+		uint32_t const *h_sz = (uint32_t const *) (h_rb + copied);
+		seg->lb.assign(h_lb, h_lb + n_red);
+		seg->rb.assign(h_rb, h_rb + n_red);
+		seg->size.assign(h_sz, h_sz + n_red);
+	}
+	seg->own_first = seg_first; seg->own_last = seg_last;
+	seg->red_a.adopt(R->red_a); seg->red_d.adopt(R->red_d);
+	gd.ok = true;
+	*out = seg;
 	return FSQ_OK;
 }
 
@@ -1208,7 +1708,7 @@ int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
 		}
 		return FSQ_OK;
 	}
-	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", "whole_waves", nullptr};
+	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", "whole_waves", "mem_limit", "window_blocks", "halo", nullptr};
 	for (char const **k = known; *k; ++k)
 		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }
 	return fail(ctx, FSQ_ERR_ARG, "unknown option '%s'", key);
@@ -1396,140 +1896,49 @@ int fsq_pbwt_states(fsq_ctx *ctx, const fsq_msa *msa, const uint64_t *columns, u
 
 // ---- long path -----------------------------------------------------------------------------------------------------
 
-int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation **out)
+int fsq_segment_sharded(fsq_ctx *ctx, const fsq_msa *msa, fsq_comm *comm, uint64_t n_total, uint64_t L, fsq_segmentation **out)
 {
 	int rc = check_shape(ctx, msa);
 	if (rc) return rc;
 	if (!out) return fail(ctx, FSQ_ERR_ARG, "null out pointer");
+	*out = nullptr;
 	if (0 == L) return fail(ctx, FSQ_ERR_ARG, "segment length bound must be positive");
-	if (0 != msa->col0) return fail(ctx, FSQ_ERR_ARG, "fsq_segment needs an alignment that starts at column 0");
-	uint64_t const n = msa->n;
-	uint32_t const m = msa->m;
-	if (n < 2 * L) return fail(ctx, FSQ_ERR_SHORT, "n = %llu < 2L = %llu: short path", (unsigned long long) n, (unsigned long long) (2 * L));
+	if (n_total >= (1ull << 31)) return fail(ctx, FSQ_ERR_UNSUPPORTED, "n = %llu columns: positions are kept in 32 bits (n < 2^31)", (unsigned long long) n_total);
+	if (n_total < 2 * L) return fail(ctx, FSQ_ERR_SHORT, "n = %llu < 2L = %llu: short path", (unsigned long long) n_total, (unsigned long long) (2 * L));
 	CK(cudaSetDevice(ctx->device));
 	flush_phases(ctx);
 	if (!ctx->call_start) CK(cudaEventCreate(&ctx->call_start));
 	CK(cudaEventRecord(ctx->call_start, ctx->stream));
+	fsq_run run;
+	if ((rc = run_init(&run, ctx, msa, comm && comm->size > 1 ? comm : nullptr, n_total, L))) return rc;
+	rc = run_segment(&run, out);
+	// the run's buffers go back to the cache when `run` dies: nothing may still be using them
+	cudaStreamSynchronize(ctx->stream);
+	return rc;
+}
 
-	fsq_shard run;
-	fsq_shard *P = &run;
-	if ((rc = shard_init(P, ctx, msa, n, L))) return rc;
-	if ((rc = prepare_scan(ctx, msa, P->S))) return rc;
-	geometry const &g = P->S.g;
-
-	// ---- pass B + DP; the top-list bound grows until the DP proves the result exact ----
-	// A round costs one chain's length of sequential work, the single-chain fallback as much as n_chunks rounds (and round r
-	// leaves the first r chains exact, so n_chunks rounds always suffice): give up on the rounds only after half of that.
-	// Slowly rising levels (thousands of distinct rows per segment) take 15-20 rounds where config 2 takes two.
-	int64_t max_rounds = ctx->opt("dp_max_rounds", 0);
-	if (max_rounds <= 0) max_rounds = std::max <int64_t>(16, P->n_chunks / 2);
-	max_rounds = std::max <int64_t>(2, max_rounds);
-	int64_t guess_rounds = ctx->opt("dp_guess_rounds", -1);           // after these the table is left to settle by itself
-	if (guess_rounds < 0) guess_rounds = max_rounds;
-	while (true)
-	{
-		if ((rc = shard_scan(P))) return rc;
-		while (true)
-		{
-			uint32_t changed = 0, reach = 0;
-			if (0 == P->rounds && P->n_chunks > 1 && !P->single_chain && max_rounds > 2 && guess_rounds >= 1)
-			{
-				if ((rc = shard_dp_first_two_rounds(P, &changed, &reach))) return rc;
-			}
-			else if ((rc = shard_dp_round(P, &changed, &reach))) return rc;
-			if (1 == P->n_chunks || P->single_chain) break;      // a single chain is the reference's own order: exact as it stands
-			if (P->rounds > 1 && 0 == changed) break;            // nothing changed: every entry was computed from the table it is part of
-			if (P->rounds >= max_rounds)
-			{
-				// the guesses keep failing: one chain over everything, exact in a single round
-				P->single_chain = true;
-				ctx->stats["dp_fallbacks"] += 1;
-			}
-			else if (P->rounds <= guess_rounds)
-			{
-				if ((rc = shard_dp_sync(P, 1, reach))) return rc;
-			}
-		}
-		uint32_t ovf = 0;
-		if (P->final_done) ovf = P->final_overflow;
-		else if ((rc = shard_dp_final(P, &ovf))) return rc;
-		if (0 == ovf) break;
-		if (P->cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list at column %u with cap = m", ovf - 1);
-		uint64_t next = std::min <uint64_t>(m, (uint64_t) P->cap * 4);
-		{
-			// four times the refused bound unless the lists of that length do not fit: then twice (config 3 whole on one
-			// GPU: 127 -> 508 -> 2,032 would be 163 GB of lists next to 25 GB of alignment; 1,016 is enough and fits)
-			size_t free_b = 0, total_b = 0;
-			CK(cudaMemGetInfo(&free_b, &total_b));
-			size_t avail = free_b + P->toplist.bytes;
-			for (auto const &blk : ctx->dev_cache) avail += blk.bytes;
-			while (next / 2 > P->cap && (size_t) n * (next + 1) * sizeof(uint2) + ((size_t) 1 << 30) > avail) next /= 2;
-		}
-		P->cap = (uint32_t) next;
-		ctx->opts["cap"] = P->cap;          // later calls on this context start from the bound that worked
-		ctx->stats["cap_retries"] += 1;
-	}
-	ctx->stats["cap"] = P->cap;
-	ctx->stats["block_columns"] = g.C;
-	ctx->stats["blocks"] = g.B;
-	ctx->stats["warps"] = (g.blocked || g.chunked) ? g.T / 32 : g.n_warps;
-	ctx->stats["chunk"] = (g.blocked || g.chunked) ? g.E : 0;
-	ctx->stats["kernel"] = g.chunked ? 3 : (g.blocked ? 2 : 1);
-
-	// ---- traceback (reference: segmentation_lp_context.cc:191-224) ----
-	fsq_segmentation *seg = new (std::nothrow) fsq_segmentation;
-	if (!seg) return fail(ctx, FSQ_ERR_NOMEM, "out of host memory");
-	struct guard { fsq_segmentation *&s; bool ok{false}; ~guard() { if (!ok) { fsq_segmentation_free(s); s = nullptr; } } } gd{seg};
-	seg->ctx = ctx; seg->m = m; seg->n = n; seg->L = L;
-	if ((rc = shard_traceback(P))) return rc;
-	seg->T = P->T; seg->h_tb_bytes = P->h_tb.bytes; seg->h_tb = P->h_tb.detach();
-	seg->K = P->K;
-	if (ctx->opt("keep_dp", 0))
-	{
-		uint64_t const dp_size = P->dp_size;
-		seg->dp_lb.resize(dp_size); seg->dp_max.resize(dp_size); seg->dp_size.resize(dp_size);
-		CK(cudaMemcpyAsync(seg->dp_lb.data(), P->tb_lb.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(seg->dp_max.data(), P->tb_max.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaMemcpyAsync(seg->dp_size.data(), P->tb_size.p, dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		CK(cudaStreamSynchronize(ctx->stream));
-	}
-	if (!(seg->K < m))
-	{
-		// generate_context.cc:192-200; the traceback stays available through the handle for inspection
-		gd.ok = true;
-		*out = seg;
-		return fail(ctx, FSQ_ERR_NOT_REDUCIBLE, "the maximum segment size %u is equal to the number of input sequences", seg->K);
-	}
-
-	// ---- greedy reduction (segmentation_lp_context.cc:335-390), then the states at the reduced right bounds
-	//      (segmentation_lp_context.cc:229-332, update_pbwt_task.cc:13-35) ----
-	if ((rc = shard_reduce_lists(P))) return rc;
-	if ((rc = shard_reduce(P, true))) return rc;
-	if ((rc = shard_reduced_states(P))) return rc;
-	seg->lb = P->red_lb; seg->rb = P->red_rb; seg->size = P->red_size;
-	seg->d_bytes[0] = P->red_a.bytes; seg->d_bytes[1] = P->red_d.bytes;
-	seg->d_a = (uint32_t *) P->red_a.detach(); seg->d_d = (uint32_t *) P->red_d.detach();
-	CK(cudaStreamSynchronize(ctx->stream));
-	gd.ok = true;
-	*out = seg;
-	return FSQ_OK;
+int fsq_segment(fsq_ctx *ctx, const fsq_msa *msa, uint64_t L, fsq_segmentation **out)
+{
+	if (msa && 0 != msa->col0) return fail(ctx, FSQ_ERR_ARG, "fsq_segment needs an alignment that starts at column 0 (column shards go through fsq_segment_sharded)");
+	return fsq_segment_sharded(ctx, msa, nullptr, msa ? msa->n : 0, L, out);
 }
 
 void fsq_segmentation_free(fsq_segmentation *seg)
 {
-	if (!seg) return;
 	// the buffers go back to the context's workspace cache (the context must outlive its segmentations)
-	fsq_ctx *ctx = seg->ctx;
-	ctx->give(false, seg->d_a, seg->d_bytes[0]);
-	ctx->give(false, seg->d_d, seg->d_bytes[1]);
-	ctx->give(true, seg->h_tb, seg->h_tb_bytes);
-	ctx->give(true, seg->h_a, seg->h_bytes[0]);
-	ctx->give(true, seg->h_d, seg->h_bytes[1]);
 	delete seg;
 }
 
 uint32_t fsq_segmentation_count(const fsq_segmentation *seg) { return seg ? (uint32_t) seg->lb.size() : 0; }
 uint32_t fsq_segmentation_max_segment_size(const fsq_segmentation *seg) { return seg ? seg->K : 0; }
+
+int fsq_segmentation_own_range(const fsq_segmentation *seg, uint32_t *first, uint32_t *last)
+{
+	if (!seg || !first || !last) return FSQ_ERR_ARG;
+	*first = seg->own_first;
+	*last = seg->own_last;
+	return FSQ_OK;
+}
 
 int fsq_segmentation_bounds(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *size)
 {
@@ -1543,18 +1952,16 @@ int fsq_segmentation_bounds(const fsq_segmentation *seg, uint64_t *lb, uint64_t 
 static int fetch_states(fsq_segmentation *seg)
 {
 	fsq_ctx *ctx = seg->ctx;
-	if (seg->h_a) return FSQ_OK;
-	size_t const bytes = seg->lb.size() * (size_t) seg->m * 4;
+	if (seg->h_a.p) return FSQ_OK;
+	size_t const bytes = (size_t) (seg->own_last - seg->own_first) * seg->m * 4;
 	CK(cudaSetDevice(ctx->device));
 	phase pd(ctx, "states_d2h");
+	CK(seg->h_a.alloc(ctx, bytes)); CK(seg->h_d.alloc(ctx, bytes));
+	if (bytes)
 	{
-		hbuf ha, hd;
-		CK(ha.alloc(ctx, bytes)); CK(hd.alloc(ctx, bytes));
-		seg->h_bytes[0] = ha.bytes; seg->h_bytes[1] = hd.bytes;
-		seg->h_a = (uint32_t *) ha.detach(); seg->h_d = (uint32_t *) hd.detach();
+		CK(cudaMemcpyAsync(seg->h_a.p, seg->red_a.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(seg->h_d.p, seg->red_d.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 	}
-	CK(cudaMemcpyAsync(seg->h_a, seg->d_a, bytes, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaMemcpyAsync(seg->h_d, seg->d_d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
 	pd.stop();
 	CK(cudaStreamSynchronize(ctx->stream));
 	return FSQ_OK;
@@ -1566,9 +1973,9 @@ int fsq_segmentation_states(const fsq_segmentation *cseg, uint32_t *a, uint32_t 
 	if (!seg || !a || !d) return FSQ_ERR_ARG;
 	int const rc = fetch_states(seg);
 	if (rc) return rc;
-	size_t const bytes = seg->lb.size() * (size_t) seg->m * 4;
-	memcpy(a, seg->h_a, bytes);
-	memcpy(d, seg->h_d, bytes);
+	size_t const bytes = (size_t) (seg->own_last - seg->own_first) * seg->m * 4;
+	memcpy(a, seg->h_a.p, bytes);
+	memcpy(d, seg->h_d.p, bytes);
 	return FSQ_OK;
 }
 
@@ -1578,28 +1985,39 @@ int fsq_segmentation_states_view(const fsq_segmentation *cseg, const uint32_t **
 	if (!seg || !a || !d) return FSQ_ERR_ARG;
 	int const rc = fetch_states(seg);
 	if (rc) return rc;
-	*a = seg->h_a;
-	*d = seg->h_d;
+	*a = seg->h_a.as <uint32_t>();
+	*d = seg->h_d.as <uint32_t>();
 	return FSQ_OK;
 }
 
 uint32_t fsq_segmentation_traceback_count(const fsq_segmentation *seg) { return seg ? seg->T : 0; }
 
-// rb u64[T], then lb, max, size u32[T] each (shard_traceback)
-static void copy_traceback(void const *h_tb, uint32_t T, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
+// rb u64[T], then lb, max, size u32[T] each
+int fsq_segmentation_traceback(const fsq_segmentation *cseg, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
 {
-	uint64_t const *h_rb = static_cast <uint64_t const *>(h_tb);
+	fsq_segmentation *seg = const_cast <fsq_segmentation *>(cseg);
+	if (!seg || !lb || !rb || !max_size || !size) return FSQ_ERR_ARG;
+	fsq_ctx *ctx = seg->ctx;
+	uint32_t const T = seg->T;
+	if (0 == T || !seg->tr_rb.p) return FSQ_OK;
+	if (!seg->h_tb.p)
+	{
+		CK(cudaSetDevice(ctx->device));
+		CK(seg->h_tb.alloc(ctx, (size_t) T * 20));
+		uint64_t *h_rb = seg->h_tb.as <uint64_t>();
+		uint32_t *h_lb = (uint32_t *) (h_rb + T), *h_max = h_lb + T, *h_size = h_max + T;
+		CK(cudaMemcpyAsync(h_rb, seg->tr_rb.p, (size_t) T * 8, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_lb, seg->tr_lb.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_max, seg->tr_max.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(h_size, seg->tr_size.p, (size_t) T * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));
+	}
+	uint64_t const *h_rb = seg->h_tb.as <uint64_t>();
 	uint32_t const *h_lb = reinterpret_cast <uint32_t const *>(h_rb + T), *h_max = h_lb + T, *h_size = h_max + T;
 	std::copy(h_lb, h_lb + T, lb);
 	std::copy(h_rb, h_rb + T, rb);
 	std::copy(h_max, h_max + T, max_size);
 	std::copy(h_size, h_size + T, size);
-}
-
-int fsq_segmentation_traceback(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
-{
-	if (!seg || !lb || !rb || !max_size || !size) return FSQ_ERR_ARG;
-	if (seg->h_tb) copy_traceback(seg->h_tb, seg->T, lb, rb, max_size, size);
 	return FSQ_OK;
 }
 
@@ -1663,11 +2081,12 @@ int fsq_distinct_rows(fsq_ctx *ctx, const fsq_msa *msa, uint32_t *row_of_run, ui
 int fsq_segment_sets(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, uint32_t *run_off, uint32_t *ids_out, uint32_t *class_of_row, uint32_t *n_runs)
 {
 	if (!ctx || !seg || !run_off || !ids_out || !class_of_row || !n_runs) return fail(ctx, FSQ_ERR_ARG, "null argument");
-	if (s >= seg->lb.size()) return fail(ctx, FSQ_ERR_ARG, "segment %u out of range", s);
+	if (s < seg->own_first || s >= seg->own_last) return fail(ctx, FSQ_ERR_ARG, "segment %u is not among the ones whose state this handle holds: [%u, %u)", s, seg->own_first, seg->own_last);
 	CK(cudaSetDevice(ctx->device));
 	uint32_t const m = seg->m;
 	dbuf off, ids, cls, nruns;
-	int rc = sets_on_device(ctx, seg->d_a + (size_t) s * m, seg->d_d + (size_t) s * m, m, seg->lb[s], off, ids, cls, nruns);
+	size_t const at = (size_t) (s - seg->own_first) * m;
+	int rc = sets_on_device(ctx, seg->red_a.as <uint32_t>() + at, seg->red_d.as <uint32_t>() + at, m, seg->lb[s], off, ids, cls, nruns);
 	if (rc) return rc;
 	uint32_t runs = 0;
 	CK(cudaMemcpyAsync(&runs, nruns.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1683,13 +2102,15 @@ int fsq_segment_sets(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, uint
 int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, int32_t *W, uint32_t *runs_lhs, uint32_t *runs_rhs)
 {
 	if (!ctx || !seg || !W || !runs_lhs || !runs_rhs) return fail(ctx, FSQ_ERR_ARG, "null argument");
-	if ((size_t) s + 1 >= seg->lb.size()) return fail(ctx, FSQ_ERR_ARG, "segment pair %u out of range", s);
+	if (s < seg->own_first || (size_t) s + 1 >= seg->own_last) return fail(ctx, FSQ_ERR_ARG, "segment pair (%u, %u) is not among the segments whose state this handle holds: [%u, %u)", s, s + 1, seg->own_first, seg->own_last);
 	CK(cudaSetDevice(ctx->device));
 	uint32_t const m = seg->m;
 	dbuf off_l, ids_l, cls_l, n_l, off_r, ids_r, cls_r, n_r, dW;
 	int rc;
-	if ((rc = sets_on_device(ctx, seg->d_a + (size_t) s * m, seg->d_d + (size_t) s * m, m, seg->lb[s], off_l, ids_l, cls_l, n_l))) return rc;
-	if ((rc = sets_on_device(ctx, seg->d_a + (size_t) (s + 1) * m, seg->d_d + (size_t) (s + 1) * m, m, seg->lb[s + 1], off_r, ids_r, cls_r, n_r))) return rc;
+	size_t const at = (size_t) (s - seg->own_first) * m;
+	uint32_t const *sa = seg->red_a.as <uint32_t>() + at, *sd = seg->red_d.as <uint32_t>() + at;
+	if ((rc = sets_on_device(ctx, sa, sd, m, seg->lb[s], off_l, ids_l, cls_l, n_l))) return rc;
+	if ((rc = sets_on_device(ctx, sa + m, sd + m, m, seg->lb[s + 1], off_r, ids_r, cls_r, n_r))) return rc;
 	uint32_t rl = 0, rr = 0;
 	CK(cudaMemcpyAsync(&rl, n_l.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
 	CK(cudaMemcpyAsync(&rr, n_r.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -1707,257 +2128,68 @@ int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, int3
 }
 
 // ---- column-sharded operation -------------------------------------------------------------------------------------------
-// One process per GPU; rank r holds the columns [c0_r, c1_r) of one alignment.  The stages below are the long path of
-// fsq_segment() cut where ranks exchange data; the exchange itself (NCCL through torch.distributed, see
-// founder-sequences_b200/sharded.py) is the caller's.
+// One process (or thread) per GPU; rank r holds the columns fsq_shard_columns() names of one alignment and calls
+// fsq_segment_sharded() with its communicator.  The exchanges are all-gathers on the context's stream (fsq_comm.cu).
 
-int fsq_shard_create(fsq_ctx *ctx, const fsq_msa *msa, uint64_t n_total, uint64_t L, fsq_shard **out)
+int fsq_shard_columns(uint64_t n_total, int size, int rank, uint64_t *c0, uint64_t *c1)
 {
-	int rc = check_shape(ctx, msa);
-	if (rc) return rc;
-	if (!out) return fail(ctx, FSQ_ERR_ARG, "null out pointer");
-	if (0 == L) return fail(ctx, FSQ_ERR_ARG, "segment length bound must be positive");
-	if (msa->col0 + msa->n > n_total) return fail(ctx, FSQ_ERR_ARG, "the shard's columns end beyond the alignment");
-	if (n_total >= (1ull << 31)) return fail(ctx, FSQ_ERR_UNSUPPORTED, "n = %llu columns: positions are kept in 32 bits (n < 2^31)", (unsigned long long) n_total);
-	if (n_total < 2 * L) return fail(ctx, FSQ_ERR_SHORT, "n = %llu < 2L = %llu: short path", (unsigned long long) n_total, (unsigned long long) (2 * L));
+	if (!c0 || !c1 || size < 1 || rank < 0 || rank >= size) return FSQ_ERR_ARG;
+	uint64_t const per = columns_per_rank(n_total, size);
+	*c0 = std::min <uint64_t>(n_total, (uint64_t) rank * per);
+	*c1 = std::min <uint64_t>(n_total, *c0 + per);
+	return *c0 < *c1 ? FSQ_OK : FSQ_ERR_ARG;
+}
+
+int fsq_comm_unique_id(uint8_t id[FSQ_COMM_ID_BYTES])
+{
+	if (!id) return FSQ_ERR_ARG;
+	std::string err;
+	if (!nccl_unique_id(id, &err)) return fail(nullptr, FSQ_ERR_CUDA, "%s", err.c_str());
+	return FSQ_OK;
+}
+
+int fsq_comm_create(fsq_ctx *ctx, const uint8_t id[FSQ_COMM_ID_BYTES], int rank, int size, fsq_comm **out)
+{
+	if (!ctx || !id || !out || size < 1 || rank < 0 || rank >= size) return fail(ctx, FSQ_ERR_ARG, "bad argument");
 	CK(cudaSetDevice(ctx->device));
-	fsq_shard *P = new (std::nothrow) fsq_shard;
-	if (!P) return fail(ctx, FSQ_ERR_NOMEM, "out of host memory");
-	if ((rc = shard_init(P, ctx, msa, n_total, L))) { delete P; return rc; }
-	*out = P;
+	std::string err;
+	fsq_comm *c = nccl_comm_create(id, rank, size, &err);
+	if (!c) return fail(ctx, FSQ_ERR_CUDA, "%s", err.c_str());
+	*out = c;
 	return FSQ_OK;
 }
 
-void fsq_shard_free(fsq_shard *P)
+int fsq_comm_adopt_nccl(fsq_ctx *ctx, void *nccl_comm, int rank, int size, fsq_comm **out)
 {
-	if (!P) return;
-	cudaSetDevice(P->ctx->device);
-	cudaStreamSynchronize(P->ctx->stream);
-	delete P;
-}
-
-int fsq_shard_local_summary(fsq_shard *P, const uint32_t **d_pi, const uint32_t **d_delta)
-{
-	if (!P || !d_pi || !d_delta) return FSQ_ERR_ARG;
-	fsq_ctx *ctx = P->ctx;
-	CK(cudaSetDevice(ctx->device));
-	flush_phases(ctx);
-	if (!ctx->call_start) CK(cudaEventCreate(&ctx->call_start));
-	CK(cudaEventRecord(ctx->call_start, ctx->stream));
-	int const rc = local_scan(ctx, P->msa, P->S);
-	if (rc) return rc;
-	CK(cudaStreamSynchronize(ctx->stream));
-	// the state at the end of the last block, relative to the identity state at c0: this rank's summary
-	*d_pi = P->S.st_a.as <uint32_t>() + (size_t) P->S.g.B * P->m;
-	*d_delta = P->S.st_d.as <uint32_t>() + (size_t) P->S.g.B * P->m;
+	if (!ctx || !nccl_comm || !out || size < 1 || rank < 0 || rank >= size) return fail(ctx, FSQ_ERR_ARG, "bad argument");
+	std::string err;
+	fsq_comm *c = nccl_comm_adopt(nccl_comm, rank, size, &err);
+	if (!c) return fail(ctx, FSQ_ERR_CUDA, "%s", err.c_str());
+	*out = c;
 	return FSQ_OK;
 }
 
-int fsq_shard_set_start(fsq_shard *P, const uint32_t *d_pis, const uint32_t *d_deltas, const uint64_t *first_columns, uint32_t count)
+int fsq_local_group_create(int size, fsq_local_group **out)
 {
-	if (!P) return FSQ_ERR_ARG;
-	fsq_ctx *ctx = P->ctx;
-	CK(cudaSetDevice(ctx->device));
-	if (!P->S.sum_a.p) return fail(ctx, FSQ_ERR_ARG, "fsq_shard_local_summary has not run");
-	uint32_t const m = P->m;
-	if (0 == count)
-	{
-		if (0 != P->c0) return fail(ctx, FSQ_ERR_ARG, "a shard that does not start at column 0 needs the summaries of the ranks before it");
-	}
-	else
-	{
-		if (!d_pis || !d_deltas || !first_columns) return fail(ctx, FSQ_ERR_ARG, "null argument");
-		if (0 != first_columns[0]) return fail(ctx, FSQ_ERR_ARG, "the first summary must start at column 0");
-		// true state at c0 = summary_0 o summary_1 o ... (summary_0 starts from the true initial state); one CTA, in order
-		dbuf tmp_a, tmp_d;
-		CK(tmp_a.alloc(ctx, (size_t) 2 * m * 4)); CK(tmp_d.alloc(ctx, (size_t) 2 * m * 4));
-		uint32_t const *cur_a = d_pis, *cur_d = d_deltas;
-		if (count > 1)
-		{
-			stitch_plan plan;
-			for (uint32_t i = 1; i < count; ++i)
-			{
-				stitch_item it;
-				memset(&it, 0, sizeof it);
-				it.in_a = cur_a; it.in_d = cur_d;
-				it.pi = d_pis + (size_t) i * m; it.delta = d_deltas + (size_t) i * m;
-				it.out_a = tmp_a.as <uint32_t>() + (size_t) (i & 1) * m; it.out_d = tmp_d.as <uint32_t>() + (size_t) (i & 1) * m;
-				it.s_mark = (uint32_t) first_columns[i];
-				plan.items.push_back(it);
-				plan.end_level();              // one launch per step: each reads what the previous one wrote
-				cur_a = it.out_a; cur_d = it.out_d;
-			}
-			phase ps(ctx, "stitch");
-			CK(cudaStreamSynchronize(ctx->stream));
-			int const rc = run_stitch_plan(ctx, P->S, plan, m, {});
-			if (rc) return rc;
-			ps.stop();
-			CK(cudaStreamSynchronize(ctx->stream));
-		}
-		int const rc = apply_start_state(ctx, P->msa, P->S, cur_a, cur_d);
-		if (rc) return rc;
-		CK(cudaStreamSynchronize(ctx->stream));
-	}
-	int const rc = compress_starts(ctx, P->msa, P->S);
-	if (rc) return rc;
-	P->started = true;
+	if (!out || size < 1) return FSQ_ERR_ARG;
+	*out = local_group_create(size);
+	return *out ? FSQ_OK : FSQ_ERR_NOMEM;
+}
+
+void fsq_local_group_free(fsq_local_group *g) { local_group_free(g); }
+
+int fsq_comm_create_local(fsq_ctx *ctx, fsq_local_group *g, int rank, fsq_comm **out)
+{
+	if (!ctx || !g || !out) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	fsq_comm *c = local_comm_create(g, rank);
+	if (!c) return fail(ctx, FSQ_ERR_ARG, "rank %d is outside the group", rank);
+	*out = c;
 	return FSQ_OK;
 }
 
-int fsq_shard_scan(fsq_shard *P)
-{
-	if (!P) return FSQ_ERR_ARG;
-	fsq_ctx *ctx = P->ctx;
-	CK(cudaSetDevice(ctx->device));
-	if (!P->started) return fail(ctx, FSQ_ERR_ARG, "fsq_shard_set_start has not run");
-	int const rc = shard_scan(P);
-	if (rc) return rc;
-	CK(cudaStreamSynchronize(ctx->stream));
-	return FSQ_OK;
-}
+void fsq_comm_free(fsq_comm *c) { delete c; }
 
-int fsq_shard_dp_table(fsq_shard *P, uint32_t **d_max, uint32_t **d_lb, uint32_t **d_size, uint64_t *entries, uint64_t *own_first, uint64_t *own_last)
-{
-	if (!P || !d_max || !d_lb || !d_size || !entries || !own_first || !own_last) return FSQ_ERR_ARG;
-	if (!P->tb_max.p) return fail(P->ctx, FSQ_ERR_ARG, "fsq_shard_scan has not run");
-	*d_max = P->tb_max.as <uint32_t>(); *d_lb = P->tb_lb.as <uint32_t>(); *d_size = P->tb_size.as <uint32_t>();
-	*entries = P->dp_size;
-	*own_first = P->t_first;
-	*own_last = (P->c1 == P->n) ? P->dp_size : P->t_last;       // the rank with the last column also owns the final entry
-	return FSQ_OK;
-}
-
-int fsq_shard_dp_round(fsq_shard *P, uint32_t *changed, uint32_t *reach)
-{
-	if (!P || !changed || !reach) return FSQ_ERR_ARG;
-	CK_(P->ctx, cudaSetDevice(P->ctx->device));
-	return shard_dp_round(P, changed, reach);
-}
-
-int fsq_shard_dp_sync(fsq_shard *P, int guess, uint32_t reach)
-{
-	if (!P) return FSQ_ERR_ARG;
-	CK_(P->ctx, cudaSetDevice(P->ctx->device));
-	return shard_dp_sync(P, guess, reach);
-}
-
-int fsq_shard_dp_single_chain(fsq_shard *P)
-{
-	if (!P) return FSQ_ERR_ARG;
-	P->single_chain = true;
-	P->ctx->stats["dp_fallbacks"] += 1;
-	return FSQ_OK;
-}
-
-int fsq_shard_dp_final(fsq_shard *P, uint32_t *overflow)
-{
-	if (!P || !overflow) return FSQ_ERR_ARG;
-	CK_(P->ctx, cudaSetDevice(P->ctx->device));
-	return shard_dp_final(P, overflow);
-}
-
-int fsq_shard_grow_cap(fsq_shard *P)
-{
-	if (!P) return FSQ_ERR_ARG;
-	fsq_ctx *ctx = P->ctx;
-	if (P->cap >= P->m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list with cap = m");
-	P->cap = (uint32_t) std::min <uint64_t>(P->m, (uint64_t) P->cap * 4);
-	ctx->opts["cap"] = P->cap;
-	ctx->stats["cap_retries"] += 1;
-	return FSQ_OK;
-}
-
-int fsq_shard_traceback(fsq_shard *P, uint32_t *count, uint32_t *K)
-{
-	if (!P || !count || !K) return FSQ_ERR_ARG;
-	CK_(P->ctx, cudaSetDevice(P->ctx->device));
-	int const rc = shard_traceback(P);
-	if (rc) return rc;
-	*count = P->T;
-	*K = P->K;
-	return FSQ_OK;
-}
-
-int fsq_shard_get_traceback(const fsq_shard *P, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size)
-{
-	if (!P || !lb || !rb || !max_size || !size) return FSQ_ERR_ARG;
-	if (P->h_tb.p) copy_traceback(P->h_tb.p, P->T, lb, rb, max_size, size);
-	return FSQ_OK;
-}
-
-int fsq_shard_position_range(const fsq_shard *P, uint64_t c0, uint64_t c1, uint32_t *first, uint32_t *last)
-{
-	if (!P || !first || !last) return FSQ_ERR_ARG;
-	if (!P->h_tb.p) return fail(P->ctx, FSQ_ERR_ARG, "fsq_shard_traceback has not run");
-	uint64_t const *h_rb = P->h_tb.as <uint64_t>();
-	*first = (uint32_t) (std::upper_bound(h_rb, h_rb + P->T, c0) - h_rb);
-	*last = (uint32_t) (std::upper_bound(h_rb, h_rb + P->T, c1) - h_rb);
-	return FSQ_OK;
-}
-
-int fsq_shard_reduce_lists(fsq_shard *P, uint32_t **d_lists, uint32_t *width, uint32_t *own_first, uint32_t *own_last)
-{
-	if (!P || !d_lists || !width || !own_first || !own_last) return FSQ_ERR_ARG;
-	fsq_ctx *ctx = P->ctx;
-	CK(cudaSetDevice(ctx->device));
-	if (!(P->K < P->m)) return fail(ctx, FSQ_ERR_NOT_REDUCIBLE, "the maximum segment size %u is equal to the number of input sequences", P->K);
-	int const rc = shard_reduce_lists(P);
-	if (rc) return rc;
-	CK(cudaStreamSynchronize(ctx->stream));
-	*d_lists = P->lists.as <uint32_t>();
-	*width = P->K + 1;
-	*own_first = P->pos_first;
-	*own_last = P->pos_last;
-	return FSQ_OK;
-}
-
-int fsq_shard_reduce(fsq_shard *P, uint32_t *count, uint32_t *own_first, uint32_t *own_last)
-{
-	if (!P || !count || !own_first || !own_last) return FSQ_ERR_ARG;
-	fsq_ctx *ctx = P->ctx;
-	CK(cudaSetDevice(ctx->device));
-	int rc = shard_reduce(P, false);
-	if (rc) return rc;
-	if ((rc = shard_reduced_states(P))) return rc;
-	CK(cudaStreamSynchronize(ctx->stream));
-	*count = P->n_reduced;
-	*own_first = P->seg_first;
-	*own_last = P->seg_last;
-	ctx->stats["cap"] = P->cap;
-	ctx->stats["block_columns"] = P->S.g.C;
-	ctx->stats["blocks"] = P->S.g.B;
-	ctx->stats["warps"] = (P->S.g.blocked || P->S.g.chunked) ? P->S.g.T / 32 : P->S.g.n_warps;
-	ctx->stats["chunk"] = (P->S.g.blocked || P->S.g.chunked) ? P->S.g.E : 0;
-	ctx->stats["kernel"] = P->S.g.chunked ? 3 : (P->S.g.blocked ? 2 : 1);
-	return FSQ_OK;
-}
-
-int fsq_shard_bounds(const fsq_shard *cP, uint64_t *lb, uint64_t *rb, uint32_t *size)
-{
-	fsq_shard *P = const_cast <fsq_shard *>(cP);
-	if (!P || !lb || !rb || !size) return FSQ_ERR_ARG;
-	CK_(P->ctx, cudaSetDevice(P->ctx->device));
-	{
-		int const rc = finish_reduced(P);
-		if (rc) return rc;
-	}
-	std::copy(P->red_lb.begin(), P->red_lb.end(), lb);
-	std::copy(P->red_rb.begin(), P->red_rb.end(), rb);
-	std::copy(P->red_size.begin(), P->red_size.end(), size);
-	return FSQ_OK;
-}
-
-int fsq_shard_states(fsq_shard *P, uint32_t *a, uint32_t *d)
-{
-	if (!P || !a || !d) return FSQ_ERR_ARG;
-	fsq_ctx *ctx = P->ctx;
-	CK(cudaSetDevice(ctx->device));
-	size_t const bytes = (size_t) (P->seg_last - P->seg_first) * P->m * 4;
-	if (0 == bytes) return FSQ_OK;
-	CK(cudaMemcpyAsync(a, P->red_a.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaMemcpyAsync(d, P->red_d.p, bytes, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
-	return FSQ_OK;
-}
+int fsq_comm_rank(const fsq_comm *c) { return c ? c->rank : 0; }
+int fsq_comm_size(const fsq_comm *c) { return c ? c->size : 1; }
 
 } // extern "C"

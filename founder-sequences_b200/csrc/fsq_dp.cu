@@ -115,7 +115,7 @@ __device__ __forceinline__ list_head load_list_head(dp_args const &A, uint64_t k
 {
 	uint32_t const lane = lane_id();
 	uint64_t const kl = k - A.col_base;
-	uint2 const *list = A.toplist + kl * (A.cap + 1);
+	uint2 const *list = A.toplist + (k - A.list_base) * (A.cap + 1);
 	list_head h;
 	h.cw = A.cnt[kl];
 	h.h0 = A.h0[kl];
@@ -140,10 +140,9 @@ __device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list
 {
 	uint32_t const lane = lane_id();
 	uint32_t const L = (uint32_t) A.L;
-	uint64_t const kl = k - A.col_base;
 	uint32_t const E = h.cw & 0x7fffffffu;
 	bool const complete = h.cw >> 31;
-	uint2 const *list = A.toplist + kl * (A.cap + 1);
+	uint2 const *list = A.toplist + (k - A.list_base) * (A.cap + 1);
 	uint32_t const hi_clip = (uint32_t) (k + 2 - L);
 
 	// candidates compare as (value, range index) packed into 32 bits -- both are < 2^16 (m <= 65000) -- so that the
@@ -200,8 +199,11 @@ __device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list
 	uint32_t const best_val = best >> 16;
 	uint32_t lb = 0, mx = whole, sz = whole;
 	if (0xffffffffu != best && best_val < whole) { lb = best_idx + L; mx = best_val; sz = best_S; }
+	// Under a list that is too short every value found is an upper bound of the true one (the candidates left out are
+	// worth more than cap), and so is everything computed from it: lists that reach as far as the largest such value
+	// prove the whole table.
 	if (0 == lane && !complete && mx > A.cap)
-		atomicMax(&A.flags[1], (uint32_t) (k + 1));
+		atomicMax(&A.flags[F_OVERFLOW], mx);
 	lb_out = lb; size_out = sz;
 	return mx;
 }
@@ -229,6 +231,7 @@ __global__ void __launch_bounds__(512, FSQ_DP_MIN_CTAS) dp_chain_kernel(dp_args 
 	__shared__ uint32_t sM[DP_RING];
 	__shared__ unsigned long long smk[DP_RING];
 	__shared__ uint32_t slev[DP_SLEV * DP_RING_BLK];
+	if (A.skip_when_done && A.flags[F_DONE]) return;
 	uint32_t const warp = threadIdx.x >> 5;
 	uint32_t const W = blockDim.x >> 5;           // columns per wavefront, <= min(L, 32)
 	uint32_t const lane = lane_id();
@@ -243,7 +246,7 @@ __global__ void __launch_bounds__(512, FSQ_DP_MIN_CTAS) dp_chain_kernel(dp_args 
 	// computed every entry from values that are final: flags[3] counts the chains for which this cannot be said.
 	// (bound_on_device: the bound is the copy of flags[2] the guess made before this round, flags[4], so that two rounds
 	// can be queued without the host in between; the live flags[2] moves while the round runs and cannot serve)
-	uint32_t const reach_bound = A.bound_on_device ? A.flags[4] : A.reach_bound;
+	uint32_t const reach_bound = A.bound_on_device ? A.flags[F_BOUND] : A.reach_bound;
 	uint32_t const tail_from = t_end > reach_bound ? t_end - reach_bound : 0u;
 	uint32_t lowest = 0xffffffffu;
 	bool unsettled = false, changed = false;      // published once per warp at the end (a store per entry would pile up on one address)
@@ -345,11 +348,11 @@ __global__ void __launch_bounds__(512, FSQ_DP_MIN_CTAS) dp_chain_kernel(dp_args 
 		}
 	}
 	if (0 == warp && pend_old != pend_new) { changed = true; unsettled = true; }
-	if (__any_sync(FSQ_FULL, changed) && 0 == lane) A.flags[0] = 1;
-	if (0 == lane && reach) atomicMax(&A.flags[2], reach);
+	if (__any_sync(FSQ_FULL, changed) && 0 == lane) A.flags[F_CHANGED] = 1;
+	if (0 == lane && reach) atomicMax(&A.flags[F_REACH], reach);
 	// reads below the own entries must stay inside the window the chains before this one watch
 	if (0xffffffffu != lowest && lowest < t_begin && t_begin - lowest > reach_bound) unsettled = true;
-	if (__any_sync(FSQ_FULL, unsettled) && 0 == lane) atomicAdd(&A.flags[3], 1u);
+	if (__any_sync(FSQ_FULL, unsettled) && 0 == lane) atomicAdd(&A.flags[F_UNSETTLED], 1u);
 }
 
 cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st)
@@ -395,9 +398,10 @@ cudaError_t launch_dp_final(dp_args const &A, cudaStream_t st)
 __global__ void __launch_bounds__(128) dp_chunk_level_kernel(dp_args const A)
 {
 	__shared__ uint32_t wmin[4];
+	if (A.skip_when_done && A.flags[F_DONE]) return;
 	uint32_t const c = blockIdx.x;
 	uint32_t const end = min(A.n_entries, (c + 1) * A.chunk);
-	uint32_t const D = 2 * A.flags[2] + 64;          // twice the farthest look-back seen so far
+	uint32_t const D = 2 * A.flags[F_REACH] + 64;          // twice the farthest look-back seen so far
 	uint32_t const begin = end > D ? end - D : 0;
 	uint32_t v = 0xffffffffu;
 	for (uint32_t t = begin + threadIdx.x; t < end; t += blockDim.x) v = min(v, A.tb_max[t]);
@@ -413,7 +417,8 @@ __global__ void __launch_bounds__(1024) dp_level_kernel(dp_args const A)
 	__shared__ uint32_t carry;
 	__shared__ uint32_t wmax[32];
 	uint32_t const lane = lane_id(), warp = threadIdx.x >> 5;
-	if (0 == threadIdx.x) { carry = 0; A.flags[4] = A.flags[2]; }      // the look-back bound of the next round (no chain is running now)
+	if (A.skip_when_done && A.flags[F_DONE]) return;
+	if (0 == threadIdx.x) { carry = 0; A.flags[F_BOUND] = A.flags[F_REACH]; }      // the look-back bound of the next round (no chain is running now)
 	__syncthreads();
 	for (uint32_t c0 = 0; c0 < A.n_chunks; c0 += blockDim.x)
 	{
@@ -438,8 +443,9 @@ __global__ void __launch_bounds__(1024) dp_level_kernel(dp_args const A)
 
 __global__ void dp_raise_kernel(dp_args const A)
 {
-	uint32_t const t = blockIdx.x * blockDim.x + threadIdx.x;
-	if (t >= A.n_entries) return;
+	uint32_t const t = A.lvl_first + blockIdx.x * blockDim.x + threadIdx.x;
+	if (t >= A.lvl_last) return;
+	if (A.skip_when_done && A.flags[F_DONE]) return;
 	uint32_t const lvl = A.chunk_level[t / A.chunk];
 	if (A.tb_max[t] < lvl) A.tb_max[t] = lvl;
 }
@@ -451,6 +457,7 @@ __global__ void dp_masks_kernel(dp_args const A)
 {
 	uint32_t const t = A.w_first + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
 	if (t >= A.w_last) return;
+	if (A.skip_when_done && A.flags[F_DONE]) return;
 	table_global v;
 	v.Mg = A.tb_max; v.mkg = A.mk; v.levg = A.lev; v.n_blk = A.n_blk;
 	unsigned long long const msk = make_mask(v, t);
@@ -475,7 +482,7 @@ cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st)
 	// (launch_dp_rebuild is declared in fsq_internal.h)
 	dp_chunk_level_kernel <<<A.n_chunks, 128, 0, st>>>(A);
 	dp_level_kernel <<<1, 1024, 0, st>>>(A);
-	dp_raise_kernel <<<(A.n_entries + 255) / 256, 256, 0, st>>>(A);
+	if (A.lvl_last > A.lvl_first) dp_raise_kernel <<<(A.lvl_last - A.lvl_first + 255) / 256, 256, 0, st>>>(A);
 	return launch_dp_rebuild(A, st);
 }
 
@@ -488,6 +495,7 @@ __global__ void dp_levels_all_kernel(dp_args const A)
 {
 	uint32_t const i = A.w_first / 64 + blockIdx.x * blockDim.x + threadIdx.x;
 	uint32_t const n_complete = A.w_last / 64;
+	if (A.skip_when_done && A.flags[F_DONE]) return;
 	uint32_t prev = 0;
 	for (uint32_t p = 0; p < A.n_levels; ++p)
 	{
@@ -513,6 +521,71 @@ cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st)
 }
 
 
+// ---- end of a DP round: the decision stays on the device ----------------------------------------------------------------
+__global__ void dp_round_end_kernel(uint32_t *flags, uint32_t first_round, uint32_t *send)
+{
+	// another round is needed: in the first round when anything changed at all; later, when a value changed that a chain after
+	// its owner may have read while it was still the old one (dp_chain_kernel)
+	bool const cont = !flags[F_DONE] && flags[F_CHANGED] && (first_round || flags[F_UNSETTLED]);
+	send[0] = cont ? 1u : 0u;
+	send[1] = flags[F_OVERFLOW];
+	send[2] = flags[F_REACH];
+	send[3] = 0;
+}
+
+__global__ void dp_round_merge_kernel(uint32_t *flags, uint32_t const *gathered, uint32_t size, uint32_t round_no, uint32_t back_bound, uint32_t one_chain)
+{
+	if (flags[F_DONE]) return;
+	uint32_t cont = 0, ovf = 0, reach = 0;
+	for (uint32_t r = 0; r < size; ++r)
+	{
+		cont |= gathered[4 * r];
+		ovf = max(ovf, gathered[4 * r + 1]);
+		reach = max(reach, gathered[4 * r + 2]);
+	}
+	flags[F_REACH] = reach;
+	flags[F_ROUNDS] = round_no;
+	if (2 * (uint64_t) reach + 128 > back_bound) flags[F_WINDOW_ERR] = 1;
+	// (one chain over everything is the reference's own order: exact as it stands)
+	if ((round_no > 1 && !cont) || one_chain)
+	{
+		flags[F_DONE] = 1;
+		flags[F_OVERFLOW] = ovf;         // of the round that found the fixed point: its values are final
+		return;
+	}
+	// a table that is still moving says nothing about the lists: values computed from guesses may exceed the final ones
+	flags[F_OVERFLOW] = 0;
+	flags[F_CHANGED] = 0;
+	flags[F_UNSETTLED] = 0;
+}
+
+// after the last entry: whether any rank's lists were too short
+__global__ void dp_overflow_merge_kernel(uint32_t *flags, uint32_t const *gathered, uint32_t size)
+{
+	uint32_t ovf = flags[F_OVERFLOW];
+	for (uint32_t r = 0; r < size; ++r) ovf = max(ovf, gathered[4 * r + 1]);
+	flags[F_OVERFLOW] = ovf;
+}
+
+cudaError_t launch_dp_overflow_merge(uint32_t *flags, uint32_t const *gathered, uint32_t size, cudaStream_t st)
+{
+	dp_overflow_merge_kernel <<<1, 1, 0, st>>>(flags, gathered, size);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_dp_round_end(uint32_t *flags, uint32_t first_round, uint32_t *send, cudaStream_t st)
+{
+	dp_round_end_kernel <<<1, 1, 0, st>>>(flags, first_round, send);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_dp_round_merge(uint32_t *flags, uint32_t const *gathered, uint32_t size, uint32_t round_no, uint32_t back_bound, uint32_t one_chain, cudaStream_t st)
+{
+	dp_round_merge_kernel <<<1, 1, 0, st>>>(flags, gathered, size, round_no, back_bound, one_chain);
+	return cudaGetLastError();
+}
+
+
 // ---- traceback (reference: segmentation_lp_context.cc:191-224) --------------------------------------------------------------
 constexpr uint32_t TRACE_END = 0xffffffffu;
 
@@ -533,7 +606,7 @@ __global__ void trace_double_kernel(trace_args const A, uint32_t k)
 	A.jump[(size_t) k * A.dp_size + t] = (TRACE_END == j) ? TRACE_END : prev[j];
 }
 
-__global__ void trace_count_kernel(trace_args const A)
+__device__ __forceinline__ void trace_count(trace_args const &A)
 {
 	uint32_t cur = A.dp_size - 1, hops = 0;
 	for (int k = (int) A.levels - 1; k >= 0; --k)
@@ -541,13 +614,17 @@ __global__ void trace_count_kernel(trace_args const A)
 		uint32_t const j = A.jump[(size_t) k * A.dp_size + cur];
 		if (TRACE_END != j) { cur = j; hops += 1u << k; }
 	}
-	*A.count = hops + 1;
+	A.ctl[I_T] = hops + 1;
+	A.ctl[I_K] = A.tb_max[A.dp_size - 1];
 }
 
-__global__ void trace_gather_kernel(trace_args const A, uint32_t count)
+__global__ void trace_count_kernel(trace_args const A) { trace_count(A); }
+
+__global__ void trace_gather_kernel(trace_args const A)
 {
+	uint32_t const count = A.ctl[I_T];
 	uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;      // hops back from the last entry
-	if (s >= count) return;
+	if (s >= count || s >= A.t_bound) return;
 	uint32_t cur = A.dp_size - 1;
 	for (uint32_t k = 0; k < A.levels; ++k)
 		if ((s >> k) & 1u) cur = A.jump[(size_t) k * A.dp_size + cur];
@@ -556,6 +633,20 @@ __global__ void trace_gather_kernel(trace_args const A, uint32_t count)
 	A.out_rb[o] = (uint64_t) cur + A.L;
 	A.out_max[o] = A.tb_max[cur];
 	A.out_size[o] = A.tb_size[cur];
+}
+
+// the traceback positions whose right bound lies in (c0, c1]: this rank holds the state there
+__global__ void trace_own_kernel(trace_args const A)
+{
+	if (threadIdx.x >= 2) return;
+	uint64_t const c = threadIdx.x ? A.c1 : A.c0;
+	uint32_t lo = 0, hi = min(A.ctl[I_T], A.t_bound);
+	while (lo < hi)
+	{
+		uint32_t const mid = (lo + hi) >> 1;
+		if (A.out_rb[mid] <= c) lo = mid + 1; else hi = mid;
+	}
+	A.ctl[I_POS_FIRST + threadIdx.x] = lo;
 }
 
 // Level-by-level phases (pointer doubling, rmq levels) are a dozen or two launches of kernels that each run for a few
@@ -605,16 +696,7 @@ __global__ void __launch_bounds__(256) trace_tables_coop_kernel(trace_args const
 		}
 	}
 	grid.sync();
-	if (0 == first)
-	{
-		uint32_t cur = A.dp_size - 1, hops = 0;
-		for (int k = (int) A.levels - 1; k >= 0; --k)
-		{
-			uint32_t const j = A.jump[(size_t) k * A.dp_size + cur];
-			if (TRACE_END != j) { cur = j; hops += 1u << k; }
-		}
-		*A.count = hops + 1;
-	}
+	if (0 == first) trace_count(A);
 }
 
 cudaError_t launch_trace_tables(trace_args const &A, cudaStream_t st)
@@ -629,9 +711,10 @@ cudaError_t launch_trace_tables(trace_args const &A, cudaStream_t st)
 	return cudaGetLastError();
 }
 
-cudaError_t launch_trace_gather(trace_args const &A, uint32_t count, cudaStream_t st)
+cudaError_t launch_trace_gather(trace_args const &A, cudaStream_t st)
 {
-	trace_gather_kernel <<<(count + 255) / 256, 256, 0, st>>>(A, count);
+	trace_gather_kernel <<<(A.t_bound + 255) / 256, 256, 0, st>>>(A);
+	trace_own_kernel <<<1, 32, 0, st>>>(A);
 	return cudaGetLastError();
 }
 
@@ -640,185 +723,263 @@ cudaError_t launch_trace_gather(trace_args const &A, uint32_t count, cudaStream_
 // The reference merges traceback segments while #{d_rb > cur_lb} <= K.  That count is the number of distinct rows over
 // [cur_lb, rb), which cannot decrease as rb grows, so the run merged from a given start is a function of the start
 // alone: one warp per start u (u = 0: left bound 0; u >= 1: left bound rb[u - 1]) extends while the count stays <= K;
-// the host then follows next[] from u = 0.
+// the walk below then follows next[] from u = 0.
 // The count itself comes from the top list of column rb - 1: with v* the largest divergence value <= lb,
 // #{d > lb} = #{d > v*} (no value lies in (v*, lb]), which is the S of the first list entry whose v is <= lb.  Only
 // entries with S <= K matter -- no such entry means the count exceeds K (K < m here) -- so each traceback position
-// keeps K + 1 entries, which is also what column-sharded ranks exchange instead of whole states.
+// keeps a row of the entries with S <= K.  Where the top lists are gone by then (the scan ran in windows over a reused
+// list buffer) the rows are the divergence arrays at the traceback positions instead and the count is taken directly.
+// A column-sharded rank does this for its own positions; a run that leaves them continues over the first rows of the
+// ranks after it (the halo), which is all the ranks exchange.
 __global__ void reduce_lists_kernel(reduce_args const A)
 {
-	uint32_t const pos = A.pos_first + blockIdx.x;
-	uint64_t const kl = A.tb_rb[pos] - 1 - A.col_base;
+	uint32_t const first = A.ctl[I_POS_FIRST], last = A.ctl[I_POS_LAST], K = A.ctl[I_K];
+	uint32_t const i = blockIdx.x;
+	if (first + i >= last) return;
+	uint64_t const kl = A.tb_rb[first + i] - 1 - A.col_base;
 	uint32_t const E = A.cnt[kl] & 0x7fffffffu;
 	uint2 const *list = A.toplist + kl * (A.cap + 1);
-	uint2 *out = A.lists + (size_t) pos * A.width;
-	for (uint32_t i = threadIdx.x; i < A.width; i += blockDim.x)
+	uint2 *out = (uint2 *) A.own_rows + (size_t) i * A.width;
+	for (uint32_t j = threadIdx.x; j < A.width; j += blockDim.x)
 	{
 		uint2 e = make_uint2(0xffffffffu, 0xffffffffu);
-		if (i < E) { uint2 const x = list[i]; if (x.y <= A.K) e = x; }
-		out[i] = e;
+		if (j < E) { uint2 const x = list[j]; if (x.y <= K) e = x; }
+		out[j] = e;
 	}
 }
 
 cudaError_t launch_reduce_lists(reduce_args const &A, cudaStream_t st)
 {
-	if (A.pos_first >= A.pos_last) return cudaSuccess;
-	reduce_lists_kernel <<<A.pos_last - A.pos_first, 64, 0, st>>>(A);
+	if (0 == A.rows_bound) return cudaSuccess;
+	reduce_lists_kernel <<<A.rows_bound, 64, 0, st>>>(A);
 	return cudaGetLastError();
+}
+
+__global__ void rank_positions_kernel(uint64_t const *tb_rb, uint32_t const *ctl, uint64_t n_per, uint32_t size, uint32_t *pos_first_all)
+{
+	uint32_t const q = blockIdx.x * blockDim.x + threadIdx.x;
+	if (q > size) return;
+	uint32_t const T = ctl[I_T];
+	uint64_t const c = (uint64_t) q * n_per;
+	uint32_t lo = 0, hi = T;
+	if (q == size) lo = T;
+	while (lo < hi)
+	{
+		uint32_t const mid = (lo + hi) >> 1;
+		if (tb_rb[mid] <= c) lo = mid + 1; else hi = mid;
+	}
+	pos_first_all[q] = lo;
+}
+
+cudaError_t launch_rank_positions(uint64_t const *tb_rb, uint32_t const *ctl, uint64_t n_per, uint32_t size, uint32_t *pos_first_all, cudaStream_t st)
+{
+	rank_positions_kernel <<<(size + 1 + 63) / 64, 64, 0, st>>>(tb_rb, ctl, n_per, size, pos_first_all);
+	return cudaGetLastError();
+}
+
+// #{d > lb} for the row of traceback position t, one warp; ~0 when the row is out of reach (halo exhausted)
+__device__ __forceinline__ uint32_t reduce_count(reduce_args const &A, uint32_t t, uint32_t first, uint32_t last, uint32_t cur_lb, uint32_t K, bool &missing)
+{
+	uint32_t const lane = lane_id();
+	size_t const row_words = A.row_kind ? (size_t) A.m : 2 * (size_t) A.width;
+	uint32_t const *row = nullptr;
+	if (t < last) row = (uint32_t const *) A.own_rows + (size_t) (t - first) * row_words;
+	else if (A.halo_rows)
+	{
+		// the rank after this one that holds position t, and its local index there
+		uint32_t q = A.rank + 1;
+		while (q < A.size && A.pos_first_all[q + 1] <= t) ++q;
+		uint32_t const i = t - A.pos_first_all[q];
+		if (q < A.size && i < A.halo) row = (uint32_t const *) A.halo_rows + ((size_t) q * A.halo + i) * row_words;
+	}
+	if (!row) { missing = true; return 0xffffffffu; }
+	if (A.row_kind)
+	{
+		uint32_t c = 0;
+		for (uint32_t i = lane; i < A.m; i += 32) c += row[i] > cur_lb;
+		return __reduce_add_sync(FSQ_FULL, c);
+	}
+	uint2 const *list = (uint2 const *) row;
+	for (uint32_t i0 = 0; i0 < A.width; i0 += 32)
+	{
+		uint32_t const i = i0 + lane;
+		uint2 const e = i < A.width ? list[i] : make_uint2(0xffffffffu, 0xffffffffu);
+		uint32_t const hit = __ballot_sync(FSQ_FULL, e.x <= cur_lb);       // the padding (v = ~0) never matches
+		if (hit) return __shfl_sync(FSQ_FULL, e.y, __ffs(hit) - 1);
+		if (__any_sync(FSQ_FULL, e.y > K)) break;                          // S ascends: nothing further counts
+	}
+	return 0xffffffffu;
 }
 
 __global__ void reduce_kernel(reduce_args const A)
 {
 	uint32_t const lane = lane_id();
-	uint32_t const u = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-	if (u >= A.T) return;
+	uint32_t const first = A.ctl[I_POS_FIRST], last = A.ctl[I_POS_LAST], T = A.ctl[I_T], K = A.ctl[I_K];
+	uint32_t const i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	uint32_t const u = first + i;
+	if (u >= last) return;
 	uint32_t const cur_lb = (0 == u) ? 0u : (uint32_t) A.tb_rb[u - 1];
 	uint32_t prev = u, size = A.tb_size[u];
-	for (uint32_t t = u + 1; t < A.T; ++t)
+	bool missing = false;
+	for (uint32_t t = u + 1; t < T; ++t)
 	{
-		uint2 const *list = A.lists + (size_t) t * A.width;
-		uint32_t s = 0xffffffffu;
-		for (uint32_t i0 = 0; i0 < A.width; i0 += 32)
-		{
-			uint32_t const i = i0 + lane;
-			uint2 const e = i < A.width ? list[i] : make_uint2(0xffffffffu, 0xffffffffu);
-			uint32_t const hit = __ballot_sync(FSQ_FULL, e.x <= cur_lb);       // the padding (v = ~0) never matches
-			if (hit)
-			{
-				s = __shfl_sync(FSQ_FULL, e.y, __ffs(hit) - 1);
-				break;
-			}
-		}
-		if (s <= A.K) { size = s; prev = t; }
+		uint32_t const s = reduce_count(A, t, first, last, cur_lb, K, missing);
+		if (missing) break;
+		if (s <= K) { size = s; prev = t; }
 		else break;
 	}
-	if (0 == lane) { A.next[u] = prev; A.next_size[u] = size; }
+	if (0 == lane)
+	{
+		A.next[i] = prev; A.next_size[i] = size;
+		if (missing) A.ctl[I_HALO_ERR] = 1;
+	}
+}
+
+// the "ran out of rows" flag rides behind the runs (word rows_bound) so that every rank learns of it
+__global__ void reduce_flag_kernel(reduce_args const A)
+{
+	A.next_size[A.rows_bound] = A.ctl[I_HALO_ERR];
+	A.next[A.rows_bound] = 0;
 }
 
 cudaError_t launch_reduce(reduce_args const &A, cudaStream_t st)
 {
+	if (0 == A.rows_bound) return cudaSuccess;
 	uint32_t const wpb = 8;
-	reduce_kernel <<<(A.T + wpb - 1) / wpb, wpb * 32, 0, st>>>(A);
+	reduce_kernel <<<(A.rows_bound + wpb - 1) / wpb, wpb * 32, 0, st>>>(A);
+	reduce_flag_kernel <<<1, 1, 0, st>>>(A);
+	return cudaGetLastError();
+}
+
+// (blocks of rows_bound + 1 words per rank: the last word of next_size is the rank's "ran out of rows" flag)
+__global__ void scatter_next_kernel(uint32_t const *next_all, uint32_t const *nsize_all, uint32_t const *pos_first_all, uint32_t size, uint32_t rows_bound, uint32_t t_bound, uint32_t *next, uint32_t *next_size, uint32_t *ctl)
+{
+	uint32_t const q = blockIdx.y;
+	uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+	size_t const stride = (size_t) rows_bound + 1;
+	if (0 == i && nsize_all[q * stride + rows_bound]) ctl[I_HALO_ERR] = 1;
+	uint32_t const first = pos_first_all[q], last = pos_first_all[q + 1];
+	if (i >= rows_bound || first + i >= last || first + i >= t_bound) return;
+	next[first + i] = next_all[q * stride + i];
+	next_size[first + i] = nsize_all[q * stride + i];
+}
+
+cudaError_t launch_scatter_next(uint32_t const *next_all, uint32_t const *nsize_all, uint32_t const *pos_first_all, uint32_t size, uint32_t rows_bound, uint32_t t_bound, uint32_t *next, uint32_t *next_size, uint32_t *ctl, cudaStream_t st)
+{
+	if (0 == rows_bound) return cudaSuccess;
+	scatter_next_kernel <<<dim3((rows_bound + 255) / 256, size), 256, 0, st>>>(next_all, nsize_all, pos_first_all, size, rows_bound, t_bound, next, next_size, ctl);
 	return cudaGetLastError();
 }
 
 
 // ---- the reduced segments from next[] -----------------------------------------------------------------------------------
-__global__ void walk_init_kernel(walk_args const A)
-{
-	uint32_t const u = blockIdx.x * blockDim.x + threadIdx.x;
-	if (u >= A.T) return;
-	uint32_t const v = A.next[u] + 1;
-	A.jump[u] = v < A.T ? v : TRACE_END;
-}
-
-__global__ void walk_double_kernel(walk_args const A, uint32_t k)
-{
-	uint32_t const u = blockIdx.x * blockDim.x + threadIdx.x;
-	if (u >= A.T) return;
-	uint32_t const *prev = A.jump + (size_t) (k - 1) * A.T;
-	uint32_t const j = prev[u];
-	A.jump[(size_t) k * A.T + u] = (TRACE_END == j) ? TRACE_END : prev[j];
-}
-
-__global__ void walk_count_kernel(walk_args const A)
+__device__ __forceinline__ void walk_count(walk_args const &A, uint32_t T)
 {
 	uint32_t cur = 0, hops = 0;
 	for (int k = (int) A.levels - 1; k >= 0; --k)
 	{
-		uint32_t const j = A.jump[(size_t) k * A.T + cur];
+		uint32_t const j = A.jump[(size_t) k * A.t_bound + cur];
 		if (TRACE_END != j) { cur = j; hops += 1u << k; }
 	}
-	A.info[0] = hops + 1;
+	A.ctl[I_NRED] = T ? hops + 1 : 0;
 }
 
-__global__ void walk_gather_kernel(walk_args const A)
+__device__ __forceinline__ void walk_own(walk_args const &A, uint32_t which)
 {
-	uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;      // segments in text order = hops from u = 0
-	if (s >= A.info[0]) return;
-	uint32_t cur = 0;
-	for (uint32_t k = 0; k < A.levels; ++k)
-		if ((s >> k) & 1u) cur = A.jump[(size_t) k * A.T + cur];
-	A.out_lb[s] = cur ? A.tb_rb[cur - 1] : 0ull;
-	A.out_rb[s] = A.tb_rb[A.next[cur]];
-	A.out_size[s] = A.next_size[cur];
-}
-
-// upper bounds of c0 and c1 among the right bounds: the segments whose end state this rank holds
-__global__ void walk_own_kernel(walk_args const A)
-{
-	if (threadIdx.x >= 2) return;
-	uint64_t const c = threadIdx.x ? A.c1 : A.c0;
-	uint32_t lo = 0, hi = A.info[0];
+	uint64_t const c = which ? A.c1 : A.c0;
+	uint32_t lo = 0, hi = A.ctl[I_NRED];
 	while (lo < hi)
 	{
 		uint32_t const mid = (lo + hi) >> 1;
 		if (A.out_rb[mid] <= c) lo = mid + 1; else hi = mid;
 	}
-	A.info[1 + threadIdx.x] = lo;
+	A.ctl[I_SEG_FIRST + which] = lo;
+}
+
+__global__ void walk_init_kernel(walk_args const A)
+{
+	uint32_t const T = min(A.ctl[I_T], A.t_bound);
+	uint32_t const u = blockIdx.x * blockDim.x + threadIdx.x;
+	if (u >= T) return;
+	uint32_t const v = A.next[u] + 1;
+	A.jump[u] = v < T ? v : TRACE_END;
+}
+
+__global__ void walk_double_kernel(walk_args const A, uint32_t k)
+{
+	uint32_t const T = min(A.ctl[I_T], A.t_bound);
+	uint32_t const u = blockIdx.x * blockDim.x + threadIdx.x;
+	if (u >= T) return;
+	uint32_t const *prev = A.jump + (size_t) (k - 1) * A.t_bound;
+	uint32_t const j = prev[u];
+	A.jump[(size_t) k * A.t_bound + u] = (TRACE_END == j) ? TRACE_END : prev[j];
+}
+
+__global__ void walk_count_kernel(walk_args const A) { walk_count(A, min(A.ctl[I_T], A.t_bound)); }
+
+__global__ void walk_gather_kernel(walk_args const A)
+{
+	uint32_t const s = blockIdx.x * blockDim.x + threadIdx.x;      // segments in text order = hops from u = 0
+	if (s >= A.ctl[I_NRED]) return;
+	uint32_t cur = 0;
+	for (uint32_t k = 0; k < A.levels; ++k)
+		if ((s >> k) & 1u) cur = A.jump[(size_t) k * A.t_bound + cur];
+	A.out_lb[s] = cur ? A.tb_rb[cur - 1] : 0ull;
+	A.out_rb[s] = A.tb_rb[A.next[cur]];
+	A.out_size[s] = A.next_size[cur];
+	A.out_pos[s] = A.next[cur];
+}
+
+// upper bounds of c0 and c1 among the right bounds: the segments whose end state this rank holds
+__global__ void walk_own_kernel(walk_args const A)
+{
+	if (threadIdx.x < 2) walk_own(A, threadIdx.x);
 }
 
 __global__ void __launch_bounds__(256) walk_coop_kernel(walk_args const A)
 {
 	cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+	uint32_t const T = min(A.ctl[I_T], A.t_bound);
 	uint32_t const stride = gridDim.x * blockDim.x, first = blockIdx.x * blockDim.x + threadIdx.x;
-	for (uint32_t u = first; u < A.T; u += stride)
+	for (uint32_t u = first; u < T; u += stride)
 	{
 		uint32_t const v = A.next[u] + 1;
-		A.jump[u] = v < A.T ? v : TRACE_END;
+		A.jump[u] = v < T ? v : TRACE_END;
 	}
 	for (uint32_t k = 1; k < A.levels; ++k)
 	{
 		grid.sync();
-		uint32_t const *prev = A.jump + (size_t) (k - 1) * A.T;
-		uint32_t *cur = A.jump + (size_t) k * A.T;
-		for (uint32_t u = first; u < A.T; u += stride)
+		uint32_t const *prev = A.jump + (size_t) (k - 1) * A.t_bound;
+		uint32_t *cur = A.jump + (size_t) k * A.t_bound;
+		for (uint32_t u = first; u < T; u += stride)
 		{
 			uint32_t const j = prev[u];
 			cur[u] = (TRACE_END == j) ? TRACE_END : prev[j];
 		}
 	}
 	grid.sync();
-	if (0 == first)
-	{
-		uint32_t cur = 0, hops = 0;
-		for (int k = (int) A.levels - 1; k >= 0; --k)
-		{
-			uint32_t const j = A.jump[(size_t) k * A.T + cur];
-			if (TRACE_END != j) { cur = j; hops += 1u << k; }
-		}
-		A.info[0] = hops + 1;
-	}
+	if (0 == first) walk_count(A, T);
 	grid.sync();
-	uint32_t const count = A.info[0];
+	uint32_t const count = A.ctl[I_NRED];
 	for (uint32_t s = first; s < count; s += stride)
 	{
 		uint32_t cur = 0;
 		for (uint32_t k = 0; k < A.levels; ++k)
-			if ((s >> k) & 1u) cur = A.jump[(size_t) k * A.T + cur];
+			if ((s >> k) & 1u) cur = A.jump[(size_t) k * A.t_bound + cur];
 		A.out_lb[s] = cur ? A.tb_rb[cur - 1] : 0ull;
 		A.out_rb[s] = A.tb_rb[A.next[cur]];
 		A.out_size[s] = A.next_size[cur];
+		A.out_pos[s] = A.next[cur];
 	}
 	grid.sync();
-	if (first < 2)
-	{
-		uint64_t const c = first ? A.c1 : A.c0;
-		uint32_t lo = 0, hi = count;
-		while (lo < hi)
-		{
-			uint32_t const mid = (lo + hi) >> 1;
-			if (A.out_rb[mid] <= c) lo = mid + 1; else hi = mid;
-		}
-		A.info[1 + first] = lo;
-	}
+	if (first < 2) walk_own(A, first);
 }
 
 cudaError_t launch_walk(walk_args const &A, cudaStream_t st)
 {
 	cudaError_t err = cudaSuccess;
-	if (launch_cooperative(walk_coop_kernel, A, 256, A.T, st, &err)) return err;
-	uint32_t const grid = (A.T + 255) / 256;
+	if (launch_cooperative(walk_coop_kernel, A, 256, A.t_bound, st, &err)) return err;
+	uint32_t const grid = (A.t_bound + 255) / 256;
 	walk_init_kernel <<<grid, 256, 0, st>>>(A);
 	for (uint32_t k = 1; k < A.levels; ++k)
 		walk_double_kernel <<<grid, 256, 0, st>>>(A, k);

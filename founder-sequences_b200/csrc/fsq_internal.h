@@ -37,7 +37,8 @@ struct block_args
 	uint32_t *sum_a, *sum_d;   // [B][m]
 
 	// MODE_EXACT output, per local column
-	uint2 *toplist;            // [(cap + 1) entries per column] (v, #{d > v}), v descending
+	uint2 *toplist;            // [(cap + 1) entries per column] (v, #{d > v}), v descending; row 0 belongs to local column list_col0
+	uint64_t list_col0;
 	uint32_t cap;
 	uint32_t *cnt;             // entries | complete << 31
 	uint32_t *h0;              // #{d == 0}
@@ -54,24 +55,6 @@ struct block_args
 
 size_t block_smem_bytes(block_args const &A, uint32_t n_warps, bool hist);
 cudaError_t launch_block(block_args const &A, uint32_t n_blocks, uint32_t n_warps, uint32_t tpw, bool hist, cudaStream_t st);
-// Blocked column step (fsq_bstep.cuh): T threads, E elements per thread, T E >= m.
-inline size_t bblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uint32_t NS, bool hist)
-{
-	auto r16 = [](size_t b) { return (b + 15) & ~size_t(15); };
-	uint32_t const n_warps = T >> 5;
-	size_t t = 0;
-	t += r16(2 * (size_t) A.cg * A.col_stride);
-	t += r16(2 * sizeof(uint64_t));
-	t += r16(sizeof(uint32_t) * (size_t) T * E);
-	t += r16(sizeof(uint32_t) * (size_t) T * NS) * 2;
-	t += r16(sizeof(uint32_t) * n_warps * NS) * 2;
-	t += r16(sizeof(uint32_t) * n_warps);
-	if (hist) t += r16(sizeof(uint32_t) * ((A.m + A.C + 2) / 2 + 1));
-	return t;
-}
-cudaError_t launch_bblock_e9(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
-cudaError_t launch_bblock_e17(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
-cudaError_t launch_bblock_e33(block_args const &A, uint32_t n_blocks, uint32_t T, uint32_t ns, bool hist, cudaStream_t st);
 // Chunked column step (fsq_cstep.cuh): T threads, E elements per thread, T E >= m; 32-bit histogram counters.
 inline size_t cblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uint32_t NS, bool hist)
 {
@@ -123,14 +106,37 @@ size_t stitch_smem_bytes(uint32_t m, uint32_t n_warps);
 cudaError_t launch_stitch(stitch_args const &A, cudaStream_t st);
 
 // ---- DP ------------------------------------------------------------------------------------------------------
+// Control words of a run, in device memory (uint32[16]): the stages are enqueued back to back and read their decisions
+// from here; the host reads the block once per batch of stages.
+enum
+{
+	F_CHANGED = 0,      // some stored value changed in this round
+	F_OVERFLOW = 1,     // max over the entries whose top list was too short to prove them exact of the value found (0 = none):
+	                    // every value computed under a short list is an upper bound of the true one, so lists that reach this far suffice
+	F_REACH = 2,        // the farthest any column looked back in the table (entries), over all rounds
+	F_UNSETTLED = 3,    // chains of this round whose result a later chain may have read half-way (see dp_chain_kernel)
+	F_BOUND = 4,        // F_REACH as it stood when the last guess ran: the look-back bound of the round queued behind it
+	F_DONE = 5,         // a round found the table at its fixed point: rounds queued behind it do nothing
+	F_ROUNDS = 6,       // rounds that did work
+	F_WINDOW_ERR = 7,   // the look-back left the part of the table whose masks and rmq cells are rebuilt between rounds
+	I_T = 8,            // traceback entries
+	I_K = 9,            // maximum segment size
+	I_NRED = 10,        // reduced segments
+	I_SEG_FIRST = 11, I_SEG_LAST = 12,      // reduced segments whose state this rank holds
+	I_POS_FIRST = 13, I_POS_LAST = 14,      // traceback positions whose right bound lies in this rank's columns
+	I_HALO_ERR = 15,    // the greedy reduction ran past the rows it had of the ranks after this one
+	N_CONTROL = 16
+};
+
 struct dp_args
 {
 	uint32_t m;
 	uint64_t n;                 // columns of the whole alignment
 	uint64_t L;
-	uint64_t col_base;          // global index of the first column this rank holds top lists for (0 on one GPU)
-	uint32_t t_first, t_last;   // the entries this rank computes: [t_first, t_last) (0 and n_entries on one GPU)
-	uint2 const *toplist; uint32_t cap; uint32_t const *cnt; uint32_t const *h0;     // indexed by column - col_base
+	uint64_t col_base;          // global index of the column cnt[0] / h0[0] belong to (this rank's first column)
+	uint64_t list_base;         // global index of the column whose top list is row 0 of toplist (a window of the rank's columns)
+	uint32_t t_first, t_last;   // the entries computed by this launch: [t_first, t_last)
+	uint2 const *toplist; uint32_t cap; uint32_t const *cnt; uint32_t const *h0;
 	uint32_t *tb_max, *tb_lb, *tb_size;   // [n - L + 1]; entry t describes right bound t + L
 	uint64_t *mk;               // [n - L + 1] in-block minima masks (see fsq_dp.cu)
 	uint32_t *lev;              // [n_levels][n_blk] rmq tables
@@ -139,63 +145,82 @@ struct dp_args
 	uint32_t chunk;             // entries per chain (multiple of 64); chain c owns entries [c chunk, (c + 1) chunk)
 	uint32_t n_chunks;
 	uint32_t *chunk_level;      // [2 n_chunks] scratch for the guess
-	uint32_t *flags;            // [0] some stored value changed  [1] 1 + column whose top list was too short to be exact
-	                            // [2] the farthest any column looked back in the table (entries), over all rounds
-	                            // [3] chains of this round whose result a later chain may have read half-way (see dp_chain_kernel)
-	                            // [4] flags[2] as it stood when the last guess ran: the look-back bound of a round queued behind it
+	uint32_t *flags;            // the control words above
 	uint32_t reach_bound;       // the look-back known when the round starts (0 in the first round)
-	uint32_t bound_on_device;   // take the bound from flags[4] instead (see dp_chain_kernel)
+	uint32_t bound_on_device;   // take the bound from flags[F_BOUND] instead (see dp_chain_kernel)
+	uint32_t skip_when_done;    // return at once when flags[F_DONE] is set
 	uint32_t w_first, w_last;   // masks and rmq cells are rebuilt for entries [w_first, w_last) (w_first a multiple of 64)
+	uint32_t lvl_first, lvl_last;   // the guess levels entries [lvl_first, lvl_last) (chains on the global grid of `chunk` entries)
 };
 
 cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st);       // every chain once, against the table as it stands
 cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st);        // between rounds: level the table, rebuild masks and rmq tables
 cudaError_t launch_dp_final(dp_args const &A, cudaStream_t st);        // the last column (entry n - L)
 cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st);      // masks and rmq tables from the table as it stands
+// End of a round on one rank: send[0..3] = {another round is needed, F_OVERFLOW, F_REACH, 0}.
+cudaError_t launch_dp_round_end(uint32_t *flags, uint32_t first_round, uint32_t *send, cudaStream_t st);
+// ... and with every rank's words at hand (gathered[size][4]): the merged decision into flags; clears the per-round words.
+cudaError_t launch_dp_round_merge(uint32_t *flags, uint32_t const *gathered, uint32_t size, uint32_t round_no, uint32_t back_bound, uint32_t one_chain, cudaStream_t st);
+cudaError_t launch_dp_overflow_merge(uint32_t *flags, uint32_t const *gathered, uint32_t size, cudaStream_t st);   // F_OVERFLOW = max over the ranks
 
 // Traceback (reference: segmentation_lp_context.cc:191-224) by pointer doubling: jump[k][t] = the entry 2^k hops
 // before t on the path t -> lb[t] - L.  The walk from the last entry is then T independent binary descents.
+// The number of entries stays on the device (ctl[I_T]); arrays are sized by the bound dp_size / L + 2.
 struct trace_args
 {
 	uint32_t const *tb_lb, *tb_max, *tb_size;
 	uint32_t L, dp_size, levels;
 	uint32_t *jump;              // [levels][dp_size]
-	uint32_t *count;             // [1] entries on the path
-	uint32_t *out_lb, *out_max, *out_size;   // [count] in text order
+	uint32_t *ctl;               // control words: I_T, I_K, I_POS_FIRST, I_POS_LAST are written here
+	uint32_t t_bound;            // capacity of the out arrays
+	uint32_t *out_lb, *out_max, *out_size;   // [t_bound] in text order
 	uint64_t *out_rb;
+	uint64_t c0, c1;             // this rank's columns
 };
-cudaError_t launch_trace_tables(trace_args const &A, cudaStream_t st);     // jump tables + count
-cudaError_t launch_trace_gather(trace_args const &A, uint32_t count, cudaStream_t st);
+cudaError_t launch_trace_tables(trace_args const &A, cudaStream_t st);     // jump tables + count + K
+cudaError_t launch_trace_gather(trace_args const &A, cudaStream_t st);     // the path in text order + this rank's positions
 
-// Greedy reduction (fsq_dp.cu).  The counts #{d_rb > lb} it needs are read off the top lists: for every traceback
-// position a row of `width` = K + 1 entries (v, #{d > v}) with #{d > v} <= K, v descending, padded with (~0, ~0).
+// Greedy reduction (fsq_dp.cu).  The counts #{d_rb > lb} it needs come from one row per traceback position: either
+// `width` entries (v, #{d > v}) of the column's top list with #{d > v} <= K, v descending, padded with (~0, ~0)
+// (rows are `width` uint2), or the divergence array itself (rows are m uint32).  A rank holds the rows of its own
+// positions [pos_first, pos_last) and the first `halo` rows of every rank (halo_rows[size][halo]).
 struct reduce_args
 {
-	uint32_t T, K, width;
-	uint64_t const *tb_rb;       // [T] right bounds of the traceback
+	uint32_t *ctl;               // I_T, I_K, I_POS_FIRST, I_POS_LAST are read here; I_HALO_ERR is raised here
+	uint32_t m, width;           // row length in the two forms
+	uint32_t row_kind;           // 0: list rows, 1: divergence rows
+	uint32_t rows_bound;         // capacity of own_rows in rows
+	uint64_t const *tb_rb;       // [T] right bounds of the traceback (replicated)
 	uint32_t const *tb_size;     // [T]
-	uint2 *lists;                // [T][width]
-	uint32_t *next;              // [T]: the last traceback entry merged into the segment that starts at entry u
-	uint32_t *next_size;         // [T]: that segment's size
-	// launch_reduce_lists only: the top lists of this rank's columns and the traceback positions it owns
+	void *own_rows;              // [rows_bound] rows of this rank's positions, compact
+	void const *halo_rows;       // [size][halo] rows, or null
+	uint32_t const *pos_first_all;   // [size + 1] first traceback position of every rank (device), or null
+	uint32_t halo, rank, size;
+	uint32_t *next;              // [rows_bound + 1] compact: the last traceback entry merged into the segment that starts at own entry u
+	uint32_t *next_size;         // [rows_bound + 1]: that segment's size; the last word receives I_HALO_ERR
+	// launch_reduce_lists only: the top lists of this rank's columns
 	uint2 const *toplist; uint32_t cap; uint32_t const *cnt; uint64_t col_base;
-	uint32_t pos_first, pos_last;
 };
-cudaError_t launch_reduce_lists(reduce_args const &A, cudaStream_t st);    // fill lists[pos_first .. pos_last)
+cudaError_t launch_reduce_lists(reduce_args const &A, cudaStream_t st);    // fill own_rows from the top lists
 cudaError_t launch_reduce(reduce_args const &A, cudaStream_t st);
+// pos_first_all[q] = first traceback position whose right bound is > q n_per, q = 0 .. size (device array of size + 1)
+cudaError_t launch_rank_positions(uint64_t const *tb_rb, uint32_t const *ctl, uint64_t n_per, uint32_t size, uint32_t *pos_first_all, cudaStream_t st);
+// next_all[size][rows_bound + 1] (gathered, compact per rank; the last word of nsize_all's blocks carries I_HALO_ERR) -> next[T], next_size[T]
+cudaError_t launch_scatter_next(uint32_t const *next_all, uint32_t const *nsize_all, uint32_t const *pos_first_all, uint32_t size, uint32_t rows_bound, uint32_t t_bound, uint32_t *next, uint32_t *next_size, uint32_t *ctl, cudaStream_t st);
 
 // The walk u -> next[u] + 1 from u = 0 (segmentation_lp_context.cc:335-390 merges in exactly this order), on the
 // device by pointer doubling: the reduced segments come out as arrays without a host loop over the traceback.
 struct walk_args
 {
-	uint32_t T, levels;          // 2^levels > T
+	uint32_t t_bound, levels;    // 2^levels > t_bound
+	uint32_t *ctl;               // reads I_T; writes I_NRED, I_SEG_FIRST, I_SEG_LAST
 	uint32_t const *next, *next_size;
 	uint64_t const *tb_rb;       // [T]
-	uint32_t *jump;              // [levels][T]
-	uint64_t *out_lb, *out_rb;   // [<= T]
+	uint32_t *jump;              // [levels][t_bound]
+	uint64_t *out_lb, *out_rb;   // [t_bound]
 	uint32_t *out_size;
+	uint32_t *out_pos;           // [t_bound] the traceback position a reduced segment ends at
 	uint64_t c0, c1;             // this rank's columns: it holds the state of the segments whose right bound lies in (c0, c1]
-	uint32_t *info;              // [0] number of reduced segments  [1], [2] first and one-past-last segment held here
 };
 cudaError_t launch_walk(walk_args const &A, cudaStream_t st);
 

@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(1024) pbwt_block_kernel(block_args const A)
 		{
 			uint64_t const kk = s + j - 1;
 			emit_top_list(H, R + (uint32_t) (j - 1), R, old, s_glob, m, A.cap,
-				A.toplist + kk * (A.cap + 1), A.cnt + kk, A.h0 + kk, zero_present);
+				A.toplist + (kk - A.list_col0) * (A.cap + 1), A.cnt + kk, A.h0 + kk, zero_present);
 		}
 		nibble_source src{(uint32_t const *) (colbuf + ((size_t) (g & 1) * A.cg + jj) * A.col_stride)};
 		column_step <uint16_t, TPW, HIST>(sh, m, A.n_tiles, A.nsym, R + (uint32_t) j, src, H);
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(1024) pbwt_block_kernel(block_args const A)
 	{
 		uint64_t const kk = s + n_cols - 1;
 		emit_top_list(H, R + (uint32_t) (n_cols - 1), R, old, s_glob, m, A.cap,
-			A.toplist + kk * (A.cap + 1), A.cnt + kk, A.h0 + kk, zero_present);
+			A.toplist + (kk - A.list_col0) * (A.cap + 1), A.cnt + kk, A.h0 + kk, zero_present);
 	}
 	if (MODE_LOCAL == A.mode)
 	{

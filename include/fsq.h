@@ -36,7 +36,6 @@ typedef enum fsq_status {
 typedef struct fsq_ctx fsq_ctx;                     /* one per device / host thread */
 typedef struct fsq_msa fsq_msa;                     /* column-major, 4-bit packed alignment resident in HBM */
 typedef struct fsq_segmentation fsq_segmentation;   /* result of the long path, device + host copies */
-typedef struct fsq_shard fsq_shard;                 /* one rank's part of a column-sharded run of the long path */
 
 /* ---- context ------------------------------------------------------------------------------------------ */
 
@@ -46,10 +45,14 @@ const char *fsq_last_error(const fsq_ctx *ctx);     /* ctx may be NULL: returns 
 const char *fsq_version(void);
 
 /* Tuning knobs (all have defaults; unknown keys are an error): "block_columns" (columns per scan block), "cap"
- * (initial bound on the per-column top list; grown automatically when the DP proves it too small), "keep_dp"
+ * (initial bound on the per-column top list; grown automatically, to what the DP proves sufficient, when it is too
+ * small; the bound a shape (m, n, L) ended with is remembered by the context, the option is never overwritten), "keep_dp"
  * (retain the full DP table for fsq_segmentation_dp_table), "store_states" (-1 auto, 0 re-scan for the boundary
  * states, 1 keep every column's state in pass B), "dp_chunks", "dp_max_rounds", "dp_guess_rounds" (DP chaining),
- * "kernel", "chunk", "warps", "stitch_sort", "stitch_group" (kernel selection, used by the parity tests). */
+ * "kernel", "chunk", "warps", "stitch_sort", "stitch_group" (kernel selection, used by the parity tests), "mem_limit"
+ * (plan device memory as if this many bytes were available), "window_blocks" (scan blocks per window of top lists:
+ * the exact scan and the DP then alternate over windows that share one list buffer), "halo" (rows of the ranks behind
+ * it that a rank's greedy reduction starts with). */
 int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value);
 int fsq_get_stat(const fsq_ctx *ctx, const char *key, double *value);   /* e.g. "ms_pack", "ms_pass_a", "ms_dp", "kernel_launches" */
 
@@ -131,60 +134,57 @@ int fsq_segment_sets(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment
 
 /* Replaces the K² set_intersection_size calls of merge_segments_task::execute
  * (founder-sequences/merge_segments_task.cc:133-176; lib/libbio/include/libbio/algorithm/set_count.hh:61-89) for the
- * adjacent reduced segments (segment, segment + 1): W[i * runs_rhs + j] = |S_i ∩ T_j| over the runs in PBWT order. */
+ * adjacent reduced segments (segment, segment + 1): W[i * runs_rhs + j] = |S_i ∩ T_j| over the runs in PBWT order.
+ * W must hold runs_lhs * runs_rhs ints; a reduced segment has at most max_segment_size runs, so
+ * fsq_segmentation_max_segment_size()^2 ints always suffice. */
 int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment, int32_t *W, uint32_t *runs_lhs, uint32_t *runs_rhs);
 
-/* ---- column-sharded operation (one process per GPU; the exchange itself is done by the caller over NCCL) ----------
+/* ---- column-sharded operation (one process -- or thread -- per GPU) -----------------------------------------------
  *
- * The reference runs the path in one process (no counterpart); these are the stages of fsq_segment() cut
- * where column shards exchange data.  Rank r holds the columns [c0_r, c1_r) of ONE alignment of n_total columns as an
- * fsq_msa whose first column is c0_r (fsq_msa_synth with col0, or fsq_msa_set_first_column).  Order of calls, with the
- * caller's collectives in brackets (founder-sequences_b200/sharded.py is the reference driver):
- *
- *   fsq_shard_local_summary      local scan from the identity state + prefix composition -> this rank's (pi, delta)
- *   [all-gather of the summaries]
- *   fsq_shard_set_start          true state at c0_r = composition of the summaries of the ranks before; block starts
- *   fsq_shard_scan               exact scan: top lists (and kept states) for the own columns; resets the DP table
- *   repeat: fsq_shard_dp_round   own DP entries against the table as it stands
- *           [broadcast of every rank's slice of tb_max; max-reduce of changed / reach]
- *           fsq_shard_dp_sync    level guess (optional) + masks and rmq tables of the whole table
- *   until no rank changed anything
- *   fsq_shard_dp_final           last entry (rank with the last column); [broadcast of the tb_max/tb_lb/tb_size slices;
- *                                max-reduce of the overflow flag -> fsq_shard_grow_cap and back to fsq_shard_scan]
- *   fsq_shard_traceback          every rank, from the complete table
- *   fsq_shard_reduce_lists       rows of the reduction's count lists for the own traceback positions
- *   [broadcast of every rank's rows]
- *   fsq_shard_reduce             greedy reduction (every rank) + the states of the own reduced segments
+ * The reference runs the path in one process (no counterpart).  Rank r of `size` holds the columns
+ * fsq_shard_columns() names of ONE alignment of n_total columns, as an fsq_msa whose first column is set accordingly
+ * (fsq_msa_synth with col0, or fsq_msa_set_first_column after an upload), and every rank calls fsq_segment_sharded()
+ * with its communicator.  The library does the exchanges itself, as all-gathers enqueued on the context's stream
+ * between its kernels (ncclAllGather over NVLink / NVSwitch): the ranks' boundary summaries (8 m bytes each), per DP
+ * round the ranks' slices of the table (4 bytes per column, in place) and four control words, the rest of the table
+ * once, and for the greedy reduction a few rows per rank.  No host thread takes part between the first and the last
+ * stage except to read the control words once per batch of stages.
  * Results are independent of the number of ranks and of the block size (tests/test_sharded*.py). */
+typedef struct fsq_comm fsq_comm;
+typedef struct fsq_local_group fsq_local_group;
+#define FSQ_COMM_ID_BYTES 128
+
+/* The columns [*c0, *c1) rank `rank` of `size` holds: equal shares of ceil(n_total / size) rounded up to 32 columns
+ * (the last rank holds what is left).  FSQ_ERR_ARG when a rank would hold no column. */
+int fsq_shard_columns(uint64_t n_total, int size, int rank, uint64_t *c0, uint64_t *c1);
+
+/* NCCL communicator, one rank per GPU.  Rank 0 makes the id (an ncclUniqueId) and hands it to the others by whatever
+ * means the host has (MPI, torch.distributed, a file); then every rank calls fsq_comm_create, which blocks until all have.
+ * libnccl.so.2 is opened at run time; a process that has it loaded already (PyTorch) shares that copy. */
+int fsq_comm_unique_id(uint8_t id[FSQ_COMM_ID_BYTES]);
+int fsq_comm_create(fsq_ctx *ctx, const uint8_t id[FSQ_COMM_ID_BYTES], int rank, int size, fsq_comm **out);
+/* The same over a communicator the host made itself (an ncclComm_t); it stays the host's. */
+int fsq_comm_adopt_nccl(fsq_ctx *ctx, void *nccl_comm, int rank, int size, fsq_comm **out);
+/* Ranks as threads of one process, each with its own context, possibly all on one device (how the tests drive several
+ * shards through one GPU): the collective is device copies ordered by events, the host threads meet at a barrier. */
+int fsq_local_group_create(int size, fsq_local_group **out);
+void fsq_local_group_free(fsq_local_group *group);
+int fsq_comm_create_local(fsq_ctx *ctx, fsq_local_group *group, int rank, fsq_comm **out);
+void fsq_comm_free(fsq_comm *comm);
+int fsq_comm_rank(const fsq_comm *comm);
+int fsq_comm_size(const fsq_comm *comm);
+
+/* For alignments uploaded shard by shard: the global index of the shard's first column. */
 int fsq_msa_set_first_column(fsq_msa *msa, uint64_t first_column);
-int fsq_shard_create(fsq_ctx *ctx, const fsq_msa *msa, uint64_t n_total, uint64_t segment_length_bound, fsq_shard **out);
-void fsq_shard_free(fsq_shard *s);
-/* Device pointers (m uint32 each, owned by the shard): the state after this rank's last column had the scan started
- * from the identity state at its first column. */
-int fsq_shard_local_summary(fsq_shard *s, const uint32_t **d_pi, const uint32_t **d_delta);
-/* d_pis / d_deltas: device arrays [count][m] with the summaries of the ranks before this one, in rank order;
- * first_columns[count]: their first columns (host).  count == 0 for the rank that starts at column 0. */
-int fsq_shard_set_start(fsq_shard *s, const uint32_t *d_pis, const uint32_t *d_deltas, const uint64_t *first_columns, uint32_t count);
-int fsq_shard_scan(fsq_shard *s);
-/* The DP table (device, `entries` uint32 each; entry t describes right bound t + L) and the range of entries this rank
- * computes, i.e. the slice it must send to the others. */
-int fsq_shard_dp_table(fsq_shard *s, uint32_t **d_max, uint32_t **d_lb, uint32_t **d_size, uint64_t *entries, uint64_t *own_first, uint64_t *own_last);
-int fsq_shard_dp_round(fsq_shard *s, uint32_t *changed, uint32_t *reach);
-int fsq_shard_dp_sync(fsq_shard *s, int guess, uint32_t reach);
-int fsq_shard_dp_single_chain(fsq_shard *s);       /* fallback: the next rounds run the own entries as one chain */
-int fsq_shard_dp_final(fsq_shard *s, uint32_t *overflow);
-int fsq_shard_grow_cap(fsq_shard *s);
-int fsq_shard_traceback(fsq_shard *s, uint32_t *count, uint32_t *max_segment_size);
-int fsq_shard_get_traceback(const fsq_shard *s, uint64_t *lb, uint64_t *rb, uint32_t *max_size, uint32_t *size);
-/* The traceback positions whose right bound lies in (c0, c1]: the rows of the reduction lists that the rank holding
- * columns [c0, c1) fills.  The traceback is replicated, so every rank can answer this for every other rank. */
-int fsq_shard_position_range(const fsq_shard *s, uint64_t c0, uint64_t c1, uint32_t *first, uint32_t *last);
-/* Device array [count][width] of (v, #{d > v}) pairs (2 uint32 each) and the rows [own_first, own_last) this rank filled. */
-int fsq_shard_reduce_lists(fsq_shard *s, uint32_t **d_lists, uint32_t *width, uint32_t *own_first, uint32_t *own_last);
-/* Reduced segments: their number and the range [own_first, own_last) whose states this rank holds. */
-int fsq_shard_reduce(fsq_shard *s, uint32_t *count, uint32_t *own_first, uint32_t *own_last);
-int fsq_shard_bounds(const fsq_shard *s, uint64_t *lb, uint64_t *rb, uint32_t *size);
-int fsq_shard_states(fsq_shard *s, uint32_t *a, uint32_t *d);      /* (own_last - own_first) x m each, to host memory */
+
+/* fsq_segment() over column shards; collective: every rank of `comm` calls it with its shard, the same n_total and the
+ * same bound.  Every rank receives the whole reduced segmentation (count, bounds, K, traceback); the states it holds
+ * are those of the reduced segments whose right bound lies in its columns, fsq_segmentation_own_range().
+ * comm == NULL (or a communicator of one rank) is fsq_segment(). */
+int fsq_segment_sharded(fsq_ctx *ctx, const fsq_msa *msa, fsq_comm *comm, uint64_t n_total, uint64_t segment_length_bound, fsq_segmentation **out);
+/* The reduced segments [*first, *last) whose states fsq_segmentation_states() returns ((last - first) x m each) and
+ * which fsq_segment_sets() / fsq_pair_weights() accept; all of them after fsq_segment(). */
+int fsq_segmentation_own_range(const fsq_segmentation *seg, uint32_t *first, uint32_t *last);
 
 #ifdef __cplusplus
 }

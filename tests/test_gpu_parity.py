@@ -295,3 +295,32 @@ def test_errors_are_loud(ctx, fsq):
     with pytest.raises(fsq.FsqError) as ei:
         ctx.msa_from_rows(rows)
     assert ei.value.code == fsq.ERR_ARG
+
+
+@pytest.mark.parametrize("m,n,L,C,wb", [(96, 3000, 8, 64, 3), (300, 2500, 12, 100, 1), (1500, 1200, 10, 0, 2)])
+def test_segmentation_with_windowed_top_lists(ctx, oracle, synth, m, n, L, C, wb):
+    """The exact scan and the DP alternate over windows of `wb` blocks that share one top-list buffer (what a shape whose
+    lists do not fit at once runs as); the reduction then works from the divergence arrays of a re-scan."""
+    rows = synth.synth_rows(m, n, seed=m + n, founders=7, gaps=True)
+    ctx.set_option("window_blocks", wb)
+    ctx.reset_stats()
+    compare_segmentation(ctx, oracle, rows, L, block_columns=C)
+    assert ctx.stat("windows") > 1
+
+
+def test_windowed_top_lists_grow_the_bound_where_it_fails(ctx, oracle, synth):
+    """A bound that is too small is found out in some window; the scan resumes there with the bound the DP proved."""
+    rows = synth.synth_rows(128, 2000, seed=9, founders=40, recomb_block=50, mu=0.01)
+    ctx.set_option("window_blocks", 2)
+    ctx.reset_stats()
+    compare_segmentation(ctx, oracle, rows, 6, block_columns=100, cap=2, sets=False)
+    assert ctx.stat("cap_retries") >= 1 and ctx.stat("windows") > 1
+
+
+def test_memory_limit_turns_into_windows(ctx, oracle, synth):
+    """mem_limit stands in for the device's answer: with room for the lists of a few blocks only, the plan is windows."""
+    rows = synth.synth_rows(200, 4000, seed=3, founders=9, gaps=True)
+    ctx.set_option("mem_limit", (1 << 30) + 4000 * 64 + 4100 * 32 + 300 * 128 * 8)
+    ctx.reset_stats()
+    compare_segmentation(ctx, oracle, rows, 10, block_columns=100, sets=False)
+    assert ctx.stat("windows") > 1

@@ -1,7 +1,8 @@
-"""The column-sharded protocol on CPU: world_size 2 and 3 over gloo, the per-rank engine replaced by the plain-Python
-stand-in of tests/cpu_shard.py (there is no CPU path in the product).  Covers the host logic of
-founder-sequences_b200/sharded.py: summary all-gather and prefix composition, the DP table exchange and its fixed-point
-rule, the exchange of the reduction lists, and the assembly of the result."""
+"""The host side of a column-sharded call on CPU: world_size 2 and 3 over gloo (tests/sharded_worker.py) -- the split rule,
+the hand-over of the communicator id through the process group, the assembly of the ranks' results.  The sharded run
+itself is CUDA code (fsq_segment_sharded; tests/test_sharded_gpu.py drives it with ranks as threads on one GPU,
+tests/sharded_torchrun.py with one rank per GPU over NCCL).  Also: the boundary stitch the sharding
+rests on, as a plain-Python model against straight scans."""
 import os
 import socket
 
@@ -19,12 +20,12 @@ def free_port():
 
 
 @pytest.mark.parametrize("world,case", [
-    (2, (10, 260, 6, 1, None)),
-    (2, (14, 300, 9, 2, [(0, 13), (13, 300)])),          # a boundary inside the first 2L columns
-    (3, (12, 330, 5, 3, None)),
-    (3, (9, 200, 4, 4, [(0, 64), (64, 199), (199, 200)])),   # a one-column last shard
+    (2, (10, 260, 6, 1)),
+    (2, (14, 300, 9, 2)),
+    (3, (12, 330, 5, 3)),
+    (3, (9, 200, 4, 4)),
 ])
-def test_sharded_protocol_over_gloo(tmp_path, world, case):
+def test_sharded_host_side_over_gloo(tmp_path, world, case):
     port = free_port()
     mp.spawn(run_rank, args=(world, port, case, str(tmp_path)), nprocs=world, join=True)
     for r in range(world):

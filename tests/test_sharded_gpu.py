@@ -1,6 +1,6 @@
-"""Column-sharded long path on the GPU: several shards of one alignment driven through one device (ranks as threads, the
-exchanges as device copies), against the oracle's unsharded answer.  The same driver runs under torchrun with NCCL
-(tests/sharded_torchrun.py, bench.py --gpus N)."""
+"""Column-sharded long path on the GPU (fsq_segment_sharded): several shards of one alignment driven through one device
+(ranks as threads, the library's ranks-as-threads communicator), against the oracle's unsharded answer.  The same
+entry point runs under torchrun with the library's NCCL communicator (tests/sharded_torchrun.py, bench.py --gpus N)."""
 import threading
 
 import numpy as np
@@ -23,12 +23,22 @@ def load_sharded():
     return mod
 
 
-def run_sharded(fsq, rows, L, parts, options=None, cuts=None):
+class ShardResult:
+    pass
+
+
+def run_sharded(fsq, rows, L, parts, options=None):
+    """`parts` ranks as threads of this process, each with its own context on device 0, through fsq_segment_sharded with
+    the library's ranks-as-threads communicator."""
     sh = load_sharded()
+    lib = fsq.load_library()
     m, n = rows.shape
-    ranges = cuts or sh.split_columns(n, parts)
-    shared = sh.ThreadComm.Shared(len(ranges))
-    results, errors = [None] * len(ranges), [None] * len(ranges)
+    ranges = sh.shard_columns(n, parts)
+    group = sh.LocalGroup(lib, parts)
+    results, errors = [None] * parts, [None] * parts
+    comp = np.zeros(256, np.uint8)
+    for i, ch in enumerate(sorted(set(rows.tobytes()) | {0})):
+        comp[ch] = i
 
     def work(rank):
         try:
@@ -36,55 +46,54 @@ def run_sharded(fsq, rows, L, parts, options=None, cuts=None):
             ctx = fsq.Context(0)
             for k, v in (options or {}).items():
                 ctx.set_option(k, v)
-            comp = np.zeros(256, np.uint8)
-            for i, ch in enumerate(sorted(set(rows.tobytes()) | {0})):
-                comp[ch] = i
             msa = ctx.msa_from_rows(np.ascontiguousarray(rows[:, c0:c1]), comp)
-            eng = sh.GpuShard(ctx, msa, c0, n, L)
+            comm = group.comm(ctx, rank)
             try:
-                results[rank] = sh.segment_sharded(eng, sh.ThreadComm(shared, rank))
+                seg = sh.segment_sharded(ctx, msa, comm, c0, n, L)
+                res = ShardResult()
+                res.K, res.count, res.own = seg.max_segment_size, seg.count, seg.own
+                res.traceback = seg.traceback()
+                res.lb, res.rb, res.size = seg.reduced_traceback()
+                res.a, res.d = seg.reduced_pbwt_samples()
+                res.cap_retries = ctx.stat("cap_retries")
+                res.dp_fallbacks = ctx.stat("dp_fallbacks")
+                res.windows = ctx.stat("windows")
+                seg.free()
+                results[rank] = res
             finally:
-                eng.close()
+                comm.free()
                 msa.free()
                 ctx.close()
-        except BaseException as e:      # noqa: a dead rank must not leave the others waiting on the barrier
+        except BaseException as e:      # noqa
             errors[rank] = e
-            shared.barrier.abort()
 
-    threads = [threading.Thread(target=work, args=(r,)) for r in range(len(ranges))]
+    threads = [threading.Thread(target=work, args=(r,)) for r in range(parts)]
     for t in threads:
         t.start()
     for t in threads:
-        t.join()
-    for e in errors:
-        if e is not None and not isinstance(e, threading.BrokenBarrierError):
-            raise e
+        t.join(timeout=300)
+    group.free()
     for e in errors:
         if e is not None:
             raise e
+    assert all(r is not None for r in results), "a rank did not finish"
     return results
 
 
 def check_against_oracle(oracle, rows, L, results):
+    sh = load_sharded()
     with oracle.open(rows) as o:
         assert o.segment(L) == 0
         olb, orb, _, osz = o.reduced()
         oa, od = o.reduced_states()
         tlb, trb, tmx, tsz = o.traceback()
         K = o.K()
-    a = np.zeros_like(oa)
-    d = np.zeros_like(od)
-    covered = np.zeros(len(olb), bool)
     for res in results:
         assert res.K == K
         for x, y in zip(res.traceback, (tlb, trb, tmx, tsz)):
             assert np.array_equal(x, y)
         assert np.array_equal(res.lb, olb) and np.array_equal(res.rb, orb) and np.array_equal(res.size, osz)
-        f, l = res.own
-        assert not covered[f:l].any()
-        covered[f:l] = True
-        a[f:l], d[f:l] = res.a, res.d
-    assert covered.all()
+    a, d = sh.assemble_states([(r.own, r.a, r.d) for r in results], len(olb), rows.shape[0])
     assert np.array_equal(a, oa) and np.array_equal(d, od)
 
 
@@ -96,12 +105,23 @@ def test_sharded_matches_oracle(fsq, oracle, synth, parts, m, n, L, C):
     check_against_oracle(oracle, rows, L, run_sharded(fsq, rows, L, parts, opts))
 
 
-def test_sharded_uneven_cuts_and_tiny_shards(fsq, oracle, synth):
-    """Shards shorter than L, a shard boundary inside the first 2L columns, and a one-column last shard."""
-    m, n, L = 64, 1500, 12
+def test_sharded_tiny_shards(fsq, oracle, synth):
+    """Shards of 32 columns: shorter than 2L, so that shard boundaries fall inside the first 2L columns and inside the
+    last L, and several ranks own no DP entry or no traceback position at all."""
+    m, n, L = 64, 250, 24
     rows = synth.synth_rows(m, n, seed=5, founders=6, gaps=False)
-    cuts = [(0, 7), (7, 20), (20, 700), (700, 1499), (1499, 1500)]
-    check_against_oracle(oracle, rows, L, run_sharded(fsq, rows, L, len(cuts), {"block_columns": 50}, cuts))
+    check_against_oracle(oracle, rows, L, run_sharded(fsq, rows, L, 8, {"block_columns": 16}))
+
+
+def test_sharded_rejects_too_many_ranks(fsq, synth):
+    rows = synth.synth_rows(16, 100, seed=1, founders=3)
+    with pytest.raises(ValueError):
+        load_sharded().shard_columns(100, 8)
+    lib = fsq.load_library()
+    import ctypes as C
+    c0, c1 = C.c_uint64(), C.c_uint64()
+    assert lib.fsq_shard_columns(100, 8, 7, C.byref(c0), C.byref(c1)) == fsq.ERR_ARG
+    assert lib.fsq_shard_columns(100, 2, 1, C.byref(c0), C.byref(c1)) == 0 and (c0.value, c1.value) == (64, 100)
 
 
 def test_sharded_small_cap_retries_and_sequential_fallback(fsq, oracle, synth):
@@ -109,15 +129,21 @@ def test_sharded_small_cap_retries_and_sequential_fallback(fsq, oracle, synth):
     res = run_sharded(fsq, rows, 6, 3, {"block_columns": 100, "cap": 2})
     assert res[0].cap_retries >= 1
     check_against_oracle(oracle, rows, 6, res)
-    sh = load_sharded()
-    # max_rounds = 2 forces the rank-by-rank fallback
-    orig = sh.segment_sharded
-    try:
-        sh.segment_sharded = lambda e, c, **kw: orig(e, c, max_rounds=2, guess_rounds=0)
-        res = run_sharded(fsq, rows, 6, 3, {"block_columns": 100, "dp_chunks": 1000})
-    finally:
-        sh.segment_sharded = orig
+    # two rounds at most: the ranks then take turns, each running its entries as one chain
+    res = run_sharded(fsq, rows, 6, 3, {"block_columns": 100, "dp_chunks": 1000, "dp_max_rounds": 2, "dp_guess_rounds": 0})
+    assert res[0].dp_fallbacks >= 1
     check_against_oracle(oracle, rows, 6, res)
+
+
+def test_sharded_windows_and_short_halo(fsq, oracle, synth):
+    """Top lists in windows of two blocks over one buffer (every round re-scans them; the reduction then runs from the
+    divergence arrays of a re-scan), and a halo of one row, which the greedy runs outgrow."""
+    rows = synth.synth_rows(96, 2400, seed=21, founders=5, gaps=True)
+    res = run_sharded(fsq, rows, 8, 3, {"block_columns": 64, "window_blocks": 2, "halo": 1})
+    assert res[0].windows > 1
+    check_against_oracle(oracle, rows, 8, res)
+    res = run_sharded(fsq, rows, 8, 3, {"block_columns": 64, "halo": 1})
+    check_against_oracle(oracle, rows, 8, res)
 
 
 def test_sharded_under_torchrun_nccl():
