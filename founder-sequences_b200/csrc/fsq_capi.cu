@@ -1395,9 +1395,13 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 	uint32_t total_rounds = 0;
 	auto grow_cap = [&](uint32_t proven) -> int {
 		if (R->cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list with cap = m");
-		// every value computed under the short lists is an upper bound of the true one: lists that reach this far are proven
-		// to suffice for what was computed so far; a quarter more, for what follows (windows) and as slack
-		uint64_t next = std::max <uint64_t>((uint64_t) proven + proven / 4 + 8, (uint64_t) R->cap + 1);
+		// Every value computed under the short lists is an upper bound of the true one, so lists that reach as far as the
+		// largest of them are proven to suffice (a quarter more: slack, and what later windows may need) -- but where no
+		// candidate at all was within the lists that bound is the whole-range value, close to m, and says little: the bound
+		// at most doubles per retry (127 -> 255 -> 511 -> 1023: config 3 settles at 1023 where its prefixes peak near 700,
+		// and lists four times as long as needed cost more in every later call than one more retry does in the first).
+		uint64_t const entries = (uint64_t) R->cap + 1;
+		uint64_t next = std::max <uint64_t>(entries + 1, std::min <uint64_t>(2 * entries, (uint64_t) proven + proven / 4 + 8));
 		next = (next + 7) & ~7ull;
 		R->cap = (uint32_t) std::min <uint64_t>(m, next - 1);
 		ctx->stats["cap_retries"] += 1;
@@ -1544,10 +1548,11 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 		CK(cudaMemcpyAsync(seg->dp_size.data(), R->tb_size(), dp_size * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		CK(cudaStreamSynchronize(ctx->stream));
 	}
-	// the traceback stays on the device with the handle; it is copied when asked for
-	seg->tr_lb.adopt(R->tr_lb); seg->tr_rb.adopt(R->tr_rb); seg->tr_max.adopt(R->tr_max); seg->tr_size.adopt(R->tr_size);
+	// the traceback stays on the device with the handle (handed over when the run is through with it); it is copied when asked for
+	auto hand_over_traceback = [&] { seg->tr_lb.adopt(R->tr_lb); seg->tr_rb.adopt(R->tr_rb); seg->tr_max.adopt(R->tr_max); seg->tr_size.adopt(R->tr_size); };
 	if (!(seg->K < m))
 	{
+		hand_over_traceback();
 		// generate_context.cc:192-200; the traceback stays available through the handle for inspection
 		gd.ok = true;
 		*out = seg;
@@ -1565,7 +1570,7 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 		std::vector <uint64_t> cols(cnt);
 		if (cnt)
 		{
-			CK(cudaMemcpyAsync(cols.data(), seg->tr_rb.as <uint64_t>() + pos_first, (size_t) cnt * 8, cudaMemcpyDeviceToHost, ctx->stream));
+			CK(cudaMemcpyAsync(cols.data(), R->tr_rb.as <uint64_t>() + pos_first, (size_t) cnt * 8, cudaMemcpyDeviceToHost, ctx->stream));
 			CK(cudaStreamSynchronize(ctx->stream));
 		}
 		for (auto &c : cols) c -= R->c0;
@@ -1636,6 +1641,7 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 	}
 	seg->own_first = seg_first; seg->own_last = seg_last;
 	seg->red_a.adopt(R->red_a); seg->red_d.adopt(R->red_d);
+	hand_over_traceback();
 	gd.ok = true;
 	*out = seg;
 	return FSQ_OK;

@@ -226,9 +226,15 @@ static void rmq_update(rmq64 *r, uint64_t last_idx)
 	}
 }
 
+/* Test switch: answer every query with the exact leftmost minimum instead.  The reference does NOT do this (SURVEY.md
+ * F3); the switch exists so that tests can show an input on which the two differ (tests/golden/rmq_dp_quirk.npz). */
+static int g_exact_rmq = 0;
+void fsqo_set_exact_rmq(int on) { g_exact_rmq = on; }
+
 /* rmq.hh:87-105 */
 static uint64_t rmq_query(rmq64 const *r, uint64_t beg, uint64_t end)
 {
+	if (g_exact_rmq) return naive_min(r, beg, end);
 	uint64_t const beg_block = beg / 64 + 1;
 	uint64_t const end_block = end / 64;
 	if (beg_block >= end_block)

@@ -39,8 +39,10 @@ namespace fseq = founder_sequences;
 namespace lb = libbio;
 
 // libbio::dispatch_ptr pulls these two symbols in; nothing from libdispatch is used.
+#ifndef FSQ_REF_HARNESS_NO_DISPATCH_STUBS      // (oracle/_ref/founder_sequences_ref gets them from the host driver's source)
 extern "C" void dispatch_retain(dispatch_object_t) {}
 extern "C" void dispatch_release(dispatch_object_t) {}
+#endif
 
 namespace {
 

@@ -69,6 +69,12 @@ def main():
     case("binary12x80_L3", rng.choice(np.frombuffer(b"AC", np.uint8), size=(12, 80), p=[0.8, 0.2]), 3)
     case("random6x40_notreducible", rng.choice(np.frombuffer(b"ACGT", np.uint8), size=(6, 40)), 3)
 
+    # An alignment on which founder_sequences::rmq's behaviour shows in the DP table: with an exact leftmost range-min in
+    # its place, table (lb of hundreds of entries), traceback and reduced segmentation all come out different (found by
+    # random search over low-diversity binary alignments, tests/golden/find_rmq_dp_quirk.py; few rows and rare changes
+    # make the ranges between consecutive divergence values span many 64-entry blocks).
+    case("rmq_dp_quirk_4x1599_L4", np.load(os.path.join(HERE, "rmq_dp_quirk_rows.npy")), 4)
+
     # rmq.hh, compiled as is: values that make the quirks visible
     vals = rng.integers(0, 1000, size=4096).astype(np.uint32)
     beg = rng.integers(0, 4095, size=3000).astype(np.uint64)

@@ -154,6 +154,30 @@ def compare_segmentation(ctx, oracle, rows, L, block_columns=None, cap=None, set
             return seg.max_segment_size, len(rlb)
 
 
+def test_rmq_quirk_decides_the_table(ctx, oracle):
+    """The fixture on which the reference's rmq (include/founder_sequences/rmq.hh:61-106: sparse levels over blocks
+    {i, i+1, i+3, ...}, block-table candidate ahead of the left partial block on ties) decides the DP table, against the
+    values the reference's own code produced (tests/golden/make_golden.py).  tests/test_oracle_golden.py shows that an
+    exact leftmost range-min gives a different table, traceback and segmentation on it."""
+    import os
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "rmq_dp_quirk_4x1599_L4.npz"))
+    rows, L = z["rows"], int(z["L"])
+    for opts in ({}, {"block_columns": 100}, {"dp_chunks": 1}, {"dp_chunks": 5}):
+        for k, v in opts.items():
+            ctx.set_option(k, v)
+        ctx.set_option("keep_dp", 1)
+        with ctx.msa_from_rows(rows) as msa, ctx.segment(msa, L) as seg:
+            lb, rb, mx, sz = seg.dp_table(len(z["dp_lb"]))
+            assert np.array_equal(lb, z["dp_lb"]) and np.array_equal(rb, z["dp_rb"]) and np.array_equal(mx, z["dp_max"]) and np.array_equal(sz, z["dp_size"])
+            for got, key in zip(seg.traceback(), ("tb_lb", "tb_rb", "tb_max", "tb_size")):
+                assert np.array_equal(got, z[key]), key
+            rlb, rrb, rsz = seg.reduced_traceback()
+            assert np.array_equal(rlb, z["red_lb"]) and np.array_equal(rrb, z["red_rb"]) and np.array_equal(rsz, z["red_size"])
+            a, d = seg.reduced_pbwt_samples()
+            assert np.array_equal(a, z["red_a"]) and np.array_equal(d, z["red_d"])
+    compare_segmentation(ctx, oracle, rows, L)
+
+
 def test_kat_segmentation(ctx, oracle):
     rows = as_rows(KAT_ROWS)
     compare_segmentation(ctx, oracle, rows, 2, block_columns=4)
