@@ -27,7 +27,7 @@ OK, ERR_ARG, ERR_CUDA, ERR_SHORT, ERR_NOT_REDUCIBLE, ERR_NOMEM, ERR_UNSUPPORTED,
 EXPORTS = [
     "fsq_create", "fsq_destroy", "fsq_last_error", "fsq_version", "fsq_set_option", "fsq_get_stat",
     "fsq_msa_from_rows", "fsq_msa_from_device_rows", "fsq_msa_synth", "fsq_synth_rows_device", "fsq_msa_free",
-    "fsq_msa_rows", "fsq_msa_columns", "fsq_pbwt_states", "fsq_segment", "fsq_segmentation_free",
+    "fsq_msa_rows", "fsq_msa_columns", "fsq_identity_columns", "fsq_pbwt_states", "fsq_segment", "fsq_segmentation_free",
     "fsq_segmentation_count", "fsq_segmentation_max_segment_size", "fsq_segmentation_bounds",
     "fsq_segmentation_states", "fsq_segmentation_states_view", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
     "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights",
@@ -77,6 +77,7 @@ def load_library():
     proto("fsq_msa_free", None, [vp])
     proto("fsq_msa_rows", u32, [vp])
     proto("fsq_msa_columns", u64, [vp])
+    proto("fsq_identity_columns", ci, [vp, vp, vp, C.POINTER(u64), pp])
     proto("fsq_pbwt_states", ci, [vp, vp, vp, u32, vp, vp])
     proto("fsq_segment", ci, [vp, vp, u64, pp])
     proto("fsq_segmentation_free", None, [vp])
@@ -176,6 +177,17 @@ class Context:
 
     def synth_rows_device(self, dptr, row_stride, m, n, seed, founders, gaps=False, col0=0):
         self.check(self.lib.fsq_synth_rows_device(self.h, C.c_void_p(dptr), row_stride, m, n, col0, seed, founders, 1 if gaps else 0))
+
+    def identity_columns(self, msa, want_msa=False):
+        """remove_identity_columns' test: the 0/1 mask of the columns in which all rows agree, and (want_msa) the alignment
+        without them."""
+        mask = np.zeros(msa.n, np.uint8)
+        cnt = C.c_uint64()
+        h = C.c_void_p()
+        self.check(self.lib.fsq_identity_columns(self.h, msa.h, _p(mask), C.byref(cnt), C.byref(h) if want_msa else None))
+        if want_msa:
+            return mask, Msa(self, h, msa.m, msa.n - cnt.value)
+        return mask
 
     # ---- the path ----
     def pbwt_states(self, msa, columns):

@@ -64,9 +64,18 @@ def build_oracle():
     _run(["make", "-C", os.path.join(ROOT, "oracle"), "libfsq_oracle.so"])
     if os.path.isdir("/root/reference/founder-sequences"):
         _run(["make", "-C", os.path.join(ROOT, "oracle"), "ref"])
+        _run(["make", "-C", os.path.join(ROOT, "host"), "ref"])
+
+
+def build_host():
+    """host/_build/founder_sequences_b200: the command-line host driver.  It compiles the reference's joiner and writer
+    sources where they lie, so it is built where the reference tree exists; the binary travels with the snapshot."""
+    if os.path.isdir("/root/reference/founder-sequences"):
+        _run(["make", "-C", os.path.join(ROOT, "host"), "all"])
 
 
 if __name__ == "__main__":
     force = "--force" in sys.argv
     print(build_library(force=force, verbose="-v" in sys.argv))
+    build_host()
     build_oracle()

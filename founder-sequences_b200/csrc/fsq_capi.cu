@@ -203,6 +203,7 @@ struct geometry
 	// chunked column step (fsq_cstep.cuh): E elements per thread, T threads, symbols sym0 .. sym0 + ns - 1
 	bool chunked;          // the default where it applies; otherwise the striped kernel (fsq_step.cuh)
 	uint32_t E, T, ns, sym0;
+	uint32_t digits;       // chunked: 2 when the comps that occur span more than 8 values (two base-4 digit steps per column)
 };
 
 geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
@@ -229,7 +230,15 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 	g.sym0 = lo;
 	g.ns = hi - lo + 1;
 	int64_t const kern = ctx->opt("kernel", 0);        // 0 auto, 1 striped, 3 chunked
-	g.chunked = (0 == kern || 3 == kern) && g.ns <= 8 && m <= cblock_thread_limit(53) * 53u;
+	g.chunked = (0 == kern || 3 == kern) && m <= cblock_thread_limit(53) * 53u;
+	g.digits = 1;
+	if (g.chunked && g.ns > 8)
+	{
+		// 9 .. 16 comps: each column as two steps over the base-4 digits of the comps as they stand (no offset)
+		g.digits = 2;
+		g.sym0 = 0;
+		g.ns = 4;
+	}
 	uint32_t threads = g.n_warps * 32, regs = 64;
 	if (g.chunked)
 	{
@@ -275,7 +284,7 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 			{
 				block_args P;
 				memset(&P, 0, sizeof P);
-				P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m;
+				P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m; P.digits = g.digits;
 				uint64_t const res = (uint64_t) ctx->prop.multiProcessorCount * per_sm;
 				P.C = (uint32_t) std::min <uint64_t>(4096, std::max <uint64_t>(64, (msa->n + res - 1) / res));
 				if ((cblock_smem_bytes(P, g.T, g.E, g.ns, true) + 1024) * per_sm <= (size_t) ctx->prop.sharedMemPerMultiprocessor) break;
@@ -287,13 +296,13 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 		uint64_t const resident = (uint64_t) ctx->prop.multiProcessorCount * per_sm;
 		C = (int64_t) ((msa->n + resident - 1) / resident);
 		C = std::max <int64_t>(C, 64);
-		int64_t c_max = std::min <int64_t>(4096, 65534 - (int64_t) m - 2);
+		int64_t c_max = std::min <int64_t>(4096, (g.chunked ? (int64_t) FSQ_CODE_LIMIT : 65534) - (int64_t) m - 2);
 		if (g.chunked)
 		{
 			// one CTA per SM and still too large (many rows): the histogram has one counter per row and per column of the block
 			block_args P;
 			memset(&P, 0, sizeof P);
-			P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m; P.C = 0;
+			P.cg = g.cg; P.col_stride = msa->col_stride; P.m = m; P.C = 0; P.digits = g.digits;
 			size_t const fixed = cblock_smem_bytes(P, g.T, g.E, g.ns, true) + 1024;
 			size_t const room = (size_t) ctx->prop.sharedMemPerBlockOptin > fixed ? ((size_t) ctx->prop.sharedMemPerBlockOptin - fixed) / 4 : 0;
 			c_max = std::min <int64_t>(c_max, (int64_t) std::max <size_t>(room, 1));
@@ -309,7 +318,7 @@ geometry choose_geometry(fsq_ctx *ctx, fsq_msa const *msa)
 			if (0 != ctx->opt("whole_waves", 1)) C = std::min <int64_t>(C, c_max); else C = c_max;
 		}
 	}
-	C = std::min <int64_t>(C, 65534 - (int64_t) m - 2);
+	C = std::min <int64_t>(C, (g.chunked ? (int64_t) FSQ_CODE_LIMIT : 65534) - (int64_t) m - 2);
 	C = std::max <int64_t>(C, 1);
 	g.C = (uint32_t) C;
 	g.cg = std::min(g.cg, g.C);
@@ -347,6 +356,7 @@ void fill_common(block_args &A, fsq_msa const *msa, geometry const &g)
 	A.C = g.C;
 	A.cg = g.cg;
 	A.magic = 0x4B000000u;
+	A.digits = g.digits;
 }
 
 __global__ void iota_kernel(uint32_t *a, uint32_t *d, uint32_t m, uint32_t dval)
@@ -375,18 +385,22 @@ __global__ void gather_stored_states_kernel(
 )
 {
 	// rbs: the right bounds of all reduced segments; this rank's are [ctl[I_SEG_FIRST], ctl[I_SEG_LAST]) (the grid may be larger)
-	uint32_t const t = blockIdx.x;                 // grid.x: up to 2^31 - 1 positions
+	uint32_t const t = blockIdx.x;                 // grid.x: up to 2^31 - 1 positions; one CTA copies one state
 	if (ctl[I_SEG_FIRST] + t >= ctl[I_SEG_LAST]) return;
-	uint32_t const i = blockIdx.y * blockDim.x + threadIdx.x;
-	if (i >= m) return;
 	uint64_t const k = rbs[ctl[I_SEG_FIRST] + t] - col0 - 1;          // local column whose output state this is (rbs are global right bounds)
 	uint32_t const b = (uint32_t) (k / C);
 	uint32_t const r = R[b];
-	uint32_t const w = states[k * stride + i];
-	uint32_t const code = w >> 16;
-	uint32_t const v = code >= r ? (uint32_t) (col0 + (uint64_t) b * C + 1 + (code - r)) : oldvals[(size_t) b * m + code];
-	dst_a[(size_t) t * m + i] = w & 0xffffu;
-	dst_d[(size_t) t * m + i] = v;
+	uint32_t const base = (uint32_t) (col0 + (uint64_t) b * C + 1) - r;
+	uint32_t const *src = states + k * stride;
+	uint32_t const *old = oldvals + (size_t) b * m;
+	uint32_t *da = dst_a + (size_t) t * m, *dd = dst_d + (size_t) t * m;
+	for (uint32_t i = threadIdx.x; i < m; i += blockDim.x)
+	{
+		uint32_t const w = src[i];
+		uint32_t const code = w >> 16;
+		da[i] = w & 0xffffu;
+		dd[i] = code >= r ? base + code : old[code];
+	}
 }
 
 // Everything the scans share: local summaries, true block start states, their rank compression.
@@ -675,6 +689,9 @@ struct fsq_run
 	uint32_t t_bound{}, rows_bound{}, width{}, halo{16};
 	dbuf tr_lb, tr_rb, tr_max, tr_size, jump, rows, rows_a, halo_rows, pos_all, next_own, nsize_own, next_all, nsize_all, next, nsize;
 	dbuf walk_jump, red_lb, red_rb, red_size, red_pos, red_a, red_d;
+	dbuf lt_jump, lt_hops, lt_xport, lt_xport_all, lt_entry, lt_own, lt_own_all;      // traceback over column shards
+	bool trace_replicated{false};       // fall back to the traceback over the whole table on every rank (needs all of it gathered)
+	bool tables_gathered{false};
 	hbuf h_ctl, h_red;
 	uint32_t h[N_CONTROL]{};    // the control words as last read
 
@@ -1055,6 +1072,26 @@ int run_enqueue_round(fsq_run *R, uint32_t round_no, size_t w_begin, size_t w_en
 	return FSQ_OK;
 }
 
+// Every rank receives the whole table (three in-place all-gathers): only the traceback over the whole table and the
+// keep_dp test tap need it; the rounds exchange tb_max alone and the sharded traceback reads own entries only.
+int run_gather_tables(fsq_run *R)
+{
+	fsq_ctx *ctx = R->ctx;
+	if (R->size <= 1 || R->tables_gathered) return FSQ_OK;
+	phase px(ctx, "exchange");
+	R->comm->group_begin();
+	size_t const off = (size_t) R->rank * R->n_per, bytes = (size_t) R->n_per * 4;
+	cudaError_t e = R->comm->all_gather(R->tbx_max.as <uint32_t>() + off, R->tbx_max.p, bytes, ctx->stream);
+	if (cudaSuccess == e) e = R->comm->all_gather(R->tbx_lb.as <uint32_t>() + off, R->tbx_lb.p, bytes, ctx->stream);
+	if (cudaSuccess == e) e = R->comm->all_gather(R->tbx_size.as <uint32_t>() + off, R->tbx_size.p, bytes, ctx->stream);
+	cudaError_t const e2 = R->comm->group_end();
+	if (cudaSuccess != e || cudaSuccess != e2)
+		return fail(ctx, FSQ_ERR_CUDA, "exchange of the DP table failed: %s", R->comm->error.empty() ? "CUDA error" : R->comm->error.c_str());
+	px.stop();
+	R->tables_gathered = true;
+	return FSQ_OK;
+}
+
 // The last entry (segmentation_lp_context.cc:165-185), on the rank that holds the last column; then every rank learns
 // whether any list was too short, and (several ranks) receives the rest of the table.
 int run_enqueue_final(fsq_run *R, bool rescan_last_window)
@@ -1080,16 +1117,15 @@ int run_enqueue_final(fsq_run *R, bool rescan_last_window)
 		uint32_t *mine = xs + 4 * (size_t) R->rank;
 		CK(launch_dp_round_end(ctl, 0, mine, ctx->stream));
 		phase px(ctx, "exchange");
-		R->comm->group_begin();
-		size_t const off = (size_t) R->rank * R->n_per, bytes = (size_t) R->n_per * 4;
-		cudaError_t e = R->comm->all_gather(R->tbx_max.as <uint32_t>() + off, R->tbx_max.p, bytes, ctx->stream);
-		if (cudaSuccess == e) e = R->comm->all_gather(R->tbx_lb.as <uint32_t>() + off, R->tbx_lb.p, bytes, ctx->stream);
-		if (cudaSuccess == e) e = R->comm->all_gather(R->tbx_size.as <uint32_t>() + off, R->tbx_size.p, bytes, ctx->stream);
-		if (cudaSuccess == e) e = R->comm->all_gather(mine, xs, 16, ctx->stream);
-		cudaError_t const e2 = R->comm->group_end();
-		if (cudaSuccess != e || cudaSuccess != e2)
-			return fail(ctx, FSQ_ERR_CUDA, "exchange of the DP table failed: %s", R->comm->error.empty() ? "CUDA error" : R->comm->error.c_str());
+		if (cudaSuccess != R->comm->all_gather(mine, xs, 16, ctx->stream))
+			return fail(ctx, FSQ_ERR_CUDA, "exchange of the DP flags failed: %s", R->comm->error.empty() ? "CUDA error" : R->comm->error.c_str());
 		px.stop();
+		R->tables_gathered = false;
+		if (R->trace_replicated || ctx->opt("keep_dp", 0))
+		{
+			int const rc = run_gather_tables(R);
+			if (rc) return rc;
+		}
 		CK(launch_dp_overflow_merge(ctl, xs, (uint32_t) R->size, ctx->stream));
 		ctx->stats["kernel_launches"] += 2;
 	}
@@ -1114,9 +1150,6 @@ int run_alloc_tail(fsq_run *R)
 	fsq_ctx *ctx = R->ctx;
 	if (R->tr_lb.p) return FSQ_OK;
 	uint32_t const tb = R->t_bound, rb = R->rows_bound;
-	uint32_t levels = 1;
-	while ((1ull << levels) <= R->dp_size / R->L + 1) ++levels;
-	CK(R->jump.alloc(ctx, (size_t) levels * R->dp_size * 4));
 	CK(R->tr_lb.alloc(ctx, (size_t) tb * 4)); CK(R->tr_rb.alloc(ctx, (size_t) tb * 8)); CK(R->tr_max.alloc(ctx, (size_t) tb * 4)); CK(R->tr_size.alloc(ctx, (size_t) tb * 4));
 	CK(R->next_own.alloc(ctx, ((size_t) rb + 1) * 4)); CK(R->nsize_own.alloc(ctx, ((size_t) rb + 1) * 4));
 	if (R->size > 1)
@@ -1138,12 +1171,60 @@ int run_enqueue_traceback(fsq_run *R)
 	int rc = run_alloc_tail(R);
 	if (rc) return rc;
 	phase pt(ctx, "traceback");
+	if (R->size > 1 && !R->trace_replicated)
+	{
+		// every rank over its own entries; the ranks exchange where a path can enter them and their parts of the path
+		ltrace_args A;
+		memset(&A, 0, sizeof A);
+		A.tb_lb = R->tb_lb(); A.tb_max = R->tb_max(); A.tb_size = R->tb_size();
+		A.L = (uint32_t) R->L; A.dp_size = (uint32_t) R->dp_size;
+		A.own_first = R->t_first; A.own_last = R->t_last;
+		A.has_final = R->c1 == R->n ? 1u : 0u;
+		A.own_n = R->t_last - R->t_first + A.has_final;
+		// the top table must span any path inside the rank (its jumps are the exits): 2^(levels - 1) hops
+		A.levels = 2;
+		while ((1ull << (A.levels - 1)) <= (uint64_t) A.own_n / R->L + 2) ++A.levels;
+		A.window = (uint32_t) std::min <uint64_t>(std::max <uint64_t>(R->n_per, 1), (uint64_t) std::max <int64_t>(1, ctx->opt("trace_window", 1 << 15)));
+		A.rank = (uint32_t) R->rank; A.size = (uint32_t) R->size; A.n_per = R->n_per;
+		A.rows_bound = R->rows_bound; A.t_bound = R->t_bound;
+		size_t const xs = (size_t) A.window + 2;
+		if (!R->lt_jump.p)
+		{
+			CK(R->lt_jump.alloc(ctx, (size_t) A.levels * std::max <uint32_t>(A.own_n, 1) * 4)); CK(R->lt_hops.alloc(ctx, (size_t) A.levels * std::max <uint32_t>(A.own_n, 1) * 4));
+			CK(R->lt_xport.alloc(ctx, xs * 8)); CK(R->lt_xport_all.alloc(ctx, xs * 8 * R->size));
+			CK(R->lt_entry.alloc(ctx, (size_t) R->size * 4));
+			CK(R->lt_own.alloc(ctx, (size_t) A.rows_bound * 20)); CK(R->lt_own_all.alloc(ctx, (size_t) A.rows_bound * 20 * R->size));
+		}
+		A.jump = R->lt_jump.as <uint32_t>(); A.hops = R->lt_hops.as <uint32_t>();
+		A.xport = R->lt_xport.as <uint2>(); A.xport_all = R->lt_xport_all.as <uint2>();
+		A.ctl = R->control();
+		A.pos_first_all = R->pos_all.as <uint32_t>(); A.entry_all = R->lt_entry.as <uint32_t>();
+		A.own = R->lt_own.as <uint32_t>(); A.own_all = R->lt_own_all.as <uint32_t>();
+		A.out_lb = R->tr_lb.as <uint32_t>(); A.out_rb = R->tr_rb.as <uint64_t>(); A.out_max = R->tr_max.as <uint32_t>(); A.out_size = R->tr_size.as <uint32_t>();
+		cudaError_t e = launch_ltrace_tables(A, ctx->stream);
+		if (cudaErrorNotSupported == e) { cudaGetLastError(); R->trace_replicated = true; }
+		else
+		{
+			CK(e);
+			if (cudaSuccess != R->comm->all_gather(R->lt_xport.p, R->lt_xport_all.p, xs * 8, ctx->stream))
+				return fail(ctx, FSQ_ERR_CUDA, "exchange of the traceback exports failed: %s", R->comm->error.c_str());
+			CK(launch_ltrace_resolve(A, ctx->stream));
+			if (cudaSuccess != R->comm->all_gather(R->lt_own.p, R->lt_own_all.p, (size_t) A.rows_bound * 20, ctx->stream))
+				return fail(ctx, FSQ_ERR_CUDA, "exchange of the traceback parts failed: %s", R->comm->error.c_str());
+			CK(launch_ltrace_scatter(A, ctx->stream));
+			ctx->stats["kernel_launches"] += 3;
+			pt.stop();
+			return FSQ_OK;
+		}
+	}
+	if ((rc = run_gather_tables(R))) return rc;
 	trace_args TA;
 	memset(&TA, 0, sizeof TA);
 	TA.tb_lb = R->tb_lb(); TA.tb_max = R->tb_max(); TA.tb_size = R->tb_size();
 	TA.L = (uint32_t) R->L; TA.dp_size = (uint32_t) R->dp_size;
 	TA.levels = 1;
 	while ((1ull << TA.levels) <= R->dp_size / R->L + 1) ++TA.levels;
+	if (!R->jump.p) CK(R->jump.alloc(ctx, (size_t) TA.levels * R->dp_size * 4));
 	TA.jump = R->jump.as <uint32_t>(); TA.ctl = R->control();
 	TA.t_bound = R->t_bound;
 	TA.out_lb = R->tr_lb.as <uint32_t>(); TA.out_rb = R->tr_rb.as <uint64_t>(); TA.out_max = R->tr_max.as <uint32_t>(); TA.out_size = R->tr_size.as <uint32_t>();
@@ -1237,8 +1318,7 @@ int run_enqueue_state_gather(fsq_run *R, uint32_t bound)
 	CK(R->red_a.alloc(ctx, (size_t) std::max <uint32_t>(bound, 1) * m * 4)); CK(R->red_d.alloc(ctx, (size_t) std::max <uint32_t>(bound, 1) * m * 4));
 	if (0 == bound) return FSQ_OK;
 	phase pc(ctx, "pass_c");
-	dim3 const grid(bound, (m + 255) / 256);
-	gather_stored_states_kernel <<<grid, 256, 0, ctx->stream>>>(R->states.as <uint32_t>(), R->state_stride, R->red_rb.as <uint64_t>(), R->control(), m, R->S.g.C, R->c0,
+	gather_stored_states_kernel <<<bound, 256, 0, ctx->stream>>>(R->states.as <uint32_t>(), R->state_stride, R->red_rb.as <uint64_t>(), R->control(), m, R->S.g.C, R->c0,
 		R->S.oldvals.as <uint32_t>(), R->S.R.as <uint32_t>(), R->red_a.as <uint32_t>(), R->red_d.as <uint32_t>());
 	CK(cudaGetLastError());
 	pc.stop();
@@ -1537,6 +1617,17 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 		if (whole && (rc = run_enqueue_reduce(R, 0))) return rc;       // harmless when K == m turns out below
 		if ((rc = run_read_control(R))) return rc;
 	}
+	if (R->h[I_TRACE_ERR])
+	{
+		// a jump longer than the window of entries the ranks export to one another: the traceback over the whole table instead
+		R->trace_replicated = true;
+		ctx->stats["trace_fallbacks"] += 1;
+		CK(cudaMemsetAsync(R->control() + I_TRACE_ERR, 0, 4, ctx->stream));
+		if ((rc = run_enqueue_traceback(R))) return rc;
+		if (whole && (rc = run_enqueue_reduce(R, 0))) return rc;
+		if ((rc = run_read_control(R))) return rc;
+		tail_done = false;
+	}
 	seg->T = R->h[I_T];
 	seg->K = R->h[I_K];
 	if (ctx->opt("keep_dp", 0))
@@ -1714,7 +1805,7 @@ int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
 		}
 		return FSQ_OK;
 	}
-	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", "whole_waves", "mem_limit", "window_blocks", "halo", nullptr};
+	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", "whole_waves", "mem_limit", "window_blocks", "halo", "trace_window", nullptr};
 	for (char const **k = known; *k; ++k)
 		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }
 	return fail(ctx, FSQ_ERR_ARG, "unknown option '%s'", key);
@@ -1874,6 +1965,44 @@ int fsq_msa_set_first_column(fsq_msa *msa, uint64_t first_column)
 
 uint32_t fsq_msa_rows(const fsq_msa *msa) { return msa ? msa->m : 0; }
 uint64_t fsq_msa_columns(const fsq_msa *msa) { return msa ? msa->n : 0; }
+
+// ---- identity columns (remove-identity-columns/main.cc:107-160) --------------------------------------------------------
+
+int fsq_identity_columns(fsq_ctx *ctx, const fsq_msa *msa, uint8_t *identity, uint64_t *n_identity, fsq_msa **without)
+{
+	int rc = check_shape(ctx, msa);
+	if (rc) return rc;
+	if (!identity && !n_identity && !without) return fail(ctx, FSQ_ERR_ARG, "nothing asked for");
+	CK(cudaSetDevice(ctx->device));
+	uint64_t const n = msa->n;
+	dbuf d_id, d_off, d_total;
+	uint32_t const n_blocks = (uint32_t) ((n + 1023) / 1024);
+	CK(d_id.alloc(ctx, n)); CK(d_off.alloc(ctx, (size_t) n_blocks * 4)); CK(d_total.alloc(ctx, 8));
+	phase pi(ctx, "identity_columns");
+	CK(launch_identity_columns(msa->cols, msa->col_stride, msa->m, n, d_id.as <uint8_t>(), ctx->stream));
+	CK(launch_kept_offsets(d_id.as <uint8_t>(), n, d_off.as <uint32_t>(), d_total.as <uint64_t>(), ctx->stream));
+	ctx->stats["kernel_launches"] += 3;
+	uint64_t kept = 0;
+	CK(cudaMemcpyAsync(&kept, d_total.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+	if (identity) CK(cudaMemcpyAsync(identity, d_id.p, n, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	if (n_identity) *n_identity = n - kept;
+	if (without)
+	{
+		*without = nullptr;
+		if (0 == kept) { pi.stop(); return fail(ctx, FSQ_ERR_ARG, "every column is an identity column: nothing is left"); }
+		fsq_msa *out = nullptr;
+		if ((rc = new_msa(ctx, msa->m, kept, 0, msa->nsym, &out))) return rc;
+		out->sym_mask = msa->sym_mask;
+		cudaError_t e = launch_compact_columns(msa->cols, msa->col_stride, n, d_id.as <uint8_t>(), d_off.as <uint32_t>(), out->cols, ctx->stream);
+		if (cudaSuccess == e) e = cudaStreamSynchronize(ctx->stream);
+		if (cudaSuccess != e) { fsq_msa_free(out); return fail(ctx, FSQ_ERR_CUDA, "column compaction: %s", cudaGetErrorString(e)); }
+		ctx->stats["kernel_launches"] += 1;
+		*without = out;
+	}
+	pi.stop();
+	return FSQ_OK;
+}
 
 // ---- PBWT states ---------------------------------------------------------------------------------------------------
 

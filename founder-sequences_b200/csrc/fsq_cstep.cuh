@@ -87,6 +87,50 @@ __device__ __forceinline__ uint32_t prmt_7632(uint32_t a, uint32_t b)
 	return r;
 }
 
+// ---- paired formulation (FSQ_STEP_HALF2): two symbols per instruction in the halves of f16x2 operations --------------
+// A divergence code c < 0x7C00 read as the bit pattern of a half is a finite non-negative number, and the order of such
+// patterns as halves is their order as integers (subnormals included: none of the instructions below flushes them), so
+// max, compare-equal and multiplication by 1.0 / 0.0 work on the codes as they stand.  The running maxima of symbols
+// (2p, 2p + 1) share a register; per element and pair: one HSET2 (one-hot, 1.0 / 0.0 per half), one HMNMX2, two HFMA2 --
+// twelve instructions for up to six symbols where the scalar form takes four per symbol.
+// (FSQ_STEP_HALF2, FSQ_PAD_CODE, FSQ_CODE_LIMIT: fsq_internal.h)
+
+__device__ __forceinline__ uint32_t h2_set_eq(uint32_t a, uint32_t b)
+{
+	uint32_t r;
+	asm("set.eq.f16x2.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+	return r;
+}
+
+__device__ __forceinline__ uint32_t h2_max(uint32_t a, uint32_t b)
+{
+	uint32_t r;
+	asm("max.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+	return r;
+}
+
+__device__ __forceinline__ uint32_t h2_fma(uint32_t a, uint32_t b, uint32_t c)
+{
+	uint32_t r;
+	asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+	return r;
+}
+
+// c - a b
+__device__ __forceinline__ uint32_t h2_fnma(uint32_t a, uint32_t b, uint32_t c)
+{
+	uint32_t r;
+	asm("{\n.reg .b32 t;\nneg.f16x2 t, %1;\nfma.rn.f16x2 %0, t, %2, %3;\n}" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+	return r;
+}
+
+__device__ __forceinline__ uint32_t h2_add(uint32_t a, uint32_t b)
+{
+	uint32_t r;
+	asm("add.rn.f16x2 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b));
+	return r;
+}
+
 struct cstep_shared
 {
 	uint32_t st;        // shared-window byte address of the packed state [T E]
@@ -220,9 +264,11 @@ __device__ __forceinline__ void column_step_chunked(
 
 	// ---- phase 1: walk the chunk -------------------------------------------------------------------------------
 	chunk_counters <NS> cnt;
+#if !FSQ_STEP_HALF2
 	float rm[NS];
 #pragma unroll
 	for (int c = 0; c < NS; ++c) rm[c] = 0.0f;
+#endif
 
 	// The chunk's words first, then their symbols, each as one batch of independent loads: the loads are volatile asm and
 	// keep their program order, so interleaving them with the arithmetic (load word, load symbol, compute, next element)
@@ -236,6 +282,59 @@ __device__ __forceinline__ void column_step_chunked(
 	// neighbour): one test per HG elements instead of a branch per element.
 	constexpr int HG = 3;
 	uint32_t chg = 0, h_old[HG], h_new[HG];
+#if FSQ_STEP_HALF2
+	constexpr int NP2 = (NS + 1) / 2;
+	uint32_t rm2[NP2];
+#pragma unroll
+	for (int p = 0; p < NP2; ++p) rm2[p] = 0u;
+#pragma unroll
+	for (int j = 0; j < E; ++j)
+	{
+		uint32_t const w = wd[j];
+		uint32_t const u = mt[j];
+		uint32_t const dd = __byte_perm(w, w, 0x3232);               // the code in both halves
+		uint32_t const uu = __byte_perm(u, 0u, 0x0404);              // u << 8 in both halves: distinct finite halves for distinct symbols
+		uint32_t const lr = cnt.bump(u);
+		uint32_t out2 = 0u;
+#pragma unroll
+		for (int p = 0; p < NP2; ++p)
+		{
+			// symbols 2 p and 2 p + 1; a pair's second half without a symbol compares against a byte no symbol has
+			uint32_t const want = ((uint32_t) (6 * (2 * p)) << 8) | ((2 * p + 1 < NS ? (uint32_t) (6 * (2 * p + 1)) : 0x7bu) << 24);
+			uint32_t const oh = h2_set_eq(uu, want);
+			uint32_t const nm = h2_max(rm2[p], dd);
+			out2 = h2_fma(nm, oh, out2);
+			rm2[p] = h2_fnma(nm, oh, nm);
+		}
+		// exactly one half of out2 holds the element's new code, the other is +0
+		uint32_t const ob = h2_add(out2, __byte_perm(out2, out2, 0x1032));
+		wd[j] = __byte_perm(w, ob, 0x5410);
+		mt[j] = lr * 256u + u;
+		if (HIST)
+		{
+			h_old[j % HG] = dd;
+			chg |= dd ^ ob;
+			if (HG - 1 == j % HG || E - 1 == j)
+			{
+				if (chg)
+				{
+					// (the new codes are read back from the words just built: no registers held for them)
+#pragma unroll
+					for (int i = 0; i <= j % HG; ++i)
+					{
+						uint32_t const nw = wd[j - j % HG + i] >> 16, od = h_old[i] & 0xffffu;
+						if (nw != od)
+						{
+							reds_add(H + 4u * nw, 1u);
+							reds_add(H + 4u * od, 0xffffffffu);
+						}
+					}
+				}
+				chg = 0;
+			}
+		}
+	}
+#else
 #pragma unroll
 	for (int j = 0; j < E; ++j)
 	{
@@ -279,6 +378,7 @@ __device__ __forceinline__ void column_step_chunked(
 			}
 		}
 	}
+#endif
 
 	// ---- chunk summaries across the warp (and the CTA) ----------------------------------------------------------
 	uint32_t n[NS], af[NS];
@@ -287,7 +387,11 @@ __device__ __forceinline__ void column_step_chunked(
 		for (int c = 0; c < NS; ++c)
 		{
 			n[c] = cnt.field(c);
+#if FSQ_STEP_HALF2
+			af[c] = (c & 1) ? (rm2[c / 2] >> 16) : (rm2[c / 2] & 0xffffu);    // 0 when nothing was seen
+#else
 			af[c] = __float_as_uint(fmaxf(rm[c], 8388608.0f)) & 0xffffu;      // 0 when nothing was seen
+#endif
 		}
 	}
 	uint32_t ex[NS], tot[NS], pv[NS], wkey[NS], nohas;

@@ -719,6 +719,157 @@ cudaError_t launch_trace_gather(trace_args const &A, cudaStream_t st)
 }
 
 
+// ---- traceback over column shards ---------------------------------------------------------------------------------------
+// Row i of the own tables is entry own_first + i; the last row is the final entry when this rank owns it.
+__device__ __forceinline__ uint32_t ltrace_row(ltrace_args const &A, uint32_t t)
+{
+	return (A.has_final && t == A.dp_size - 1) ? A.own_n - 1 : t - A.own_first;
+}
+
+__device__ __forceinline__ uint32_t ltrace_entry(ltrace_args const &A, uint32_t row)
+{
+	return (A.has_final && row == A.own_n - 1) ? A.dp_size - 1 : A.own_first + row;
+}
+
+__device__ __forceinline__ bool ltrace_own(ltrace_args const &A, uint32_t t)
+{
+	return TRACE_END != t && t >= A.own_first && (t < A.own_last || (A.has_final && t == A.dp_size - 1));
+}
+
+__global__ void __launch_bounds__(256) ltrace_tables_coop_kernel(ltrace_args const A)
+{
+	cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+	uint32_t const stride = gridDim.x * blockDim.x, first = blockIdx.x * blockDim.x + threadIdx.x;
+	for (uint32_t i = first; i < A.own_n; i += stride)
+	{
+		uint32_t const lb = A.tb_lb[ltrace_entry(A, i)];
+		A.jump[i] = lb ? lb - A.L : TRACE_END;
+		A.hops[i] = 1;
+	}
+	for (uint32_t k = 1; k < A.levels; ++k)
+	{
+		grid.sync();
+		uint32_t const *pj = A.jump + (size_t) (k - 1) * A.own_n, *ph = A.hops + (size_t) (k - 1) * A.own_n;
+		uint32_t *cj = A.jump + (size_t) k * A.own_n, *ch = A.hops + (size_t) k * A.own_n;
+		for (uint32_t i = first; i < A.own_n; i += stride)
+		{
+			uint32_t const j = pj[i];
+			if (ltrace_own(A, j)) { uint32_t const r = ltrace_row(A, j); cj[i] = pj[r]; ch[i] = ph[i] + ph[r]; }
+			else { cj[i] = j; ch[i] = ph[i]; }
+		}
+	}
+	grid.sync();
+	// exports: where a path that enters at one of the last `window` entries leaves this rank, and how many entries it has here
+	uint32_t const *tj = A.jump + (size_t) (A.levels - 1) * A.own_n, *th = A.hops + (size_t) (A.levels - 1) * A.own_n;
+	uint32_t const own_cols = A.own_last - A.own_first;
+	for (uint32_t i = first; i < A.window + 2; i += stride)
+	{
+		uint2 x = make_uint2(TRACE_END, 0);
+		if (i < A.window) { if (i < own_cols) { uint32_t const r = own_cols - 1 - i; x = make_uint2(tj[r], th[r]); } }
+		else if (i == A.window) { if (A.has_final) x = make_uint2(tj[A.own_n - 1], th[A.own_n - 1]); }
+		else if (A.has_final) x = make_uint2(A.tb_max[A.dp_size - 1], A.ctl[F_REACH]);
+		A.xport[i] = x;
+	}
+}
+
+cudaError_t launch_ltrace_tables(ltrace_args const &A, cudaStream_t st)
+{
+	cudaError_t err = cudaSuccess;
+	if (launch_cooperative(ltrace_tables_coop_kernel, A, 256, std::max <uint64_t>(A.own_n, A.window + 2), st, &err)) return err;
+	return cudaErrorNotSupported;
+}
+
+// One thread walks the chain of exports (every rank does, and arrives at the same answer); then the rank's own part of the
+// path is listed by all threads: the s-th entry before the one the path enters at is a binary descent through the tables.
+constexpr uint32_t LTRACE_MAX_RANKS = 256;
+
+__global__ void __launch_bounds__(256) ltrace_resolve_kernel(ltrace_args const A)
+{
+	__shared__ uint32_t s_first[LTRACE_MAX_RANKS + 1], s_enter[LTRACE_MAX_RANKS];
+	__shared__ uint32_t s_bad;
+	if (0 == threadIdx.x)
+	{
+		size_t const xs = (size_t) A.window + 2;
+		for (uint32_t q = 0; q < A.size; ++q) { s_enter[q] = TRACE_END; s_first[q] = 0; }
+		uint32_t const last = A.size - 1;
+		uint2 const fin = A.xport_all[last * xs + A.window];
+		uint2 const kk = A.xport_all[last * xs + A.window + 1];
+		s_enter[last] = A.dp_size - 1;
+		s_first[last] = fin.y;                      // counts for now; turned into offsets below
+		uint32_t cur = fin.x;
+		bool bad = false;
+		while (TRACE_END != cur)
+		{
+			uint64_t const col = (uint64_t) cur + A.L - 1;
+			uint32_t const q = (uint32_t) min((uint64_t) last, col / A.n_per);
+			// rank q's per-column entries end at min(n_entries, (q + 1) n_per + 1 - L)
+			uint64_t const hi = (uint64_t) (q + 1) * A.n_per + 1 > A.L ? (uint64_t) (q + 1) * A.n_per + 1 - A.L : 0;
+			uint32_t const q_last = (uint32_t) min((uint64_t) (A.dp_size - A.L), hi);      // n_entries = dp_size - L
+			if (cur >= q_last || q_last - 1 - cur >= A.window) { bad = true; break; }
+			uint2 const x = A.xport_all[q * xs + (q_last - 1 - cur)];
+			s_enter[q] = cur;
+			s_first[q] = x.y;
+			cur = x.x;
+		}
+		uint32_t sum = 0;
+		for (uint32_t q = 0; q < A.size; ++q) { uint32_t const c = s_first[q]; s_first[q] = sum; sum += c; }
+		s_first[A.size] = sum;
+		if (sum > A.t_bound) bad = true;
+		s_bad = bad ? 1u : 0u;
+		if (0 == blockIdx.x)
+		{
+			for (uint32_t q = 0; q <= A.size; ++q) A.pos_first_all[q] = bad ? 0u : s_first[q];
+			for (uint32_t q = 0; q < A.size; ++q) A.entry_all[q] = s_enter[q];
+			A.ctl[I_T] = bad ? 0u : sum;
+			A.ctl[I_K] = kk.x;
+			A.ctl[I_POS_FIRST] = bad ? 0u : s_first[A.rank];
+			A.ctl[I_POS_LAST] = bad ? 0u : s_first[A.rank + 1];
+			if (bad) A.ctl[I_TRACE_ERR] = 1;
+		}
+	}
+	__syncthreads();
+	uint32_t const count = s_bad ? 0u : min(s_first[A.rank + 1] - s_first[A.rank], A.rows_bound);
+	uint32_t const enter = s_enter[A.rank];
+	for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < count; s += gridDim.x * blockDim.x)
+	{
+		uint32_t row = ltrace_row(A, enter);
+		for (uint32_t k = 0; k < A.levels; ++k)
+			if ((s >> k) & 1u) row = ltrace_row(A, A.jump[(size_t) k * A.own_n + row]);
+		uint32_t const t = ltrace_entry(A, row);
+		uint32_t *o = A.own + (size_t) (count - 1 - s) * 5;
+		uint64_t const rb = (uint64_t) t + A.L;
+		o[0] = (uint32_t) rb; o[1] = (uint32_t) (rb >> 32);
+		o[2] = A.tb_lb[t]; o[3] = A.tb_max[t]; o[4] = A.tb_size[t];
+	}
+}
+
+cudaError_t launch_ltrace_resolve(ltrace_args const &A, cudaStream_t st)
+{
+	uint32_t const grid = std::max <uint32_t>(1, std::min <uint32_t>(1024, (A.rows_bound + 255) / 256));
+	ltrace_resolve_kernel <<<grid, 256, 0, st>>>(A);
+	return cudaGetLastError();
+}
+
+__global__ void ltrace_scatter_kernel(ltrace_args const A)
+{
+	uint32_t const q = blockIdx.y;
+	uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t const first = A.pos_first_all[q], last = A.pos_first_all[q + 1];
+	if (i >= A.rows_bound || first + i >= last || first + i >= A.t_bound) return;
+	uint32_t const *o = A.own_all + ((size_t) q * A.rows_bound + i) * 5;
+	A.out_rb[first + i] = (uint64_t) o[0] | ((uint64_t) o[1] << 32);
+	A.out_lb[first + i] = o[2];
+	A.out_max[first + i] = o[3];
+	A.out_size[first + i] = o[4];
+}
+
+cudaError_t launch_ltrace_scatter(ltrace_args const &A, cudaStream_t st)
+{
+	ltrace_scatter_kernel <<<dim3((A.rows_bound + 255) / 256, A.size), 256, 0, st>>>(A);
+	return cudaGetLastError();
+}
+
+
 // ---- greedy reduction (reference: segmentation_lp_context.cc:335-390; pbwt.hh:206-216) ------------------------------
 // The reference merges traceback segments while #{d_rb > cur_lb} <= K.  That count is the number of distinct rows over
 // [cur_lb, rb), which cannot decrease as rb grows, so the run merged from a given start is a function of the start

@@ -8,7 +8,16 @@
 #define FSQ_MAX_SYMS 16            // 4-bit packed symbols
 #endif
 
+// The chunked column step (fsq_cstep.cuh) in its paired form: divergence codes take part in f16x2 arithmetic as bit
+// patterns, so they stay below the first non-finite half (0x7C00).
+#ifndef FSQ_STEP_HALF2
+#define FSQ_STEP_HALF2 1
+#endif
+
 namespace fsq {
+
+constexpr uint32_t FSQ_PAD_CODE = FSQ_STEP_HALF2 ? 0x7bffu : 0xffffu;      // the largest code; padding rows carry it
+constexpr uint32_t FSQ_CODE_LIMIT = FSQ_STEP_HALF2 ? 0x7bfeu : 0xfffeu;    // codes in use stay below it (chunked step)
 
 enum { MODE_LOCAL = 0, MODE_EXACT = 1, MODE_DUMP = 2 };
 
@@ -25,6 +34,7 @@ struct block_args
 	uint32_t cg;               // columns per TMA stage
 	uint32_t first_block;
 	uint32_t magic;            // 0x4B000000, passed as an argument so that the step's PRMT reads it from the constant bank
+	uint32_t digits;           // chunked step: 1, or 2 = a column is two steps over the base-4 digits of its symbols (alphabets of 9 .. 16 comps)
 	int mode;
 
 	// start states (MODE_EXACT, MODE_DUMP)
@@ -64,7 +74,7 @@ inline size_t cblock_smem_bytes(block_args const &A, uint32_t T, uint32_t E, uin
 	size_t t = 0;
 	t += r16(2 * (size_t) A.cg * A.col_stride);
 	t += r16(2 * sizeof(uint64_t));
-	t += r16((size_t) A.cg * ((words + 15) & ~size_t(15)));
+	t += r16((size_t) A.cg * (A.digits > 1 ? 2 : 1) * ((words + 15) & ~size_t(15)));
 	t += r16(sizeof(uint32_t) * words);
 	t += r16(sizeof(uint32_t) * (size_t) T * ((((6 * (NS - 1)) & ~3u) / 4 + 1) | 1));      // cstep_nsp(NS), fsq_cstep.cuh
 	t += r16(sizeof(uint32_t) * n_warps * 2 * NS);
@@ -125,7 +135,8 @@ enum
 	I_SEG_FIRST = 11, I_SEG_LAST = 12,      // reduced segments whose state this rank holds
 	I_POS_FIRST = 13, I_POS_LAST = 14,      // traceback positions whose right bound lies in this rank's columns
 	I_HALO_ERR = 15,    // the greedy reduction ran past the rows it had of the ranks after this one
-	N_CONTROL = 16
+	I_TRACE_ERR = 16,   // column shards: the path entered a rank below the entries it had exported (a jump longer than the window)
+	N_CONTROL = 20
 };
 
 struct dp_args
@@ -180,6 +191,39 @@ struct trace_args
 cudaError_t launch_trace_tables(trace_args const &A, cudaStream_t st);     // jump tables + count + K
 cudaError_t launch_trace_gather(trace_args const &A, cudaStream_t st);     // the path in text order + this rank's positions
 
+// The same for column shards, without anyone holding the whole table: every rank builds jump tables over its own entries
+// only (a jump that leaves them is an exit: the entry of some rank before), exports (exit, entries on the path) for the
+// entries a path can enter it at -- the last `window` ones, a jump being no longer than the DP's farthest look-back --
+// and after one all-gather of those exports resolves the chain last rank -> ... -> first: where the path enters each
+// rank and how many of its entries lie there.  Each rank then lists its own part of the path.
+struct ltrace_args
+{
+	uint32_t const *tb_lb, *tb_max, *tb_size;      // the table (entry t at [t]); only own entries are read
+	uint32_t L, dp_size, levels;
+	uint32_t own_first, own_last;                  // own per-column entries [own_first, own_last)
+	uint32_t has_final;                            // this rank also owns entry dp_size - 1
+	uint32_t own_n;                                // own_last - own_first + has_final: rows of the tables (the final entry is the last row)
+	uint32_t *jump, *hops;                         // [levels][own_n]
+	uint32_t window;                               // entries exported per rank
+	uint2 *xport;                                  // [window + 2] own export: (exit, count) of entry own_last - 1 - i at [i]; [window] the final entry's;
+	                                               // [window + 1] = (K, farthest look-back) from the rank with the final entry
+	uint2 const *xport_all;                        // [size][window + 2] gathered
+	uint32_t rank, size;
+	uint64_t n_per;
+	uint32_t *ctl;                                 // I_T, I_K, I_POS_FIRST, I_POS_LAST written; I_TRACE_ERR raised when a path enters a rank below its window
+	uint32_t *pos_first_all;                       // [size + 1] first traceback position of every rank
+	uint32_t *entry_all;                           // [size] the entry at which the path enters each rank (~0: it does not)
+	uint32_t rows_bound;
+	uint32_t *own;                                 // [rows_bound][5] this rank's part of the path in text order: rb (2 words), lb, max, size
+	uint32_t const *own_all;                       // [size][rows_bound][5] gathered
+	uint32_t t_bound;
+	uint32_t *out_lb, *out_max, *out_size;         // [t_bound] the whole path in text order
+	uint64_t *out_rb;
+};
+cudaError_t launch_ltrace_tables(ltrace_args const &A, cudaStream_t st);      // own tables + export
+cudaError_t launch_ltrace_resolve(ltrace_args const &A, cudaStream_t st);     // chain over the gathered exports + own part of the path
+cudaError_t launch_ltrace_scatter(ltrace_args const &A, cudaStream_t st);     // gathered parts -> the whole path
+
 // Greedy reduction (fsq_dp.cu).  The counts #{d_rb > lb} it needs come from one row per traceback position: either
 // `width` entries (v, #{d > v}) of the column's top list with #{d > v} <= K, v descending, padded with (~0, ~0)
 // (rows are `width` uint2), or the divergence array itself (rows are m uint32).  A rank holds the rows of its own
@@ -229,6 +273,10 @@ cudaError_t launch_pair_weights(uint32_t const *cls_l, uint32_t const *cls_r, ui
 
 // ---- pack / synth ----------------------------------------------------------------------------------------------
 cudaError_t launch_pack(uint8_t const *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint8_t const *d_comp, uint8_t *cols, uint64_t col_stride, uint64_t col_first, uint32_t *sym_mask, cudaStream_t st);
+// identity columns (remove-identity-columns/main.cc:107-160) and the alignment without them
+cudaError_t launch_identity_columns(uint8_t const *cols, uint64_t col_stride, uint32_t m, uint64_t n, uint8_t *identity, cudaStream_t st);
+cudaError_t launch_kept_offsets(uint8_t const *identity, uint64_t n, uint32_t *block_off, uint64_t *total, cudaStream_t st);
+cudaError_t launch_compact_columns(uint8_t const *cols, uint64_t col_stride, uint64_t n, uint8_t const *identity, uint32_t const *block_off, uint8_t *out, cudaStream_t st);
 cudaError_t launch_synth_packed(uint8_t *cols, uint64_t col_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps, cudaStream_t st);
 cudaError_t launch_synth_rows(uint8_t *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps, cudaStream_t st);
 

@@ -149,4 +149,116 @@ cudaError_t launch_synth_rows(uint8_t *d_rows, uint64_t row_stride, uint32_t m, 
 	return cudaGetLastError();
 }
 
+
+// ---- identity columns (reference: remove-identity-columns/main.cc:107-160) --------------------------------------------
+// A column all of whose rows carry the same character.  On the packed, column-major alignment a column is col_stride
+// contiguous bytes: one warp compares every nibble of it with the first row's.
+__global__ void identity_columns_kernel(uint8_t const *cols, uint64_t col_stride, uint32_t m, uint64_t n, uint8_t *identity)
+{
+	uint64_t const c = (uint64_t) blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	if (c >= n) return;
+	uint32_t const lane = threadIdx.x & 31u;
+	uint32_t const *col = (uint32_t const *) (cols + c * col_stride);
+	uint32_t const first = col[0] & 15u;
+	uint32_t const want = first * 0x11111111u;
+	uint32_t const full = m >> 3, rest = m & 7u;
+	bool same = true;
+	for (uint32_t w = lane; w < full; w += 32) same &= col[w] == want;
+	if (rest && 0 == lane)
+	{
+		uint32_t const mask = (1u << (4 * rest)) - 1u;
+		same &= ((col[full] ^ want) & mask) == 0;
+	}
+	same = __all_sync(FSQ_FULL, same);
+	if (0 == lane) identity[c] = same ? 1 : 0;
+}
+
+// exclusive prefix sums of (1 - identity) in three steps: per-block totals, their scan by one block, the final positions
+constexpr int SCAN_BLOCK = 1024;
+
+__global__ void __launch_bounds__(SCAN_BLOCK) kept_block_totals_kernel(uint8_t const *identity, uint64_t n, uint32_t *block_tot)
+{
+	__shared__ uint32_t wsum[32];
+	uint64_t const i = (uint64_t) blockIdx.x * SCAN_BLOCK + threadIdx.x;
+	uint32_t const v = (i < n && !identity[i]) ? 1u : 0u;
+	uint32_t const b = __ballot_sync(FSQ_FULL, v);
+	if (0 == (threadIdx.x & 31u)) wsum[threadIdx.x >> 5] = __popc(b);
+	__syncthreads();
+	if (threadIdx.x < 32)
+	{
+		uint32_t const s = __reduce_add_sync(FSQ_FULL, wsum[threadIdx.x]);
+		if (0 == threadIdx.x) block_tot[blockIdx.x] = s;
+	}
+}
+
+__global__ void __launch_bounds__(1024) scan_block_totals_kernel(uint32_t *block_tot, uint32_t n_blocks, uint64_t *total)
+{
+	__shared__ uint32_t wsum[32];
+	__shared__ uint32_t carry;
+	if (0 == threadIdx.x) carry = 0;
+	__syncthreads();
+	for (uint32_t b0 = 0; b0 < n_blocks; b0 += 1024)
+	{
+		uint32_t const b = b0 + threadIdx.x;
+		uint32_t const v = b < n_blocks ? block_tot[b] : 0u;
+		uint32_t const inc = warp_incl_sum(v);
+		if (31 == (threadIdx.x & 31u)) wsum[threadIdx.x >> 5] = inc;
+		__syncthreads();
+		uint32_t before = carry;
+		for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) before += wsum[w];
+		if (b < n_blocks) block_tot[b] = before + inc - v;
+		__syncthreads();
+		if (1023 == threadIdx.x) carry = before + inc;
+		__syncthreads();
+	}
+	if (0 == threadIdx.x) *total = carry;
+}
+
+// the kept columns move to their new places: one CTA copies the columns of one scan block
+__global__ void __launch_bounds__(SCAN_BLOCK) compact_columns_kernel(uint8_t const *cols, uint64_t col_stride, uint64_t n, uint8_t const *identity, uint32_t const *block_off, uint8_t *out)
+{
+	__shared__ uint32_t wsum[32];
+	__shared__ uint32_t dst_of[SCAN_BLOCK];
+	uint64_t const i = (uint64_t) blockIdx.x * SCAN_BLOCK + threadIdx.x;
+	uint32_t const v = (i < n && !identity[i]) ? 1u : 0u;
+	uint32_t const lane = threadIdx.x & 31u;
+	uint32_t const b = __ballot_sync(FSQ_FULL, v);
+	if (0 == lane) wsum[threadIdx.x >> 5] = __popc(b);
+	__syncthreads();
+	uint32_t before = block_off[blockIdx.x];
+	for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) before += wsum[w];
+	dst_of[threadIdx.x] = v ? before + __popc(b & ((1u << lane) - 1u)) : 0xffffffffu;
+	__syncthreads();
+	uint32_t const words = (uint32_t) (col_stride / 16);
+	for (uint32_t c = threadIdx.x >> 5; c < SCAN_BLOCK; c += SCAN_BLOCK / 32)
+	{
+		uint32_t const d = dst_of[c];
+		if (0xffffffffu == d) continue;
+		uint4 const *src = (uint4 const *) (cols + ((uint64_t) blockIdx.x * SCAN_BLOCK + c) * col_stride);
+		uint4 *dst = (uint4 *) (out + (uint64_t) d * col_stride);
+		for (uint32_t w = lane; w < words; w += 32) dst[w] = src[w];
+	}
+}
+
+cudaError_t launch_identity_columns(uint8_t const *cols, uint64_t col_stride, uint32_t m, uint64_t n, uint8_t *identity, cudaStream_t st)
+{
+	identity_columns_kernel <<<(unsigned) ((n + 7) / 8), 256, 0, st>>>(cols, col_stride, m, n, identity);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_kept_offsets(uint8_t const *identity, uint64_t n, uint32_t *block_off, uint64_t *total, cudaStream_t st)
+{
+	uint32_t const n_blocks = (uint32_t) ((n + SCAN_BLOCK - 1) / SCAN_BLOCK);
+	kept_block_totals_kernel <<<n_blocks, SCAN_BLOCK, 0, st>>>(identity, n, block_off);
+	scan_block_totals_kernel <<<1, 1024, 0, st>>>(block_off, n_blocks, total);
+	return cudaGetLastError();
+}
+
+cudaError_t launch_compact_columns(uint8_t const *cols, uint64_t col_stride, uint64_t n, uint8_t const *identity, uint32_t const *block_off, uint8_t *out, cudaStream_t st)
+{
+	uint32_t const n_blocks = (uint32_t) ((n + SCAN_BLOCK - 1) / SCAN_BLOCK);
+	compact_columns_kernel <<<n_blocks, SCAN_BLOCK, 0, st>>>(cols, col_stride, n, identity, block_off, out);
+	return cudaGetLastError();
+}
+
 } // namespace fsq

@@ -52,7 +52,8 @@ const char *fsq_version(void);
  * "kernel", "chunk", "warps", "stitch_sort", "stitch_group" (kernel selection, used by the parity tests), "mem_limit"
  * (plan device memory as if this many bytes were available), "window_blocks" (scan blocks per window of top lists:
  * the exact scan and the DP then alternate over windows that share one list buffer), "halo" (rows of the ranks behind
- * it that a rank's greedy reduction starts with). */
+ * it that a rank's greedy reduction starts with), "trace_window" (entries per rank exported as places where the traceback
+ * path may enter it; a longer jump falls back to the traceback over the gathered table). */
 int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value);
 int fsq_get_stat(const fsq_ctx *ctx, const char *key, double *value);   /* e.g. "ms_pack", "ms_pass_a", "ms_dp", "kernel_launches" */
 
@@ -74,6 +75,13 @@ int fsq_msa_from_device_rows(fsq_ctx *ctx, const uint8_t *d_rows, uint64_t row_s
 int fsq_msa_synth(fsq_ctx *ctx, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps, fsq_msa **out);
 /* The same cells as ASCII rows (row-major m × n) into a device buffer, for end-to-end runs that start from host rows. */
 int fsq_synth_rows_device(fsq_ctx *ctx, uint8_t *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint64_t col0, uint64_t seed, uint32_t founders, int gaps);
+
+/* Replaces the column test of remove_identity_columns (remove-identity-columns/main.cc:107-160), the pre-processing tool
+ * that drops the columns in which every row carries the same character: identity[i] = 1 for such a column i (n bytes, host;
+ * may be NULL), *n_identity their number (may be NULL), and -- when `without` is given -- the alignment that is left, in
+ * HBM, ready for fsq_segment (FSQ_ERR_ARG when nothing is left).  The tool's other half, re-inserting the columns into the
+ * founders (insert-identity-columns), is host text processing driven by the same 0/1 mask. */
+int fsq_identity_columns(fsq_ctx *ctx, const fsq_msa *msa, uint8_t *identity, uint64_t *n_identity, fsq_msa **without);
 
 /* Must run before fsq_destroy() of the context that made the alignment: packed alignments of up to 4 GB return to the
  * context's buffer cache (reused by the next upload on that context, released by fsq_destroy or when memory runs short). */

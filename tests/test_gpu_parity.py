@@ -348,3 +348,76 @@ def test_memory_limit_turns_into_windows(ctx, oracle, synth):
     ctx.reset_stats()
     compare_segmentation(ctx, oracle, rows, 10, block_columns=100, sets=False)
     assert ctx.stat("windows") > 1
+
+
+@pytest.mark.parametrize("m,n", [(5, 37), (64, 5000), (1000, 4100), (2500, 1025)])
+def test_identity_columns(ctx, oracle, synth, m, n):
+    """remove-identity-columns/main.cc:107-160: a column is dropped when the set of its characters has one element; the
+    alignment that is left must scan exactly like the rows with those columns cut out on the host."""
+    rows = synth.synth_rows(m, n, seed=m * 7 + n, founders=3, gaps=True, mu=2e-4)
+    rows[:, n // 3: n // 3 + 40] = rows[0, n // 3: n // 3 + 40]          # a run of identity columns for sure
+    want = (rows == rows[0]).all(axis=0).astype(np.uint8)
+    comp = np.zeros(256, np.uint8)
+    for i, ch in enumerate(sorted(set(rows.tobytes()) | {0})):
+        comp[ch] = i
+    with ctx.msa_from_rows(rows, comp) as msa:
+        mask, reduced = ctx.identity_columns(msa, want_msa=True)
+        assert np.array_equal(mask, want) and 0 < want.sum() < n
+        kept = np.ascontiguousarray(rows[:, want == 0])
+        assert reduced.n == kept.shape[1]
+        cols = np.unique(np.linspace(1, kept.shape[1], 7).astype(np.uint64))
+        a, d = ctx.pbwt_states(reduced, cols)
+        with ctx.msa_from_rows(kept, comp) as direct:
+            a2, d2 = ctx.pbwt_states(direct, cols)
+        reduced.free()
+    assert np.array_equal(a, a2) and np.array_equal(d, d2)
+    with oracle.open(kept) as o:
+        oa, od = o.scan_dump(int(cols[-1]), hist=False)[:2]
+    for i, c in enumerate(cols):
+        assert np.array_equal(a[i], oa[int(c) - 1]) and np.array_equal(d[i], od[int(c) - 1])
+
+
+def mosaic_rows(m, n, letters, seed, founders=8, block=150, mu=2e-3):
+    """A founder mosaic over an arbitrary alphabet (the stock generator knows ACGT and '-')."""
+    rng = np.random.default_rng(seed)
+    al = np.frombuffer(letters, np.uint8)
+    f = al[rng.integers(0, len(al), size=(founders, n))]
+    rows = np.empty((m, n), np.uint8)
+    for r in range(m):
+        starts = np.arange(0, n, block)
+        pick = rng.integers(0, founders, size=len(starts))
+        for s, p in zip(starts, pick):
+            rows[r, s:s + block] = f[p, s:s + block]
+    mut = rng.random((m, n)) < mu
+    rows[mut] = al[rng.integers(0, len(al), size=int(mut.sum()))]
+    return rows
+
+
+@pytest.mark.parametrize("m,n,L,letters", [
+    (40, 1500, 6, b"ACGTNRYKM"),                       # 9 comps + NUL
+    (1000, 3000, 15, b"ACGTNRYKMSWB"),                # 12
+    (1000, 2500, 12, b"-ACGTNRYKMSWBDH"),             # 15: the most the 4-bit packing holds
+    (2500, 1200, 20, b"ACGTacgtNn-"),                 # lower case and N: FASTA as it comes
+])
+def test_wide_alphabets(ctx, oracle, m, n, L, letters):
+    """Alphabets of 9 .. 15 characters run on the chunked scan as two steps per column over the base-4 digits of the
+    comps (consecutive_alphabet.hh:259-264 gives any byte a comp; DNA with IUPAC codes or lower case needs more than
+    eight)."""
+    rows = mosaic_rows(m, n, letters, seed=m + len(letters))
+    ctx.reset_stats()
+    with ctx.msa_from_rows(rows) as msa:
+        cols = np.unique(np.linspace(1, n, 9).astype(np.uint64))
+        a, d = ctx.pbwt_states(msa, cols)
+    with oracle.open(rows) as o:
+        oa, od = o.scan_dump(n, hist=False)[:2]
+    for i, c in enumerate(cols):
+        assert np.array_equal(a[i], oa[int(c) - 1]) and np.array_equal(d[i], od[int(c) - 1]), int(c)
+    compare_segmentation(ctx, oracle, rows, L)
+    assert ctx.stat("kernel") == 3        # the chunked step, not the striped fallback
+
+
+def test_alphabet_of_more_than_15_characters_is_refused(ctx):
+    rows = np.frombuffer(bytes(range(65, 65 + 16)) * 4, np.uint8).reshape(4, 16).copy()
+    with pytest.raises(Exception) as e:
+        ctx.msa_from_rows(rows)
+    assert e.value.code == 1 and "15 distinct characters" in str(e.value)

@@ -161,3 +161,15 @@ def test_sharded_under_torchrun_nccl():
     from sharded_torchrun import CASES
     assert r.stdout.count("sharded ok:") == len(CASES), r.stdout[-3000:]
     assert "sharded all ok %d" % len(CASES) in r.stdout, r.stdout[-3000:]
+
+
+def test_sharded_traceback_fallback_when_jumps_outgrow_the_window(fsq, oracle, synth):
+    """The ranks trace the path through their own entries and export only the last `trace_window` of them as places where
+    it can enter; a window of one entry is outgrown at once, and the run falls back to the traceback over the whole
+    (gathered) table."""
+    rows = synth.synth_rows(80, 2000, seed=33, founders=6, gaps=True)
+    lib = fsq.load_library()
+    res = run_sharded(fsq, rows, 9, 4, {"block_columns": 90, "trace_window": 1})
+    check_against_oracle(oracle, rows, 9, res)
+    res = run_sharded(fsq, rows, 9, 4, {"block_columns": 90})
+    check_against_oracle(oracle, rows, 9, res)
