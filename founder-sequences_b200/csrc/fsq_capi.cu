@@ -1042,6 +1042,8 @@ int run_enqueue_round(fsq_run *R, uint32_t round_no, size_t w_begin, size_t w_en
 		if (rescan && (rc = run_scan_window(R, w))) return rc;
 		phase pd(ctx, "dp");
 		if (1 == round_no) { D.bound_on_device = 0; D.reach_bound = 0; }
+		D.round_no = round_no;
+		D.chain_base = 1 == R->size ? D.t_first / D.chunk : 0;
 		if (D.t_first < D.t_last) chains += (D.t_last - 1) / D.chunk - D.t_first / D.chunk + 1;
 		CK(launch_dp_chains(D, ctx->stream));
 		pd.stop();
@@ -1473,15 +1475,17 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 	bool tail_done = false;
 	uint32_t resume_block = 0;            // one rank, windows: everything before this block's first entry is final
 	uint32_t total_rounds = 0;
-	auto grow_cap = [&](uint32_t proven) -> int {
+	auto grow_cap = [&]() -> int {
 		if (R->cap >= m) return fail(ctx, FSQ_ERR_INTERNAL, "DP reported an incomplete top list with cap = m");
-		// Every value computed under the short lists is an upper bound of the true one, so lists that reach as far as the
-		// largest of them are proven to suffice (a quarter more: slack, and what later windows may need) -- but where no
-		// candidate at all was within the lists that bound is the whole-range value, close to m, and says little: the bound
-		// at most doubles per retry (127 -> 255 -> 511 -> 1023: config 3 settles at 1023 where its prefixes peak near 700,
-		// and lists four times as long as needed cost more in every later call than one more retry does in the first).
+		// The lists double.  Every value computed under lists that are too short is an upper bound of the true one, so lists
+		// that reach as far as the largest of them (F_OVERFLOW) are proven to suffice -- but that bound is loose (one entry
+		// without a good candidate in its list inflates everything computed from it; measured on config 3: 4,095 where 1,023
+		// does), so it only serves when it is the smaller of the two.  A retry is cheap: the chains that are final already
+		// (F_SURE) report a short list after the first rounds, before the rest of the table has settled.
 		uint64_t const entries = (uint64_t) R->cap + 1;
-		uint64_t next = std::max <uint64_t>(entries + 1, std::min <uint64_t>(2 * entries, (uint64_t) proven + proven / 4 + 8));
+		uint64_t next = 2 * entries;
+		if (R->h[F_OVERFLOW] && !R->h[F_BLIND]) next = std::min <uint64_t>(next, (uint64_t) R->h[F_OVERFLOW] + R->h[F_OVERFLOW] / 8 + 8);
+		next = std::max <uint64_t>(next, entries + 1);
 		next = (next + 7) & ~7ull;
 		R->cap = (uint32_t) std::min <uint64_t>(m, next - 1);
 		ctx->stats["cap_retries"] += 1;
@@ -1489,6 +1493,7 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 		R->rows.release();
 		return FSQ_OK;
 	};
+	auto lists_too_short = [&]() { return 0 != R->h[F_OVERFLOW] || 0 != R->h[F_BLIND]; };
 
 	while (true)
 	{
@@ -1517,6 +1522,7 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 				if ((rc = run_read_control(R))) return rc;
 				if (R->h[F_WINDOW_ERR] && R->size > 1 && 0xffffffffu != R->back_bound) { R->back_bound = 0xffffffffu; restart = true; break; }
 				if (R->h[F_DONE]) { tail_done = with_tail; break; }
+				if (R->h[F_SURE] && lists_too_short()) break;          // chains that are final already ran out of list: no point in settling the rest
 				if (rounds >= (uint32_t) max_rounds)
 				{
 					// the guesses keep failing: the chains one after the other, exact in a single pass
@@ -1558,6 +1564,7 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 					if ((rc = run_read_control(R))) return rc;
 					if (R->h[F_WINDOW_ERR] && 0xffffffffu != R->back_bound) { R->back_bound = 0xffffffffu; rounds = 0; CK(cudaMemsetAsync(R->control(), 0, 8 * 4, ctx->stream)); continue; }
 					if (R->h[F_DONE]) break;
+					if (R->h[F_SURE] && lists_too_short()) break;
 					if (rounds >= (uint32_t) max_rounds)
 					{
 						// the guesses keep failing: this window's entries as one chain behind the final ones
@@ -1581,16 +1588,16 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 					batch = std::min <uint32_t>(8, rounds);
 				}
 				total_rounds += rounds;
-				if (R->h[F_OVERFLOW]) { overflow = true; resume_block = w.b0; }
+				if (lists_too_short()) { overflow = true; resume_block = w.b0; }
 			}
 			if (overflow)
 			{
-				if ((rc = grow_cap(R->h[F_OVERFLOW]))) return rc;
+				if ((rc = grow_cap())) return rc;
 				continue;
 			}
 		}
-		if (0 == R->h[F_OVERFLOW]) break;
-		if ((rc = grow_cap(R->h[F_OVERFLOW]))) return rc;
+		if (!lists_too_short()) break;
+		if ((rc = grow_cap())) return rc;
 		resume_block = 0;
 	}
 	ctx->learned_cap[std::make_tuple(R->m, R->n, R->L)] = R->cap;      // later calls on this shape start from the bound that worked

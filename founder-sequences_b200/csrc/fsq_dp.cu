@@ -136,7 +136,7 @@ __device__ __forceinline__ list_head load_list_head(dp_args const &A, uint64_t k
 // S: once S exceeds the best value so far nothing later can win or tie.
 // Returns (in every lane) the entry's max; lb and size through the references.
 template <typename V>
-__device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list_head const &h, uint64_t const k, uint64_t const t_out, uint32_t &reach, uint32_t &lowest, uint32_t &lb_out, uint32_t &size_out)
+__device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list_head const &h, uint64_t const k, uint64_t const t_out, uint32_t &reach, uint32_t &lowest, uint32_t &lb_out, uint32_t &size_out, bool const sure = false)
 {
 	uint32_t const lane = lane_id();
 	uint32_t const L = (uint32_t) A.L;
@@ -203,7 +203,13 @@ __device__ __forceinline__ uint32_t dp_column(dp_args const &A, V const &v, list
 	// worth more than cap), and so is everything computed from it: lists that reach as far as the largest such value
 	// prove the whole table.
 	if (0 == lane && !complete && mx > A.cap)
-		atomicMax(&A.flags[F_OVERFLOW], mx);
+	{
+		// ... unless the list did not reach a single admissible candidate (all of it lies within the last L columns): then
+		// the value is the whole-range one and says nothing about how long the lists need to be
+		if (0xffffffffu == best) atomicAdd(&A.flags[F_BLIND], 1u);
+		else atomicMax(&A.flags[F_OVERFLOW], mx);
+		if (sure) A.flags[F_SURE] = 1;
+	}
 	lb_out = lb; size_out = sz;
 	return mx;
 }
@@ -294,7 +300,7 @@ __global__ void __launch_bounds__(512, FSQ_DP_MIN_CTAS) dp_chain_kernel(dp_args 
 		if (t < t1)
 		{
 			uint32_t lb = 0, sz = 0;
-			uint32_t const mx = dp_column(A, v, cur, (uint64_t) t + L - 1, t, reach, lowest, lb, sz);
+			uint32_t const mx = dp_column(A, v, cur, (uint64_t) t + L - 1, t, reach, lowest, lb, sz, c >= A.chain_base && c - A.chain_base < A.round_no);
 			if (0 == lane)
 			{
 				A.tb_max[t] = mx;
@@ -373,7 +379,7 @@ __global__ void dp_final_kernel(dp_args const A)
 	v.Mg = A.tb_max; v.mkg = A.mk; v.levg = A.lev; v.n_blk = A.n_blk;
 	uint64_t const t = A.n - A.L;
 	list_head const h = load_list_head(A, A.n - 1);
-	uint32_t const mx = dp_column(A, v, h, A.n - 1, t, reach, lowest, lb, sz);
+	uint32_t const mx = dp_column(A, v, h, A.n - 1, t, reach, lowest, lb, sz, 0 != A.flags[F_DONE]);
 	if (0 == lane_id())
 	{
 		A.tb_max[t] = mx;
@@ -530,31 +536,37 @@ __global__ void dp_round_end_kernel(uint32_t *flags, uint32_t first_round, uint3
 	send[0] = cont ? 1u : 0u;
 	send[1] = flags[F_OVERFLOW];
 	send[2] = flags[F_REACH];
-	send[3] = 0;
+	send[3] = min(flags[F_BLIND], 0x7fffffffu) | (flags[F_SURE] ? 0x80000000u : 0u);
 }
 
 __global__ void dp_round_merge_kernel(uint32_t *flags, uint32_t const *gathered, uint32_t size, uint32_t round_no, uint32_t back_bound, uint32_t one_chain)
 {
 	if (flags[F_DONE]) return;
-	uint32_t cont = 0, ovf = 0, reach = 0;
+	uint32_t cont = 0, ovf = 0, reach = 0, blind = 0, sure = 0;
 	for (uint32_t r = 0; r < size; ++r)
 	{
 		cont |= gathered[4 * r];
 		ovf = max(ovf, gathered[4 * r + 1]);
 		reach = max(reach, gathered[4 * r + 2]);
+		blind = max(blind, gathered[4 * r + 3] & 0x7fffffffu);
+		sure |= gathered[4 * r + 3] >> 31;
 	}
 	flags[F_REACH] = reach;
 	flags[F_ROUNDS] = round_no;
+	if (sure) flags[F_SURE] = 1;
 	if (2 * (uint64_t) reach + 128 > back_bound) flags[F_WINDOW_ERR] = 1;
 	// (one chain over everything is the reference's own order: exact as it stands)
 	if ((round_no > 1 && !cont) || one_chain)
 	{
 		flags[F_DONE] = 1;
 		flags[F_OVERFLOW] = ovf;         // of the round that found the fixed point: its values are final
+		flags[F_BLIND] = blind;
 		return;
 	}
 	// a table that is still moving says nothing about the lists: values computed from guesses may exceed the final ones
-	flags[F_OVERFLOW] = 0;
+	// (what the chains that are final already found out stays in F_SURE)
+	if (!sure) { flags[F_OVERFLOW] = 0; flags[F_BLIND] = 0; }
+	else { flags[F_OVERFLOW] = ovf; flags[F_BLIND] = blind; }
 	flags[F_CHANGED] = 0;
 	flags[F_UNSETTLED] = 0;
 }
@@ -562,9 +574,14 @@ __global__ void dp_round_merge_kernel(uint32_t *flags, uint32_t const *gathered,
 // after the last entry: whether any rank's lists were too short
 __global__ void dp_overflow_merge_kernel(uint32_t *flags, uint32_t const *gathered, uint32_t size)
 {
-	uint32_t ovf = flags[F_OVERFLOW];
-	for (uint32_t r = 0; r < size; ++r) ovf = max(ovf, gathered[4 * r + 1]);
+	uint32_t ovf = flags[F_OVERFLOW], blind = flags[F_BLIND];
+	for (uint32_t r = 0; r < size; ++r)
+	{
+		ovf = max(ovf, gathered[4 * r + 1]);
+		blind = max(blind, gathered[4 * r + 3] & 0x7fffffffu);
+	}
 	flags[F_OVERFLOW] = ovf;
+	flags[F_BLIND] = blind;
 }
 
 cudaError_t launch_dp_overflow_merge(uint32_t *flags, uint32_t const *gathered, uint32_t size, cudaStream_t st)

@@ -136,6 +136,8 @@ enum
 	I_POS_FIRST = 13, I_POS_LAST = 14,      // traceback positions whose right bound lies in this rank's columns
 	I_HALO_ERR = 15,    // the greedy reduction ran past the rows it had of the ranks after this one
 	I_TRACE_ERR = 16,   // column shards: the path entered a rank below the entries it had exported (a jump longer than the window)
+	F_BLIND = 17,       // entries whose top list was too short to hold a single admissible candidate: nothing is known of them but "> cap"
+	F_SURE = 18,        // a list proved too short in a chain whose entries are final already (chain c is exact from round c + 1 on)
 	N_CONTROL = 20
 };
 
@@ -160,6 +162,8 @@ struct dp_args
 	uint32_t reach_bound;       // the look-back known when the round starts (0 in the first round)
 	uint32_t bound_on_device;   // take the bound from flags[F_BOUND] instead (see dp_chain_kernel)
 	uint32_t skip_when_done;    // return at once when flags[F_DONE] is set
+	uint32_t round_no;          // 1-based; chains chain_base .. chain_base + round_no - 1 (global index) compute final values:
+	uint32_t chain_base;        // everything before chain chain_base is final when the rounds start
 	uint32_t w_first, w_last;   // masks and rmq cells are rebuilt for entries [w_first, w_last) (w_first a multiple of 64)
 	uint32_t lvl_first, lvl_last;   // the guess levels entries [lvl_first, lvl_last) (chains on the global grid of `chunk` entries)
 };
@@ -168,7 +172,7 @@ cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st);       // every 
 cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st);        // between rounds: level the table, rebuild masks and rmq tables
 cudaError_t launch_dp_final(dp_args const &A, cudaStream_t st);        // the last column (entry n - L)
 cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st);      // masks and rmq tables from the table as it stands
-// End of a round on one rank: send[0..3] = {another round is needed, F_OVERFLOW, F_REACH, 0}.
+// End of a round on one rank: send[0..3] = {another round is needed, F_OVERFLOW, F_REACH, F_BLIND | F_SURE << 31}.
 cudaError_t launch_dp_round_end(uint32_t *flags, uint32_t first_round, uint32_t *send, cudaStream_t st);
 // ... and with every rank's words at hand (gathered[size][4]): the merged decision into flags; clears the per-round words.
 cudaError_t launch_dp_round_merge(uint32_t *flags, uint32_t const *gathered, uint32_t size, uint32_t round_no, uint32_t back_bound, uint32_t one_chain, cudaStream_t st);
