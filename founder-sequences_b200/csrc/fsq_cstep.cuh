@@ -131,6 +131,20 @@ __device__ __forceinline__ uint32_t h2_add(uint32_t a, uint32_t b)
 	return r;
 }
 
+// One count moves from the old code's histogram cell to the new one's for each of up to three elements (old codes in
+// the low halves of o*, new ones in the high halves of the rebuilt words w*; equal codes: nothing to do).
+static __device__ __noinline__ void hist_moves(uint32_t H, uint32_t o0, uint32_t w0, uint32_t o1, uint32_t w1, uint32_t o2, uint32_t w2)
+{
+	uint32_t const od[3] = {o0 & 0xffffu, o1 & 0xffffu, o2 & 0xffffu}, nw[3] = {w0 >> 16, w1 >> 16, w2 >> 16};
+#pragma unroll
+	for (int i = 0; i < 3; ++i)
+		if (nw[i] != od[i])
+		{
+			reds_add(H + 4u * nw[i], 1u);
+			reds_add(H + 4u * od[i], 0xffffffffu);
+		}
+}
+
 struct cstep_shared
 {
 	uint32_t st;        // shared-window byte address of the packed state [T E]
@@ -318,17 +332,10 @@ __device__ __forceinline__ void column_step_chunked(
 			{
 				if (chg)
 				{
-					// (the new codes are read back from the words just built: no registers held for them)
-#pragma unroll
-					for (int i = 0; i <= j % HG; ++i)
-					{
-						uint32_t const nw = wd[j - j % HG + i] >> 16, od = h_old[i] & 0xffffu;
-						if (nw != od)
-						{
-							reds_add(H + 4u * nw, 1u);
-							reds_add(H + 4u * od, 0xffffffffu);
-						}
-					}
+					// rare, and out of line: eleven inlined copies of it were a tenth of the loop body, which is fetched from
+					// beyond the instruction cache as it is (the new codes are read back from the words just built)
+					hist_moves(H, h_old[0], wd[j - j % HG], j % HG >= 1 ? h_old[1] : 0u, j % HG >= 1 ? wd[j - j % HG + 1] : 0u,
+						j % HG >= 2 ? h_old[2] : 0u, j % HG >= 2 ? wd[j - j % HG + 2] : 0u);
 				}
 				chg = 0;
 			}
