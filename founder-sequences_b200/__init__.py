@@ -30,7 +30,7 @@ EXPORTS = [
     "fsq_msa_rows", "fsq_msa_columns", "fsq_identity_columns", "fsq_pbwt_states", "fsq_segment", "fsq_segmentation_free",
     "fsq_segmentation_count", "fsq_segmentation_max_segment_size", "fsq_segmentation_bounds",
     "fsq_segmentation_states", "fsq_segmentation_states_view", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
-    "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights",
+    "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights", "fsq_pair_counts",
     "fsq_msa_set_first_column", "fsq_shard_columns", "fsq_comm_unique_id", "fsq_comm_create", "fsq_comm_adopt_nccl",
     "fsq_local_group_create", "fsq_local_group_free", "fsq_comm_create_local", "fsq_comm_free", "fsq_comm_rank", "fsq_comm_size",
     "fsq_segment_sharded", "fsq_segmentation_own_range",
@@ -92,6 +92,7 @@ def load_library():
     proto("fsq_distinct_rows", ci, [vp, vp, vp, vp, C.POINTER(u32)])
     proto("fsq_segment_sets", ci, [vp, vp, u32, vp, vp, vp, C.POINTER(u32)])
     proto("fsq_pair_weights", ci, [vp, vp, u32, vp, C.POINTER(u32), C.POINTER(u32)])
+    proto("fsq_pair_counts", ci, [vp, vp, u32, vp, vp, vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)])
     pu32, pu64 = C.POINTER(u32), C.POINTER(u64)
     proto("fsq_msa_set_first_column", ci, [vp, u64])
     proto("fsq_shard_columns", ci, [u64, ci, ci, pu64, pu64])
@@ -311,6 +312,13 @@ class Segmentation:
         runs = C.c_uint32()
         self.ctx.check(self.ctx.lib.fsq_segment_sets(self.ctx.h, self.h, s, _p(off), _p(ids), _p(cls), C.byref(runs)))
         return off[: runs.value + 1], ids, cls
+
+    def pair_counts(self, s):
+        """greedy_matcher.cc:293-343: the distinct (lhs class, rhs class) pairs of segments (s, s + 1), ascending, with counts."""
+        l, r, c = np.zeros(self.m, np.uint32), np.zeros(self.m, np.uint32), np.zeros(self.m, np.uint32)
+        n = C.c_uint32()
+        self.ctx.check(self.ctx.lib.fsq_pair_counts(self.ctx.h, self.h, s, _p(l), _p(r), _p(c), C.byref(n), None, None))
+        return l[: n.value], r[: n.value], c[: n.value]
 
     def pair_weights(self, s):
         k = max(1, self.max_segment_size)

@@ -126,8 +126,11 @@ struct fsq_segmentation
 	uint32_t m{};
 	uint64_t n{}, L{};
 	uint32_t K{};
-	std::vector <uint64_t> lb, rb;            // reduced (every rank holds all of them)
+	uint32_t n_reduced{};
+	std::vector <uint64_t> lb, rb;            // reduced (every rank holds all of them); on the host once asked for (or copied for free)
 	std::vector <uint32_t> size;
+	dbuf d_lb, d_rb, d_size;                  // ... on the device: n_reduced entries each
+	bool bounds_on_host{false};
 	uint32_t own_first{}, own_last{};         // the reduced segments whose state this rank holds (all of them on one GPU)
 	dbuf red_a, red_d;                        // their states on the device, (own_last - own_first) x m
 	hbuf h_a, h_d;                            // pinned host copies, made on first request
@@ -1096,7 +1099,7 @@ int run_gather_tables(fsq_run *R)
 
 // The last entry (segmentation_lp_context.cc:165-185), on the rank that holds the last column; then every rank learns
 // whether any list was too short, and (several ranks) receives the rest of the table.
-int run_enqueue_final(fsq_run *R, bool rescan_last_window)
+int run_enqueue_final(fsq_run *R, bool rescan_last_window, bool traceback_follows = false)
 {
 	fsq_ctx *ctx = R->ctx;
 	uint32_t *ctl = R->control();
@@ -1115,6 +1118,9 @@ int run_enqueue_final(fsq_run *R, bool rescan_last_window)
 	}
 	if (R->size > 1)
 	{
+		R->tables_gathered = false;
+		// (the ranks' verdicts on their lists travel with the traceback's exports when that is enqueued right behind)
+		if (traceback_follows && !R->trace_replicated && !ctx->opt("keep_dp", 0)) return FSQ_OK;
 		uint32_t *xs = R->xflags.as <uint32_t>();
 		uint32_t *mine = xs + 4 * (size_t) R->rank;
 		CK(launch_dp_round_end(ctl, 0, mine, ctx->stream));
@@ -1189,7 +1195,7 @@ int run_enqueue_traceback(fsq_run *R)
 		A.window = (uint32_t) std::min <uint64_t>(std::max <uint64_t>(R->n_per, 1), (uint64_t) std::max <int64_t>(1, ctx->opt("trace_window", 1 << 15)));
 		A.rank = (uint32_t) R->rank; A.size = (uint32_t) R->size; A.n_per = R->n_per;
 		A.rows_bound = R->rows_bound; A.t_bound = R->t_bound;
-		size_t const xs = (size_t) A.window + 2;
+		size_t const xs = (size_t) A.window + 3;
 		if (!R->lt_jump.p)
 		{
 			CK(R->lt_jump.alloc(ctx, (size_t) A.levels * std::max <uint32_t>(A.own_n, 1) * 4)); CK(R->lt_hops.alloc(ctx, (size_t) A.levels * std::max <uint32_t>(A.own_n, 1) * 4));
@@ -1516,8 +1522,8 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 					++rounds;
 					if ((rc = run_enqueue_round(R, rounds, 0, R->windows.size(), (int64_t) rounds - 1 <= guess_rounds, rescan))) return rc;
 				}
-				if ((rc = run_enqueue_final(R, rescan))) return rc;
 				bool const with_tail = can_fast_tail && rounds <= 2;
+				if ((rc = run_enqueue_final(R, rescan, with_tail))) return rc;
 				if (with_tail && (rc = run_enqueue_fast_tail(R, true, (size_t) R->t_bound * 20 <= ((size_t) 4 << 20)))) return rc;
 				if ((rc = run_read_control(R))) return rc;
 				if (R->h[F_WINDOW_ERR] && R->size > 1 && 0xffffffffu != R->back_bound) { R->back_bound = 0xffffffffu; restart = true; break; }
@@ -1722,21 +1728,20 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 			if (own && (rc = dump_states(ctx, R->msa, R->S, cols, R->red_a.as <uint32_t>(), R->red_d.as <uint32_t>()))) return rc;
 		}
 	}
-	bool const bounds_copied = tail_done && (size_t) R->t_bound * 20 <= ((size_t) 4 << 20);
-	uint32_t const copied = bounds_copied ? R->t_bound : n_red;
-	if (!bounds_copied)
+	// The reduced bounds stay on the device with the handle and reach the host when asked for -- unless they were small
+	// enough to ride along with the control words already.
+	seg->n_reduced = n_red;
+	if (tail_done && (size_t) R->t_bound * 20 <= ((size_t) 4 << 20))
 	{
-		if ((rc = run_enqueue_bounds_copy(R, n_red))) return rc;
-		CK(cudaStreamSynchronize(ctx->stream));
-		ctx->stats["host_syncs"] += 1;
-	}
-	{
+		uint32_t const copied = R->t_bound;
 		uint64_t const *h_lb = R->h_red.as <uint64_t>(), *h_rb = h_lb + copied;
 		uint32_t const *h_sz = (uint32_t const *) (h_rb + copied);
 		seg->lb.assign(h_lb, h_lb + n_red);
 		seg->rb.assign(h_rb, h_rb + n_red);
 		seg->size.assign(h_sz, h_sz + n_red);
+		seg->bounds_on_host = true;
 	}
+	seg->d_lb.adopt(R->red_lb); seg->d_rb.adopt(R->red_rb); seg->d_size.adopt(R->red_size);
 	seg->own_first = seg_first; seg->own_last = seg_last;
 	seg->red_a.adopt(R->red_a); seg->red_d.adopt(R->red_d);
 	hand_over_traceback();
@@ -2071,7 +2076,7 @@ void fsq_segmentation_free(fsq_segmentation *seg)
 	delete seg;
 }
 
-uint32_t fsq_segmentation_count(const fsq_segmentation *seg) { return seg ? (uint32_t) seg->lb.size() : 0; }
+uint32_t fsq_segmentation_count(const fsq_segmentation *seg) { return seg ? seg->n_reduced : 0; }
 uint32_t fsq_segmentation_max_segment_size(const fsq_segmentation *seg) { return seg ? seg->K : 0; }
 
 int fsq_segmentation_own_range(const fsq_segmentation *seg, uint32_t *first, uint32_t *last)
@@ -2082,9 +2087,32 @@ int fsq_segmentation_own_range(const fsq_segmentation *seg, uint32_t *first, uin
 	return FSQ_OK;
 }
 
-int fsq_segmentation_bounds(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *size)
+static int fetch_bounds(fsq_segmentation *seg)
 {
+	fsq_ctx *ctx = seg->ctx;
+	if (seg->bounds_on_host) return FSQ_OK;
+	uint32_t const n = seg->n_reduced;
+	seg->lb.resize(n); seg->rb.resize(n); seg->size.resize(n);
+	if (n)
+	{
+		CK(cudaSetDevice(ctx->device));
+		CK(cudaMemcpyAsync(seg->lb.data(), seg->d_lb.p, (size_t) n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(seg->rb.data(), seg->d_rb.p, (size_t) n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaMemcpyAsync(seg->size.data(), seg->d_size.p, (size_t) n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		CK(cudaStreamSynchronize(ctx->stream));
+	}
+	seg->bounds_on_host = true;
+	return FSQ_OK;
+}
+
+int fsq_segmentation_bounds(const fsq_segmentation *cseg, uint64_t *lb, uint64_t *rb, uint32_t *size)
+{
+	fsq_segmentation *seg = const_cast <fsq_segmentation *>(cseg);
 	if (!seg || !lb || !rb || !size) return FSQ_ERR_ARG;
+	{
+		int const rc = fetch_bounds(seg);
+		if (rc) return rc;
+	}
 	std::copy(seg->lb.begin(), seg->lb.end(), lb);
 	std::copy(seg->rb.begin(), seg->rb.end(), rb);
 	std::copy(seg->size.begin(), seg->size.end(), size);
@@ -2225,6 +2253,10 @@ int fsq_segment_sets(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, uint
 	if (!ctx || !seg || !run_off || !ids_out || !class_of_row || !n_runs) return fail(ctx, FSQ_ERR_ARG, "null argument");
 	if (s < seg->own_first || s >= seg->own_last) return fail(ctx, FSQ_ERR_ARG, "segment %u is not among the ones whose state this handle holds: [%u, %u)", s, seg->own_first, seg->own_last);
 	CK(cudaSetDevice(ctx->device));
+	{
+		int const rcb = fetch_bounds(const_cast <fsq_segmentation *>(seg));
+		if (rcb) return rcb;
+	}
 	uint32_t const m = seg->m;
 	dbuf off, ids, cls, nruns;
 	size_t const at = (size_t) (s - seg->own_first) * m;
@@ -2249,6 +2281,7 @@ int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, int3
 	uint32_t const m = seg->m;
 	dbuf off_l, ids_l, cls_l, n_l, off_r, ids_r, cls_r, n_r, dW;
 	int rc;
+	if ((rc = fetch_bounds(const_cast <fsq_segmentation *>(seg)))) return rc;
 	size_t const at = (size_t) (s - seg->own_first) * m;
 	uint32_t const *sa = seg->red_a.as <uint32_t>() + at, *sd = seg->red_d.as <uint32_t>() + at;
 	if ((rc = sets_on_device(ctx, sa, sd, m, seg->lb[s], off_l, ids_l, cls_l, n_l))) return rc;
@@ -2266,6 +2299,42 @@ int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, int3
 	CK(cudaStreamSynchronize(ctx->stream));
 	*runs_lhs = rl;
 	*runs_rhs = rr;
+	return FSQ_OK;
+}
+
+int fsq_pair_counts(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, uint32_t *lhs, uint32_t *rhs, uint32_t *count, uint32_t *n_pairs, uint32_t *runs_lhs, uint32_t *runs_rhs)
+{
+	if (!ctx || !seg || !lhs || !rhs || !count || !n_pairs) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	if (s < seg->own_first || (size_t) s + 1 >= seg->own_last) return fail(ctx, FSQ_ERR_ARG, "segment pair (%u, %u) is not among the segments whose state this handle holds: [%u, %u)", s, s + 1, seg->own_first, seg->own_last);
+	CK(cudaSetDevice(ctx->device));
+	uint32_t const m = seg->m;
+	dbuf off_l, ids_l, cls_l, n_l, off_r, ids_r, cls_r, n_r, dW, d_lhs, d_rhs, d_cnt, d_n;
+	int rc;
+	if ((rc = fetch_bounds(const_cast <fsq_segmentation *>(seg)))) return rc;
+	size_t const at = (size_t) (s - seg->own_first) * m;
+	uint32_t const *sa = seg->red_a.as <uint32_t>() + at, *sd = seg->red_d.as <uint32_t>() + at;
+	if ((rc = sets_on_device(ctx, sa, sd, m, seg->lb[s], off_l, ids_l, cls_l, n_l))) return rc;
+	if ((rc = sets_on_device(ctx, sa + m, sd + m, m, seg->lb[s + 1], off_r, ids_r, cls_r, n_r))) return rc;
+	uint32_t rl = 0, rr = 0;
+	CK(cudaMemcpyAsync(&rl, n_l.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(&rr, n_r.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	size_t const bytes = (size_t) rl * rr * 4;
+	CK(dW.alloc(ctx, bytes)); CK(d_lhs.alloc(ctx, (size_t) m * 4)); CK(d_rhs.alloc(ctx, (size_t) m * 4)); CK(d_cnt.alloc(ctx, (size_t) m * 4)); CK(d_n.alloc(ctx, 4));
+	CK(cudaMemsetAsync(dW.p, 0, bytes, ctx->stream));
+	CK(launch_pair_weights(cls_l.as <uint32_t>(), cls_r.as <uint32_t>(), m, rr, dW.as <int32_t>(), ctx->stream));
+	CK(launch_pair_counts(dW.as <int32_t>(), rl, rr, d_lhs.as <uint32_t>(), d_rhs.as <uint32_t>(), d_cnt.as <uint32_t>(), d_n.as <uint32_t>(), ctx->stream));
+	ctx->stats["kernel_launches"] += 2;
+	uint32_t np = 0;
+	CK(cudaMemcpyAsync(&np, d_n.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	CK(cudaMemcpyAsync(lhs, d_lhs.p, (size_t) np * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(rhs, d_rhs.p, (size_t) np * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(count, d_cnt.p, (size_t) np * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	*n_pairs = np;
+	if (runs_lhs) *runs_lhs = rl;
+	if (runs_rhs) *runs_rhs = rr;
 	return FSQ_OK;
 }
 

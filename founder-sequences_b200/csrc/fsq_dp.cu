@@ -779,12 +779,13 @@ __global__ void __launch_bounds__(256) ltrace_tables_coop_kernel(ltrace_args con
 	// exports: where a path that enters at one of the last `window` entries leaves this rank, and how many entries it has here
 	uint32_t const *tj = A.jump + (size_t) (A.levels - 1) * A.own_n, *th = A.hops + (size_t) (A.levels - 1) * A.own_n;
 	uint32_t const own_cols = A.own_last - A.own_first;
-	for (uint32_t i = first; i < A.window + 2; i += stride)
+	for (uint32_t i = first; i < A.window + 3; i += stride)
 	{
 		uint2 x = make_uint2(TRACE_END, 0);
 		if (i < A.window) { if (i < own_cols) { uint32_t const r = own_cols - 1 - i; x = make_uint2(tj[r], th[r]); } }
 		else if (i == A.window) { if (A.has_final) x = make_uint2(tj[A.own_n - 1], th[A.own_n - 1]); }
-		else if (A.has_final) x = make_uint2(A.tb_max[A.dp_size - 1], A.ctl[F_REACH]);
+		else if (i == A.window + 1) { if (A.has_final) x = make_uint2(A.tb_max[A.dp_size - 1], A.ctl[F_REACH]); }
+		else x = make_uint2(A.ctl[F_OVERFLOW], A.ctl[F_BLIND]);      // this rank's verdict on its lists rides along (the last entry's included)
 		A.xport[i] = x;
 	}
 }
@@ -792,7 +793,7 @@ __global__ void __launch_bounds__(256) ltrace_tables_coop_kernel(ltrace_args con
 cudaError_t launch_ltrace_tables(ltrace_args const &A, cudaStream_t st)
 {
 	cudaError_t err = cudaSuccess;
-	if (launch_cooperative(ltrace_tables_coop_kernel, A, 256, std::max <uint64_t>(A.own_n, A.window + 2), st, &err)) return err;
+	if (launch_cooperative(ltrace_tables_coop_kernel, A, 256, std::max <uint64_t>(A.own_n, A.window + 3), st, &err)) return err;
 	return cudaErrorNotSupported;
 }
 
@@ -806,7 +807,7 @@ __global__ void __launch_bounds__(256) ltrace_resolve_kernel(ltrace_args const A
 	__shared__ uint32_t s_bad;
 	if (0 == threadIdx.x)
 	{
-		size_t const xs = (size_t) A.window + 2;
+		size_t const xs = (size_t) A.window + 3;
 		for (uint32_t q = 0; q < A.size; ++q) { s_enter[q] = TRACE_END; s_first[q] = 0; }
 		uint32_t const last = A.size - 1;
 		uint2 const fin = A.xport_all[last * xs + A.window];
@@ -839,6 +840,14 @@ __global__ void __launch_bounds__(256) ltrace_resolve_kernel(ltrace_args const A
 			for (uint32_t q = 0; q < A.size; ++q) A.entry_all[q] = s_enter[q];
 			A.ctl[I_T] = bad ? 0u : sum;
 			A.ctl[I_K] = kk.x;
+			uint32_t ovf = 0, blind = 0;
+			for (uint32_t q = 0; q < A.size; ++q)
+			{
+				uint2 const v = A.xport_all[q * xs + A.window + 2];
+				ovf = max(ovf, v.x); blind = max(blind, v.y);
+			}
+			A.ctl[F_OVERFLOW] = ovf;
+			A.ctl[F_BLIND] = blind;
 			A.ctl[I_POS_FIRST] = bad ? 0u : s_first[A.rank];
 			A.ctl[I_POS_LAST] = bad ? 0u : s_first[A.rank + 1];
 			if (bad) A.ctl[I_TRACE_ERR] = 1;
@@ -1242,6 +1251,48 @@ __global__ void pair_weights_kernel(uint32_t const *cls_l, uint32_t const *cls_r
 cudaError_t launch_pair_weights(uint32_t const *cls_l, uint32_t const *cls_r, uint32_t m, uint32_t runs_r, int32_t *W, cudaStream_t st)
 {
 	pair_weights_kernel <<<(m + 255) / 256, 256, 0, st>>>(cls_l, cls_r, m, runs_r, W);
+	return cudaGetLastError();
+}
+
+
+// ---- class pairs of adjacent segments with their counts (reference: greedy_matcher.cc:293-343) --------------------------
+// The greedy matcher encodes, for every row, (class in the left segment, class in the right segment), radix-sorts the
+// codes and counts runs: the distinct pairs in ascending (lhs, rhs) order with their multiplicities.  That list is the
+// non-zero cells of the contingency table W in row-major order; one CTA streams over W and compacts them.
+__global__ void __launch_bounds__(1024) pair_counts_kernel(int32_t const *W, uint32_t runs_l, uint32_t runs_r, uint32_t *lhs, uint32_t *rhs, uint32_t *count, uint32_t *n_pairs)
+{
+	__shared__ uint32_t wsum[32];
+	__shared__ uint32_t carry;
+	if (0 == threadIdx.x) carry = 0;
+	__syncthreads();
+	uint64_t const cells = (uint64_t) runs_l * runs_r;
+	uint32_t const lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+	for (uint64_t c0 = 0; c0 < cells; c0 += 1024)
+	{
+		uint64_t const c = c0 + threadIdx.x;
+		int32_t const v = c < cells ? W[c] : 0;
+		uint32_t const b = __ballot_sync(FSQ_FULL, v > 0);
+		if (0 == lane) wsum[warp] = __popc(b);
+		__syncthreads();
+		uint32_t before = carry;
+		for (uint32_t w = 0; w < warp; ++w) before += wsum[w];
+		if (v > 0)
+		{
+			uint32_t const at = before + __popc(b & ((1u << lane) - 1u));
+			lhs[at] = (uint32_t) (c / runs_r);
+			rhs[at] = (uint32_t) (c % runs_r);
+			count[at] = (uint32_t) v;
+		}
+		__syncthreads();
+		if (1023 == threadIdx.x) carry = before + __popc(b);
+		__syncthreads();
+	}
+	if (0 == threadIdx.x) *n_pairs = carry;
+}
+
+cudaError_t launch_pair_counts(int32_t const *W, uint32_t runs_l, uint32_t runs_r, uint32_t *lhs, uint32_t *rhs, uint32_t *count, uint32_t *n_pairs, cudaStream_t st)
+{
+	pair_counts_kernel <<<1, 1024, 0, st>>>(W, runs_l, runs_r, lhs, rhs, count, n_pairs);
 	return cudaGetLastError();
 }
 

@@ -209,9 +209,9 @@ struct ltrace_args
 	uint32_t own_n;                                // own_last - own_first + has_final: rows of the tables (the final entry is the last row)
 	uint32_t *jump, *hops;                         // [levels][own_n]
 	uint32_t window;                               // entries exported per rank
-	uint2 *xport;                                  // [window + 2] own export: (exit, count) of entry own_last - 1 - i at [i]; [window] the final entry's;
-	                                               // [window + 1] = (K, farthest look-back) from the rank with the final entry
-	uint2 const *xport_all;                        // [size][window + 2] gathered
+	uint2 *xport;                                  // [window + 3] own export: (exit, count) of entry own_last - 1 - i at [i]; [window] the final entry's;
+	                                               // [window + 1] = (K, farthest look-back) from the rank with the final entry; [window + 2] = (F_OVERFLOW, F_BLIND)
+	uint2 const *xport_all;                        // [size][window + 3] gathered
 	uint32_t rank, size;
 	uint64_t n_per;
 	uint32_t *ctl;                                 // I_T, I_K, I_POS_FIRST, I_POS_LAST written; I_TRACE_ERR raised when a path enters a rank below its window
@@ -274,6 +274,8 @@ cudaError_t launch_walk(walk_args const &A, cudaStream_t st);
 
 cudaError_t launch_segment_sets(uint32_t const *a, uint32_t const *d, uint32_t m, uint64_t lb, uint32_t *run_off, uint32_t *ids, uint32_t *class_of_row, uint32_t *n_runs, cudaStream_t st);
 cudaError_t launch_pair_weights(uint32_t const *cls_l, uint32_t const *cls_r, uint32_t m, uint32_t runs_r, int32_t *W, cudaStream_t st);
+// the non-zero cells of W in row-major order: (lhs class, rhs class, count); at most min(m, runs_l runs_r) of them
+cudaError_t launch_pair_counts(int32_t const *W, uint32_t runs_l, uint32_t runs_r, uint32_t *lhs, uint32_t *rhs, uint32_t *count, uint32_t *n_pairs, cudaStream_t st);
 
 // ---- pack / synth ----------------------------------------------------------------------------------------------
 cudaError_t launch_pack(uint8_t const *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint8_t const *d_comp, uint8_t *cols, uint64_t col_stride, uint64_t col_first, uint32_t *sym_mask, cudaStream_t st);

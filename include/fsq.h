@@ -147,6 +147,14 @@ int fsq_segment_sets(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment
  * fsq_segmentation_max_segment_size()^2 ints always suffice. */
 int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment, int32_t *W, uint32_t *runs_lhs, uint32_t *runs_rhs);
 
+/* Replaces the pair counting of greedy_matcher::match (founder-sequences/greedy_matcher.cc:293-343: every row's
+ * (class in the left segment, class in the right segment) encoded, radix-sorted, runs counted) for the adjacent
+ * reduced segments (segment, segment + 1): the distinct pairs in ascending (lhs, rhs) order with their counts -- the
+ * non-zero cells of fsq_pair_weights' table in row-major order.  lhs, rhs, count: m entries each (there are at most m
+ * distinct pairs).  What the matcher does with them (index_pairs_by_count, the edge drawing, :345-437) is a short
+ * sequential loop over at most min(m, K^2) items and stays on the host. */
+int fsq_pair_counts(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment, uint32_t *lhs, uint32_t *rhs, uint32_t *count, uint32_t *n_pairs, uint32_t *runs_lhs, uint32_t *runs_rhs);
+
 /* ---- column-sharded operation (one process -- or thread -- per GPU) -----------------------------------------------
  *
  * The reference runs the path in one process (no counterpart).  Rank r of `size` holds the columns

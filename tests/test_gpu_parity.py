@@ -149,8 +149,12 @@ def compare_segmentation(ctx, oracle, rows, L, block_columns=None, cap=None, set
                     assert np.array_equal(off, ooff) and np.array_equal(ids, oids) and np.array_equal(cls, ocls)
                     if s + 1 < seg.count:
                         W = seg.pair_weights(s)
-                        noff = o.segment_sets(s + 1)[0]
+                        noff, _, ncls = o.segment_sets(s + 1)
                         assert np.array_equal(W, o.pair_weights(s, len(off) - 1, len(noff) - 1))
+                        # greedy_matcher.cc:293-343: every row's (lhs class, rhs class) encoded, sorted, runs counted
+                        code, cnt = np.unique(ocls.astype(np.uint64) * (len(noff) - 1) + ncls, return_counts=True)
+                        pl, pr, pc = seg.pair_counts(s)
+                        assert np.array_equal(pl, code // (len(noff) - 1)) and np.array_equal(pr, code % (len(noff) - 1)) and np.array_equal(pc, cnt)
             return seg.max_segment_size, len(rlb)
 
 
