@@ -30,7 +30,7 @@ EXPORTS = [
     "fsq_msa_rows", "fsq_msa_columns", "fsq_identity_columns", "fsq_pbwt_states", "fsq_segment", "fsq_segmentation_free",
     "fsq_segmentation_count", "fsq_segmentation_max_segment_size", "fsq_segmentation_bounds",
     "fsq_segmentation_states", "fsq_segmentation_states_view", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
-    "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights", "fsq_pair_counts",
+    "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights", "fsq_pair_counts", "fsq_match_founders",
     "fsq_msa_set_first_column", "fsq_shard_columns", "fsq_comm_unique_id", "fsq_comm_create", "fsq_comm_adopt_nccl",
     "fsq_local_group_create", "fsq_local_group_free", "fsq_comm_create_local", "fsq_comm_free", "fsq_comm_rank", "fsq_comm_size",
     "fsq_segment_sharded", "fsq_segmentation_own_range",
@@ -93,6 +93,7 @@ def load_library():
     proto("fsq_segment_sets", ci, [vp, vp, u32, vp, vp, vp, C.POINTER(u32)])
     proto("fsq_pair_weights", ci, [vp, vp, u32, vp, C.POINTER(u32), C.POINTER(u32)])
     proto("fsq_pair_counts", ci, [vp, vp, u32, vp, vp, vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)])
+    proto("fsq_match_founders", ci, [vp, vp, vp, u64, vp, vp, vp, vp, u64, C.POINTER(u64)])
     pu32, pu64 = C.POINTER(u32), C.POINTER(u64)
     proto("fsq_msa_set_first_column", ci, [vp, u64])
     proto("fsq_shard_columns", ci, [u64, ci, ci, pu64, pu64])
@@ -189,6 +190,17 @@ class Context:
         if want_msa:
             return mask, Msa(self, h, msa.m, msa.n - cnt.value)
         return mask
+
+    def match_founders(self, sequences, founders, min_segment_length=0):
+        """match_founder_sequences: (seq, lb, rb, founder bit sets [count, ceil(K / 32)]) for the rows of `sequences`
+        against the rows of `founders` (two alignments packed with the same comp table)."""
+        cnt = C.c_uint64()
+        self.check(self.lib.fsq_match_founders(self.h, sequences.h, founders.h, min_segment_length, None, None, None, None, 0, C.byref(cnt)))
+        n, words = cnt.value, (founders.m + 31) // 32
+        sq, lb, rb = np.zeros(n, np.uint32), np.zeros(n, np.uint64), np.zeros(n, np.uint64)
+        bits = np.zeros((n, words), np.uint32)
+        self.check(self.lib.fsq_match_founders(self.h, sequences.h, founders.h, min_segment_length, _p(sq), _p(lb), _p(rb), _p(bits), max(n, 1), C.byref(cnt)))
+        return sq, lb, rb, bits
 
     # ---- the path ----
     def pbwt_states(self, msa, columns):

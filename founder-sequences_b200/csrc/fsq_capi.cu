@@ -2338,6 +2338,48 @@ int fsq_pair_counts(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t s, uint3
 	return FSQ_OK;
 }
 
+// ---- match_founder_sequences (match-sequences-to-founders/match_founder_sequences.cc:127-214) -----------------------------
+
+int fsq_match_founders(fsq_ctx *ctx, const fsq_msa *sequences, const fsq_msa *founders, uint64_t min_segment_length,
+	uint32_t *seq_idx, uint64_t *lb, uint64_t *rb, uint32_t *founder_bits, uint64_t capacity, uint64_t *count)
+{
+	int rc = check_shape(ctx, sequences);
+	if (rc) return rc;
+	if ((rc = check_shape(ctx, founders))) return rc;
+	if (!count) return fail(ctx, FSQ_ERR_ARG, "null argument");
+	if (sequences->n != founders->n) return fail(ctx, FSQ_ERR_ARG, "sequences have %llu columns, founders %llu", (unsigned long long) sequences->n, (unsigned long long) founders->n);
+	uint32_t const K = founders->m, m = sequences->m, W = (K + 31) / 32;
+	if (K > 8192) return fail(ctx, FSQ_ERR_UNSUPPORTED, "%u founders: the matching kernel holds 8,192", K);
+	uint64_t const n = sequences->n;
+	uint32_t const nsym = std::max(sequences->nsym, founders->nsym);
+	CK(cudaSetDevice(ctx->device));
+	dbuf masks, row_count, row_off, d_seq, d_lb, d_rb, d_bits;
+	if (cudaSuccess != masks.alloc(ctx, (size_t) n * nsym * W * 4)) { cudaGetLastError(); return fail(ctx, FSQ_ERR_NOMEM, "%llu bytes of founder masks do not fit", (unsigned long long) n * nsym * W * 4); }
+	CK(row_count.alloc(ctx, (size_t) m * 8)); CK(row_off.alloc(ctx, ((size_t) m + 1) * 8));
+	phase pm(ctx, "match_founders");
+	CK(launch_founder_masks(founders->cols, founders->col_stride, K, n, nsym, W, masks.as <uint32_t>(), ctx->stream));
+	CK(launch_match_founders(sequences->cols, sequences->col_stride, m, n, masks.as <uint32_t>(), nsym, K, W, min_segment_length, 0,
+		row_count.as <uint64_t>(), row_off.as <uint64_t>(), nullptr, nullptr, nullptr, nullptr, ctx->stream));
+	uint64_t total = 0;
+	CK(cudaMemcpyAsync(&total, row_off.as <uint64_t>() + m, 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	ctx->stats["kernel_launches"] += 3;
+	*count = total;
+	if (!seq_idx || !lb || !rb || !founder_bits || capacity < total) { pm.stop(); return FSQ_OK; }       // the caller learns the size and calls again
+	CK(d_seq.alloc(ctx, (size_t) std::max <uint64_t>(total, 1) * 4)); CK(d_lb.alloc(ctx, (size_t) std::max <uint64_t>(total, 1) * 8));
+	CK(d_rb.alloc(ctx, (size_t) std::max <uint64_t>(total, 1) * 8)); CK(d_bits.alloc(ctx, (size_t) std::max <uint64_t>(total, 1) * W * 4));
+	CK(launch_match_founders(sequences->cols, sequences->col_stride, m, n, masks.as <uint32_t>(), nsym, K, W, min_segment_length, 1,
+		row_count.as <uint64_t>(), row_off.as <uint64_t>(), d_seq.as <uint32_t>(), d_lb.as <uint64_t>(), d_rb.as <uint64_t>(), d_bits.as <uint32_t>(), ctx->stream));
+	ctx->stats["kernel_launches"] += 1;
+	pm.stop();
+	CK(cudaMemcpyAsync(seq_idx, d_seq.p, (size_t) total * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(lb, d_lb.p, (size_t) total * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(rb, d_rb.p, (size_t) total * 8, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(founder_bits, d_bits.p, (size_t) total * W * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
+	return FSQ_OK;
+}
+
 // ---- column-sharded operation -------------------------------------------------------------------------------------------
 // One process (or thread) per GPU; rank r holds the columns fsq_shard_columns() names of one alignment and calls
 // fsq_segment_sharded() with its communicator.  The exchanges are all-gathers on the context's stream (fsq_comm.cu).

@@ -279,6 +279,10 @@ cudaError_t launch_pair_counts(int32_t const *W, uint32_t runs_l, uint32_t runs_
 
 // ---- pack / synth ----------------------------------------------------------------------------------------------
 cudaError_t launch_pack(uint8_t const *d_rows, uint64_t row_stride, uint32_t m, uint64_t n, uint8_t const *d_comp, uint8_t *cols, uint64_t col_stride, uint64_t col_first, uint32_t *sym_mask, cudaStream_t st);
+// match_founder_sequences (fsq_match.cu)
+cudaError_t launch_founder_masks(uint8_t const *fcols, uint64_t fstride, uint32_t K, uint64_t n, uint32_t nsym, uint32_t W, uint32_t *masks, cudaStream_t st);
+cudaError_t launch_match_founders(uint8_t const *scols, uint64_t sstride, uint32_t m, uint64_t n, uint32_t const *masks, uint32_t nsym, uint32_t K, uint32_t W, uint64_t min_len,
+	int mode, uint64_t *row_count, uint64_t *row_off, uint32_t *out_seq, uint64_t *out_lb, uint64_t *out_rb, uint32_t *out_bits, cudaStream_t st);
 // identity columns (remove-identity-columns/main.cc:107-160) and the alignment without them
 cudaError_t launch_identity_columns(uint8_t const *cols, uint64_t col_stride, uint32_t m, uint64_t n, uint8_t *identity, cudaStream_t st);
 cudaError_t launch_kept_offsets(uint8_t const *identity, uint64_t n, uint32_t *block_off, uint64_t *total, cudaStream_t st);

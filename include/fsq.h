@@ -155,6 +155,18 @@ int fsq_pair_weights(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment
  * sequential loop over at most min(m, K^2) items and stays on the host. */
 int fsq_pair_counts(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment, uint32_t *lhs, uint32_t *rhs, uint32_t *count, uint32_t *n_pairs, uint32_t *runs_lhs, uint32_t *runs_rhs);
 
+/* Replaces match_context::match_sequence_and_report of the evaluation tool match_founder_sequences
+ * (match-sequences-to-founders/match_founder_sequences.cc:127-214): every row of `sequences` is walked left to right
+ * against the rows of `founders` (both packed with the SAME char -> comp table; equal lengths), keeping the founders
+ * that agree with it since the current range began; when none is left -- or, with min_segment_length != 0, when the range
+ * has that length (:163-165) -- the range is reported with the set as it stood and the next begins.  Output: the ranges
+ * in the order the tool prints them single-threaded (by sequence, then left bound): sequence index, [lb, rb), and the
+ * founder set as ceil(K / 32) words (bit f of word f / 32).  *count receives the number of ranges; nothing is written
+ * when the arrays are NULL or `capacity` is smaller (call again with room).  What the tool writes to stderr (characters
+ * no founder has) shows here as ranges with an empty set, as on its stdout. */
+int fsq_match_founders(fsq_ctx *ctx, const fsq_msa *sequences, const fsq_msa *founders, uint64_t min_segment_length,
+	uint32_t *seq_idx, uint64_t *lb, uint64_t *rb, uint32_t *founder_bits, uint64_t capacity, uint64_t *count);
+
 /* ---- column-sharded operation (one process -- or thread -- per GPU) -----------------------------------------------
  *
  * The reference runs the path in one process (no counterpart).  Rank r of `size` holds the columns

@@ -636,3 +636,56 @@ void fsqo_rmq_queries(uint32_t const *vals, uint64_t count, uint64_t const *beg,
 	for (uint64_t q = 0; q < nq; ++q) out[q] = rmq_query(&r, beg[q], end[q]);
 	rmq_free(&r); free(tb);
 }
+
+
+/* ---- match-sequences-to-founders/match_founder_sequences.cc:127-214 (match_sequence_and_report) ----
+ * Ranges (sequence, lb, rb, founder set) in the order the reference prints them for one sequence after the other
+ * (--single-threaded); a founder set is K bits in `words` = ceil(K / 32) uint32.  Returns the number of ranges, or
+ * (uint64_t) -1 when `cap` is too small.  The reference's messages to stderr are not part of the result. */
+uint64_t fsqo_match_founders(
+	uint8_t const *seqs, uint32_t m, uint8_t const *founders, uint32_t K, uint64_t n, uint64_t min_len,
+	uint32_t *out_seq, uint64_t *out_lb, uint64_t *out_rb, uint32_t *out_bits, uint64_t cap
+)
+{
+	uint32_t const words = (K + 31) / 32;
+	uint8_t *cand = malloc(K ? K : 1), *dst = malloc(K ? K : 1);
+	uint64_t count = 0;
+	int overflow = 0;
+#define FSQO_EMIT(rb_) do { \
+		if (count < cap) { \
+			out_seq[count] = r; out_lb[count] = lb; out_rb[count] = (rb_); \
+			for (uint32_t w = 0; w < words; ++w) out_bits[count * words + w] = 0; \
+			for (uint32_t f = 0; f < K; ++f) if (cand[f]) out_bits[count * words + f / 32] |= 1u << (f % 32); \
+		} else overflow = 1; \
+		++count; } while (0)
+	for (uint32_t r = 0; r < m; ++r)
+	{
+		uint8_t const *seq = seqs + (size_t) r * n;
+		uint64_t lb = 0, n_cand = K, n_dst = 0;
+		memset(cand, 1, K);
+		for (uint64_t chr = 0; chr < n; ++chr)
+		{
+			uint8_t const c = seq[chr];
+			int recheck = (0 != min_len && min_len <= chr - lb);                 /* :163-165 */
+			if (!recheck)
+			{
+				n_dst = 0;                                                          /* compare_to_sequences, :89-108 */
+				for (uint32_t f = 0; f < K; ++f) { dst[f] = cand[f] && founders[(size_t) f * n + chr] == c; n_dst += dst[f]; }
+				if (0 == n_dst) recheck = 1;                                        /* :169-175 */
+			}
+			if (recheck)
+			{
+				FSQO_EMIT(chr);                                                     /* :181 */
+				lb = chr;                                                           /* :184-191 */
+				n_dst = 0;
+				for (uint32_t f = 0; f < K; ++f) { dst[f] = founders[(size_t) f * n + chr] == c; n_dst += dst[f]; }
+			}
+			n_cand = n_dst;                                                         /* :197-201 */
+			{ uint8_t *t = cand; cand = dst; dst = t; }
+		}
+		if (0 != n_cand) FSQO_EMIT(n);                                             /* :206-215 */
+	}
+#undef FSQO_EMIT
+	free(cand); free(dst);
+	return overflow ? (uint64_t) -1 : count;
+}

@@ -54,6 +54,8 @@ class Checker:
             f(nm, None, [_vp, _vp, _vp])
         f("short_path", _u64, [_vp, _vp, _vp])
         f("rmq_queries", None, [_vp, _u64, _vp, _vp, _u64, _vp])
+        if not is_ref:
+            f("match_founders", _u64, [_vp, _u32, _vp, _u32, _u64, _u64, _vp, _vp, _vp, _vp, _u64])
 
     def _f(self, name, restype, argtypes):
         fn = getattr(self.lib, self.p + name)
@@ -69,6 +71,22 @@ class Checker:
         out = np.zeros(len(beg), np.uint64)
         self._rmq_queries(_ptr(vals), len(vals), _ptr(beg), _ptr(end), len(beg), _ptr(out))
         return out
+
+    def match_founders(self, seqs, founders, min_len=0):
+        """match_founder_sequences.cc:127-214: (seq, lb, rb, founder bit sets [count, ceil(K / 32)])."""
+        seqs = np.ascontiguousarray(seqs, np.uint8)
+        founders = np.ascontiguousarray(founders, np.uint8)
+        m, n = seqs.shape
+        K = founders.shape[0]
+        words = (K + 31) // 32
+        cap = 1024
+        while True:
+            sq, lb, rb = np.zeros(cap, np.uint32), np.zeros(cap, np.uint64), np.zeros(cap, np.uint64)
+            bits = np.zeros((cap, words), np.uint32)
+            cnt = self._match_founders(_ptr(seqs), m, _ptr(founders), K, n, min_len, _ptr(sq), _ptr(lb), _ptr(rb), _ptr(bits), cap)
+            if cnt != 0xffffffffffffffff:
+                return sq[:cnt], lb[:cnt], rb[:cnt], bits[:cnt]
+            cap *= 8
 
     def open(self, rows):
         return Session(self, rows)

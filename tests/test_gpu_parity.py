@@ -425,3 +425,28 @@ def test_alphabet_of_more_than_15_characters_is_refused(ctx):
     with pytest.raises(Exception) as e:
         ctx.msa_from_rows(rows)
     assert e.value.code == 1 and "15 distinct characters" in str(e.value)
+
+
+@pytest.mark.parametrize("m,n,K,min_len", [(7, 300, 3, 0), (40, 2500, 9, 0), (64, 4000, 70, 0), (25, 1500, 33, 40), (12, 900, 5, 7)])
+def test_match_founders(ctx, oracle, synth, m, n, K, min_len):
+    """match_founder_sequences (match-sequences-to-founders/match_founder_sequences.cc:127-214): greedy longest match of
+    every input row against the founders; rows that carry characters no founder has produce ranges with empty sets."""
+    rng = np.random.default_rng(m * 31 + K)
+    founders = synth.synth_rows(K, n, seed=K + 3, founders=max(2, K // 2), gaps=True, recomb_block=120)
+    pick = rng.integers(0, K, size=(m, (n + 79) // 80))
+    seqs = np.empty((m, n), np.uint8)
+    for r in range(m):
+        for b in range(pick.shape[1]):
+            seqs[r, 80 * b: 80 * b + 80] = founders[pick[r, b], 80 * b: 80 * b + 80]
+    noise = rng.random((m, n)) < 0.004
+    seqs[noise] = np.frombuffer(b"ACGTN", np.uint8)[rng.integers(0, 5, size=int(noise.sum()))]      # 'N': in no founder
+    comp = np.zeros(256, np.uint8)
+    for i, ch in enumerate(sorted(set(seqs.tobytes()) | set(founders.tobytes()) | {0})):
+        comp[ch] = i
+    with ctx.msa_from_rows(seqs, comp) as ms, ctx.msa_from_rows(founders, comp) as mf:
+        got = ctx.match_founders(ms, mf, min_len)
+    want = oracle.match_founders(seqs, founders, min_len)
+    assert len(got[0]) == len(want[0]) and len(want[0]) >= m
+    for g, w in zip(got, want):
+        assert np.array_equal(g, w)
+    assert (want[3].sum(axis=1) == 0).any() or min_len        # some 'N' produced an empty set
