@@ -321,7 +321,8 @@ def sharded_parity(np, torch, dist, fsq, sharded, ctx, comm, rank, world, dev, m
                 ref[0] = (seg.max_segment_size, lb, rb, sz, crc_rows(np, a, d))
     dist.broadcast_object_list(ref, src=0)
     K, lb, rb, sz, crcs = ref[0]
-    with ctx.msa_synth(m, n, seed, founders, gaps, col0=rank * n) as msa, sharded.segment_sharded(ctx, msa, comm, rank * n, n_total, L) as seg:
+    c0, c1 = sharded.shard_columns(n_total, world, rank)
+    with ctx.msa_synth(m, c1 - c0, seed, founders, gaps, col0=c0) as msa, sharded.segment_sharded(ctx, msa, comm, c0, n_total, L) as seg:
         mlb, mrb, msz = seg.reduced_traceback()
         a, d = seg.reduced_pbwt_samples_view()
         f, l = seg.own
@@ -397,8 +398,11 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             comm.free()
             ctx = new_context()
             comm = sharded.nccl_comm(ctx, dist)
-    # every rank holds its columns of the same alignment: the generator is a pure function of (seed, row, column)
-    msa = ctx.msa_synth(m, n, seed, founders, gaps, col0=rank * n)
+    # every rank holds its columns of the same alignment (the library's split rule: equal shares rounded up to 32 columns):
+    # the generator is a pure function of (seed, row, column)
+    my0, my1 = (0, n) if world == 1 else sharded.shard_columns(n_total, world, rank)
+    my_n = my1 - my0
+    msa = ctx.msa_synth(m, my_n, seed, founders, gaps, col0=my0)
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -412,7 +416,7 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             seg = c.segment(a, L if total is None else total[1])
         else:
             cm = cm or comm
-            seg = sharded.segment_sharded(c, a, cm, rank * n if first is None else first, n_total if total is None else total[0], L if total is None else total[1])
+            seg = sharded.segment_sharded(c, a, cm, my0 if first is None else first, n_total if total is None else total[0], L if total is None else total[1])
         info = (seg.max_segment_size, seg.count)
         seg.free()
         return info
@@ -483,9 +487,9 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
     e2e = None
     e2e_cold = None
     if not args.no_e2e:
-        rows_dev = torch.empty((m, n), dtype=torch.uint8, device="cuda:%d" % dev)
-        ctx.synth_rows_device(rows_dev.data_ptr(), n, m, n, seed, founders, gaps, col0=rank * n)
-        rows_host = torch.empty((m, n), dtype=torch.uint8, pin_memory=True)
+        rows_dev = torch.empty((m, my_n), dtype=torch.uint8, device="cuda:%d" % dev)
+        ctx.synth_rows_device(rows_dev.data_ptr(), my_n, m, my_n, seed, founders, gaps, col0=my0)
+        rows_host = torch.empty((m, my_n), dtype=torch.uint8, pin_memory=True)
         rows_host.copy_(rows_dev)
         del rows_dev
         torch.cuda.synchronize(dev)
@@ -499,7 +503,7 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
                 if sharded is None:
                     seg = c.segment(mm, L)
                 else:
-                    seg = sharded.segment_sharded(c, mm, cm, rank * n, n_total, L)
+                    seg = sharded.segment_sharded(c, mm, cm, my0, n_total, L)
                 with seg:
                     lb, rb, sz = seg.reduced_traceback()
                     a, d = seg.reduced_pbwt_samples_view()
