@@ -29,7 +29,7 @@ EXPORTS = [
     "fsq_msa_from_rows", "fsq_msa_from_device_rows", "fsq_msa_synth", "fsq_synth_rows_device", "fsq_msa_free",
     "fsq_msa_rows", "fsq_msa_columns", "fsq_identity_columns", "fsq_pbwt_states", "fsq_segment", "fsq_segmentation_free",
     "fsq_segmentation_count", "fsq_segmentation_max_segment_size", "fsq_segmentation_bounds",
-    "fsq_segmentation_states", "fsq_segmentation_states_view", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
+    "fsq_segmentation_states", "fsq_segmentation_states_range", "fsq_segmentation_states_view", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
     "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights", "fsq_pair_counts", "fsq_match_founders",
     "fsq_msa_set_first_column", "fsq_shard_columns", "fsq_comm_unique_id", "fsq_comm_create", "fsq_comm_adopt_nccl",
     "fsq_local_group_create", "fsq_local_group_free", "fsq_comm_create_local", "fsq_comm_free", "fsq_comm_rank", "fsq_comm_size",
@@ -85,6 +85,7 @@ def load_library():
     proto("fsq_segmentation_max_segment_size", u32, [vp])
     proto("fsq_segmentation_bounds", ci, [vp, vp, vp, vp])
     proto("fsq_segmentation_states", ci, [vp, vp, vp])
+    proto("fsq_segmentation_states_range", ci, [vp, u32, u32, vp, vp])
     proto("fsq_segmentation_states_view", ci, [vp, pp, pp])
     proto("fsq_segmentation_traceback_count", u32, [vp])
     proto("fsq_segmentation_traceback", ci, [vp, vp, vp, vp, vp])
@@ -287,6 +288,13 @@ class Segmentation:
         a = np.zeros((cnt, self.m), np.uint32)
         d = np.zeros((cnt, self.m), np.uint32)
         self.ctx.check(self.ctx.lib.fsq_segmentation_states(self.h, _p(a), _p(d)))
+        return a, d
+
+    def reduced_pbwt_samples_range(self, first, count):
+        """States of segments [first, first + count), copied from the device on their own."""
+        a = np.zeros((count, self.m), np.uint32)
+        d = np.zeros((count, self.m), np.uint32)
+        self.ctx.check(self.ctx.lib.fsq_segmentation_states_range(self.h, first, count, _p(a), _p(d)))
         return a, d
 
     def reduced_pbwt_samples_view(self):

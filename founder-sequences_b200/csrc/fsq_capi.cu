@@ -869,7 +869,9 @@ int run_plan(fsq_run *R)
 	else
 	{
 		size_t const avail = plannable_bytes(ctx);
-		size_t const other = (size_t) nl * 64 + (size_t) R->tb_len * 32 + ((size_t) 1 << 30);
+		// beside the lists: per-column words, the tables, and -- should the lists not fit at once -- what the tail then needs
+		// (divergence and prefix rows at the own traceback positions, the reduced states)
+		size_t const other = (size_t) nl * 64 + (size_t) R->tb_len * 32 + ((size_t) 1 << 30) + (size_t) R->rows_bound * R->m * 16;
 		size_t const states = (size_t) (R->state_stride * 4 * nl);
 		int64_t const want_states = ctx->opt("store_states", -1);
 		int64_t const forced = ctx->opt("window_blocks", 0);
@@ -1669,6 +1671,7 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 	if (!tail_done && !whole)
 	{
 		// the lists are gone (windows): the divergence arrays at the own traceback positions, from a re-scan, serve instead
+		R->toplist.release();         // (back to the context's cache, which gives memory back to the device when an allocation needs it)
 		host_watch hw(ctx, "reduced_states");
 		uint32_t const cnt = pos_last - pos_first;
 		std::vector <uint64_t> cols(cnt);
@@ -2146,6 +2149,22 @@ int fsq_segmentation_states(const fsq_segmentation *cseg, uint32_t *a, uint32_t 
 	size_t const bytes = (size_t) (seg->own_last - seg->own_first) * seg->m * 4;
 	memcpy(a, seg->h_a.p, bytes);
 	memcpy(d, seg->h_d.p, bytes);
+	return FSQ_OK;
+}
+
+int fsq_segmentation_states_range(const fsq_segmentation *cseg, uint32_t first, uint32_t count, uint32_t *a, uint32_t *d)
+{
+	fsq_segmentation *seg = const_cast <fsq_segmentation *>(cseg);
+	if (!seg || !a || !d) return FSQ_ERR_ARG;
+	fsq_ctx *ctx = seg->ctx;
+	if (first < seg->own_first || (uint64_t) first + count > seg->own_last)
+		return fail(ctx, FSQ_ERR_ARG, "segments [%u, %u) are not among the ones whose state this handle holds: [%u, %u)", first, first + count, seg->own_first, seg->own_last);
+	if (0 == count) return FSQ_OK;
+	CK(cudaSetDevice(ctx->device));
+	size_t const at = (size_t) (first - seg->own_first) * seg->m, bytes = (size_t) count * seg->m * 4;
+	CK(cudaMemcpyAsync(a, seg->red_a.as <uint32_t>() + at, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaMemcpyAsync(d, seg->red_d.as <uint32_t>() + at, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+	CK(cudaStreamSynchronize(ctx->stream));
 	return FSQ_OK;
 }
 

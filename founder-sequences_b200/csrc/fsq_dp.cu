@@ -996,19 +996,52 @@ __global__ void reduce_kernel(reduce_args const A)
 	uint32_t const u = first + i;
 	if (u >= last) return;
 	uint32_t const cur_lb = (0 == u) ? 0u : (uint32_t) A.tb_rb[u - 1];
-	uint32_t prev = u, size = A.tb_size[u];
+	// The rows at hand are a prefix of the positions from `first` on: the own ones, then the first `halo` rows of every rank
+	// behind this one until a rank has more positions than that.
+	uint32_t avail = last;
+	if (A.halo_rows)
+		for (uint32_t q = A.rank + 1; q < A.size; ++q)
+		{
+			uint32_t const cnt = A.pos_first_all[q + 1] - A.pos_first_all[q];
+			avail += min(cnt, A.halo);
+			if (cnt > A.halo) break;
+		}
+	avail = min(avail, T);
+	// The count #{d_rb(t) > cur_lb} cannot decrease with t (it is the number of distinct rows over [cur_lb, rb(t))), so the
+	// last position that still merges is found by galloping and bisection: a logarithmic number of counts per start where
+	// walking the run costs its length (runs are hundreds of positions long when K is in the thousands, and with
+	// divergence rows a count reads m values).
 	bool missing = false;
-	for (uint32_t t = u + 1; t < T; ++t)
+	uint32_t lo = u, size = A.tb_size[u];             // count(lo) <= K
+	uint32_t hi = u + 1, step = 1;                    // first position not yet known to merge
+	while (hi < avail)
 	{
-		uint32_t const s = reduce_count(A, t, first, last, cur_lb, K, missing);
-		if (missing) break;
-		if (s <= K) { size = s; prev = t; }
-		else break;
+		uint32_t const s = reduce_count(A, hi, first, last, cur_lb, K, missing);
+		if (s > K) break;
+		lo = hi; size = s;
+		hi = min(avail, hi + step);
+		step <<= 1;
+		if (lo + 1 == avail) { hi = avail; break; }
 	}
+	if (hi >= avail) hi = avail;                      // everything at hand up to avail - 1 may merge: bisect (lo, avail)
+	else { /* count(hi) > K */ }
+	// invariant: count(lo) <= K; hi == avail or count(hi) > K
+	{
+		uint32_t l = lo, h = hi;                      // answer in [l, h)
+		while (l + 1 < h)
+		{
+			uint32_t const mid = l + (h - l) / 2;
+			uint32_t const s = reduce_count(A, mid, first, last, cur_lb, K, missing);
+			if (s <= K) { l = mid; size = s; } else h = mid;
+		}
+		lo = l; hi = h;
+	}
+	// the run ends at lo; that is certain when the position behind it was counted (> K) or does not exist
+	bool const ran_out = hi == avail && avail < T && lo + 1 == avail;
 	if (0 == lane)
 	{
-		A.next[i] = prev; A.next_size[i] = size;
-		if (missing) A.ctl[I_HALO_ERR] = 1;
+		A.next[i] = lo; A.next_size[i] = size;
+		if (ran_out || missing) A.ctl[I_HALO_ERR] = 1;
 	}
 }
 

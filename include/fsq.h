@@ -113,6 +113,9 @@ uint32_t fsq_segmentation_max_segment_size(const fsq_segmentation *seg);
 int fsq_segmentation_bounds(const fsq_segmentation *seg, uint64_t *lb, uint64_t *rb, uint32_t *size);
 /* reduced_pbwt_samples[i].input_permutation() / input_divergence(); count × m each */
 int fsq_segmentation_states(const fsq_segmentation *seg, uint32_t *a, uint32_t *d);
+/* A slice of them, straight from the device: the states of segments [first, first + count), count x m each (hundreds of
+ * thousands of reduced segments times thousands of rows do not have to fit the host at once). */
+int fsq_segmentation_states_range(const fsq_segmentation *seg, uint32_t first, uint32_t count, uint32_t *a, uint32_t *d);
 /* The same without the extra copy: pointers into pinned host memory owned by the handle (valid until it is freed).
  * The device->host copy happens on the first call of either function. */
 int fsq_segmentation_states_view(const fsq_segmentation *seg, const uint32_t **a, const uint32_t **d);

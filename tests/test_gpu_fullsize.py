@@ -126,3 +126,72 @@ def test_config3_one_gpu_share(ctx, oracle, synth):
 def test_config5_rows_slice(ctx, oracle, synth):
     _full_size_case(ctx, oracle, synth, 20000, 250_000, 100, 64, 5, 3000,
                     ({"dp_chunks": 37}, {"store_states": 0}))
+
+
+# ---- shapes whose reduced states do not fit the host at once: read back in slices --------------------------------------
+def _sliced_digest_and_checks(seg, m, n, L, check=True, step=40000):
+    """K, the bounds' bytes and a running digest of the states, slice by slice; with `check`, the size-independent
+    properties of _full_size_case on every slice."""
+    lb, rb, sz = seg.reduced_traceback()
+    K = seg.max_segment_size
+    if check:
+        assert K < m and len(lb) > 0
+        assert lb[0] == 0 and rb[-1] == n and np.array_equal(lb[1:], rb[:-1])
+        assert np.all(rb - lb >= L) and sz.max() <= K
+    acc = np.uint64(0)
+    ident = np.arange(m, dtype=np.uint32)
+    for f in range(0, len(lb), step):
+        c = min(step, len(lb) - f)
+        a, d = seg.reduced_pbwt_samples_range(f, c)
+        if check:
+            distinct = (d > lb[f:f + c, None].astype(np.uint32)).sum(axis=1)      # pbwt.hh:206-216
+            assert np.array_equal(distinct.astype(np.uint32), sz[f:f + c])
+            assert np.all(d[:, 0] == rb[f:f + c].astype(np.uint32))
+            assert np.array_equal(np.sort(a[0]), ident) and np.array_equal(np.sort(a[c - 1]), ident)
+        # (a cheap running digest: wrapping sums and xors of the states read as 64-bit words, chained over the slices)
+        va, vd = a.reshape(-1)[: c * m // 2 * 2].view(np.uint64), d.reshape(-1)[: c * m // 2 * 2].view(np.uint64)
+        with np.errstate(over="ignore"):
+            acc = acc * np.uint64(1000003) + va.sum() + np.bitwise_xor.reduce(va) * np.uint64(3) + vd.sum() * np.uint64(5) + np.bitwise_xor.reduce(vd) * np.uint64(7)
+    return K, lb.tobytes(), rb.tobytes(), sz.tobytes(), int(acc)
+
+
+def _large_case(ctx, oracle, synth, m, n, L, F, seed, P, variants):
+    msa = ctx.msa_synth(m, n, seed, F, True)
+    try:
+        ctx.set_option("keep_dp", 1)
+        with ctx.segment(msa, L) as seg:
+            ctx.set_option("keep_dp", 0)
+            base = _sliced_digest_and_checks(seg, m, n, L)
+            dlb, drb, dmx, dsz = seg.dp_table(n - L + 1)
+        rows = synth.synth_rows(m, P, seed=seed, founders=F, gaps=True)
+        with oracle.open(rows) as o:
+            assert o.segment(L) == 0
+            olb, orb, omx, osz = o.dp()
+            cnt = P - 2 * L + 1
+            assert np.array_equal(dlb[:cnt], olb[:cnt]) and np.array_equal(drb[:cnt], orb[:cnt])
+            assert np.array_equal(dmx[:cnt], omx[:cnt]) and np.array_equal(dsz[:cnt], osz[:cnt])
+        del dlb, drb, dmx, dsz
+        for opts in variants:
+            for k, v in opts.items():
+                ctx.set_option(k, v)
+            try:
+                with ctx.segment(msa, L) as other:
+                    assert _sliced_digest_and_checks(other, m, n, L, check=False) == base, opts
+            finally:
+                for k in opts:
+                    ctx.set_option(k, {"block_columns": 0, "dp_chunks": 0, "store_states": -1, "window_blocks": 0}[k])
+    finally:
+        ctx.set_option("keep_dp", 0)
+        msa.free()
+
+
+# Config 4 at L = 5 and 10 over the full 5M columns: 660,505 and 364,395 reduced segments (13 and 7 GB of states).
+@pytest.mark.parametrize("L", [5, 10])
+def test_config4_short_bounds_full_length(ctx, oracle, synth, L):
+    _large_case(ctx, oracle, synth, 2500, 5_000_000, L, 24, 4, 8000, ({"dp_chunks": 37},))
+
+
+# Config 3 whole on one GPU with default options (25 GB packed, 82 GB of top lists at the bound the DP settles on, states
+# by re-scan); the same bytes with the lists in windows over one buffer.
+def test_config3_whole_on_one_gpu(ctx, oracle, synth):
+    _large_case(ctx, oracle, synth, 5000, 10_000_000, 50, 32, 3, 5000, ({"window_blocks": 700},))

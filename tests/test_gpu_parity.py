@@ -109,7 +109,7 @@ def test_synth_device_matches_host(ctx, fsq, synth, oracle):
     assert np.array_equal(a1, a2) and np.array_equal(d1, d2)
 
 
-def compare_segmentation(ctx, oracle, rows, L, block_columns=None, cap=None, sets=True):
+def compare_segmentation(ctx, oracle, rows, L, block_columns=None, cap=None, sets=True, all_sets=False):
     m, n = rows.shape
     if block_columns:
         ctx.set_option("block_columns", block_columns)
@@ -143,7 +143,7 @@ def compare_segmentation(ctx, oracle, rows, L, block_columns=None, cap=None, set
             oa, od = o.reduced_states()
             assert np.array_equal(a, oa) and np.array_equal(d, od)
             if sets:
-                for s in range(min(seg.count, 6)):
+                for s in range(seg.count if all_sets else min(seg.count, 6)):
                     off, ids, cls = seg.segment_sets(s)
                     ooff, oids, ocls = o.segment_sets(s)
                     assert np.array_equal(off, ooff) and np.array_equal(ids, oids) and np.array_equal(cls, ocls)
@@ -450,3 +450,34 @@ def test_match_founders(ctx, oracle, synth, m, n, K, min_len):
     for g, w in zip(got, want):
         assert np.array_equal(g, w)
     assert (want[3].sum(axis=1) == 0).any() or min_len        # some 'N' produced an empty set
+
+
+
+@pytest.mark.parametrize("m,n,L,founders,cap", [(1500, 4000, 20, 16, None), (128, 1500, 6, 40, 2), (2500, 1500, 30, 24, 8)])
+def test_sets_weights_and_pair_counts_over_all_segments(ctx, oracle, synth, m, n, L, founders, cap):
+    """Segment sets (create_segment_texts_task.cc:15-35), edge weights (merge_segments_task.cc:133-176) and the greedy
+    matcher's pair counts (greedy_matcher.cc:293-343) for EVERY reduced segment and adjacent pair: a scan CTA of several
+    warps (1,500 and 2,500 rows) and bounds far below K that the DP has to grow."""
+    kw = dict(recomb_block=50, mu=0.01) if founders == 40 else {}
+    rows = synth.synth_rows(m, n, seed=m + L, founders=founders, gaps=True, **kw)
+    ctx.reset_stats()
+    res = compare_segmentation(ctx, oracle, rows, L, cap=cap, all_sets=True)
+    assert res is not None and res[1] > 6
+    if cap:
+        assert ctx.stat("cap_retries") >= 1
+
+
+@pytest.mark.parametrize("m,n,gaps", [(1, 9, False), (33, 64, True), (300, 199, True), (1057, 120, False), (2500, 398, True), (6000, 60, True)])
+def test_short_path_shapes(ctx, fsq, oracle, synth, m, n, gaps):
+    """n < 2L (generate_context.cc:379-390 -> segmentation_sp_context.cc:21-28): the distinct rows in PBWT order with their
+    multiplicities; one row, more rows than one warp's chunks hold, gaps, duplicates."""
+    rows = synth.synth_rows(m, n, seed=m + n, founders=max(1, min(5, m)), gaps=gaps, recomb_block=40, mu=0.002)
+    with ctx.msa_from_rows(rows) as msa:
+        with pytest.raises(fsq.FsqError) as ei:
+            ctx.segment(msa, n // 2 + 1)
+        assert ei.value.code == fsq.ERR_SHORT
+        row, ln = ctx.distinct_rows(msa)
+    with oracle.open(rows) as o:
+        orow, oln = o.short_path()
+    assert np.array_equal(row, orow) and np.array_equal(ln, oln)
+    assert ln.sum() == m and len(np.unique(rows, axis=0)) == len(row)
