@@ -481,6 +481,7 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
             "chunk": int(ctx.stat("chunk")), "dp_chains": int(ctx.stat("dp_chunks")), "dp_rounds_per_step": ctx.stat("dp_rounds") / args.steps,
             "states_kept_by_pass_b": bool(ctx.stat("store_states")), "list_windows": int(ctx.stat("windows")),
             "host_syncs_per_step": ctx.stat("host_syncs") / args.steps,
+            "host_ms_enqueueing_per_step": ctx.stat("hms_enqueue") / args.steps, "host_ms_waiting_per_step": ctx.stat("hms_wait") / args.steps,
             "first_call_ms": first_call_ms, "first_call_cap_retries": first_call_retries}
 
     # ---- end to end: host rows -> C ABI -> host results ----

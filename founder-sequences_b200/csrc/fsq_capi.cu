@@ -37,6 +37,8 @@ struct fsq_ctx
 	std::vector <std::pair <std::string, std::pair <cudaEvent_t, cudaEvent_t>>> pending;   // phase timers
 	cudaEvent_t timer_ev[2]{nullptr, nullptr};   // option "timer": 1 records the start, 0 the stop, on the context's stream ("ms_timer")
 	cudaEvent_t call_start{nullptr};       // recorded at the entry of fsq_segment: phases report their offset from it ("at_<phase>")
+	std::vector <cudaEvent_t> event_pool;  // phase timers take their events here and give them back (no create / destroy per phase)
+	cudaEvent_t take_event() { if (event_pool.empty()) { cudaEvent_t e{}; cudaEventCreate(&e); return e; } cudaEvent_t e = event_pool.back(); event_pool.pop_back(); return e; }
 
 	// what calls on a shape (m, n, L) have learned: the top-list bound that proved exact.  The option "cap" stays the caller's.
 	std::map <std::tuple <uint32_t, uint64_t, uint64_t>, uint32_t> learned_cap;
@@ -161,7 +163,7 @@ struct phase
 	fsq_ctx *ctx; std::string name; cudaEvent_t e0{}, e1{};
 	phase(fsq_ctx *c, char const *n): ctx(c), name(n)
 	{
-		cudaEventCreate(&e0); cudaEventCreate(&e1);
+		e0 = ctx->take_event(); e1 = ctx->take_event();
 		cudaEventRecord(e0, ctx->stream);
 	}
 	void stop()
@@ -193,8 +195,8 @@ void flush_phases(fsq_ctx *ctx)
 			if (cudaSuccess == cudaEventElapsedTime(&at, ctx->call_start, p.second.first)) ctx->stats["at_" + p.first] = at;
 			if (cudaSuccess == cudaEventElapsedTime(&at, ctx->call_start, p.second.second)) ctx->stats["end_" + p.first] = at;
 		}
-		cudaEventDestroy(p.second.first);
-		cudaEventDestroy(p.second.second);
+		ctx->event_pool.push_back(p.second.first);
+		ctx->event_pool.push_back(p.second.second);
 	}
 	ctx->pending.clear();
 }
@@ -693,6 +695,7 @@ struct fsq_run
 	dbuf tr_lb, tr_rb, tr_max, tr_size, jump, rows, rows_a, halo_rows, pos_all, next_own, nsize_own, next_all, nsize_all, next, nsize;
 	dbuf walk_jump, red_lb, red_rb, red_size, red_pos, red_a, red_d;
 	dbuf lt_jump, lt_hops, lt_xport, lt_xport_all, lt_entry, lt_own, lt_own_all;      // traceback over column shards
+	std::chrono::steady_clock::time_point t_mark{std::chrono::steady_clock::now()};
 	bool trace_replicated{false};       // fall back to the traceback over the whole table on every rank (needs all of it gathered)
 	bool tables_gathered{false};
 	hbuf h_ctl, h_red;
@@ -1147,7 +1150,15 @@ int run_read_control(fsq_run *R)
 {
 	fsq_ctx *ctx = R->ctx;
 	CK(cudaMemcpyAsync(R->h_ctl.p, R->ctl.p, N_CONTROL * 4, cudaMemcpyDeviceToHost, ctx->stream));
-	CK(cudaStreamSynchronize(ctx->stream));
+	{
+		// how long the host spent enqueueing since the call (or the last read) began, and how long it then waited for the
+		// device: a host that waits little is the one holding the device up
+		auto const t0 = std::chrono::steady_clock::now();
+		ctx->stats["hms_enqueue"] += std::chrono::duration <double, std::milli>(t0 - R->t_mark).count();
+		CK(cudaStreamSynchronize(ctx->stream));
+		R->t_mark = std::chrono::steady_clock::now();
+		ctx->stats["hms_wait"] += std::chrono::duration <double, std::milli>(R->t_mark - t0).count();
+	}
 	ctx->stats["host_syncs"] += 1;
 	memcpy(R->h, R->h_ctl.p, N_CONTROL * 4);
 	if (R->comm && !R->comm->error.empty()) return fail(ctx, FSQ_ERR_CUDA, "%s", R->comm->error.c_str());
@@ -1793,6 +1804,7 @@ void fsq_destroy(fsq_ctx *ctx)
 	if (!ctx) return;
 	cudaSetDevice(ctx->device);
 	flush_phases(ctx);
+	for (auto e : ctx->event_pool) cudaEventDestroy(e);
 	ctx->trim(false);
 	ctx->trim(true);
 	cudaStreamDestroy(ctx->stream);

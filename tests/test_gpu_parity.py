@@ -348,7 +348,7 @@ def test_windowed_top_lists_grow_the_bound_where_it_fails(ctx, oracle, synth):
 def test_memory_limit_turns_into_windows(ctx, oracle, synth):
     """mem_limit stands in for the device's answer: with room for the lists of a few blocks only, the plan is windows."""
     rows = synth.synth_rows(200, 4000, seed=3, founders=9, gaps=True)
-    ctx.set_option("mem_limit", (1 << 30) + 4000 * 64 + 4100 * 32 + 300 * 128 * 8)
+    ctx.set_option("mem_limit", (1 << 30) + 4000 * 64 + 4100 * 32 + 402 * 200 * 16 + 300 * 128 * 8)       # what run_plan sets aside + the lists of 300 columns
     ctx.reset_stats()
     compare_segmentation(ctx, oracle, rows, 10, block_columns=100, sets=False)
     assert ctx.stat("windows") > 1
