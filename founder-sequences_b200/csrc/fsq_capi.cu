@@ -37,6 +37,7 @@ struct fsq_ctx
 	std::vector <std::pair <std::string, std::pair <cudaEvent_t, cudaEvent_t>>> pending;   // phase timers
 	cudaEvent_t timer_ev[2]{nullptr, nullptr};   // option "timer": 1 records the start, 0 the stop, on the context's stream ("ms_timer")
 	cudaEvent_t call_start{nullptr};       // recorded at the entry of fsq_segment: phases report their offset from it ("at_<phase>")
+	size_t call_first_pending{0};         // the phase timers from here on belong to the call whose start call_start marks
 	std::vector <cudaEvent_t> event_pool;  // phase timers take their events here and give them back (no create / destroy per phase)
 	cudaEvent_t take_event() { if (event_pool.empty()) { cudaEvent_t e{}; cudaEventCreate(&e); return e; } cudaEvent_t e = event_pool.back(); event_pool.pop_back(); return e; }
 
@@ -189,7 +190,7 @@ void flush_phases(fsq_ctx *ctx)
 		cudaEventSynchronize(p.second.second);
 		cudaEventElapsedTime(&ms, p.second.first, p.second.second);
 		ctx->stats["ms_" + p.first] += ms;
-		if (ctx->call_start)
+		if (ctx->call_start && (size_t) (&p - ctx->pending.data()) >= ctx->call_first_pending)
 		{
 			float at = 0;
 			if (cudaSuccess == cudaEventElapsedTime(&at, ctx->call_start, p.second.first)) ctx->stats["at_" + p.first] = at;
@@ -199,6 +200,7 @@ void flush_phases(fsq_ctx *ctx)
 		ctx->event_pool.push_back(p.second.second);
 	}
 	ctx->pending.clear();
+	ctx->call_first_pending = 0;
 }
 
 // The geometry of one scan: warps per block (column range), tiles per warp, columns per block.
@@ -2068,7 +2070,11 @@ int fsq_segment_sharded(fsq_ctx *ctx, const fsq_msa *msa, fsq_comm *comm, uint64
 	if (n_total >= (1ull << 31)) return fail(ctx, FSQ_ERR_UNSUPPORTED, "n = %llu columns: positions are kept in 32 bits (n < 2^31)", (unsigned long long) n_total);
 	if (n_total < 2 * L) return fail(ctx, FSQ_ERR_SHORT, "n = %llu < 2L = %llu: short path", (unsigned long long) n_total, (unsigned long long) (2 * L));
 	CK(cudaSetDevice(ctx->device));
-	flush_phases(ctx);
+	// (the phase timers of earlier calls are read when somebody asks for a statistic, not here: twenty event pairs take
+	// 0.2 ms of host time during which the device would sit idle; the offsets from the call's start, "at_<phase>", are kept
+	// for the call before a read only)
+	if (ctx->pending.size() > 4096) flush_phases(ctx);
+	else ctx->call_first_pending = ctx->pending.size();
 	if (!ctx->call_start) CK(cudaEventCreate(&ctx->call_start));
 	CK(cudaEventRecord(ctx->call_start, ctx->stream));
 	fsq_run run;
