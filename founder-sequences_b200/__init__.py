@@ -30,7 +30,7 @@ EXPORTS = [
     "fsq_msa_rows", "fsq_msa_columns", "fsq_identity_columns", "fsq_pbwt_states", "fsq_segment", "fsq_segmentation_free",
     "fsq_segmentation_count", "fsq_segmentation_max_segment_size", "fsq_segmentation_bounds",
     "fsq_segmentation_states", "fsq_segmentation_states_range", "fsq_segmentation_states_view", "fsq_segmentation_traceback_count", "fsq_segmentation_traceback",
-    "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights", "fsq_pair_counts", "fsq_match_founders",
+    "fsq_segmentation_dp_table", "fsq_distinct_rows", "fsq_segment_sets", "fsq_pair_weights", "fsq_pair_counts", "fsq_pair_counts_noalloc", "fsq_match_founders",
     "fsq_msa_set_first_column", "fsq_shard_columns", "fsq_comm_unique_id", "fsq_comm_create", "fsq_comm_adopt_nccl",
     "fsq_local_group_create", "fsq_local_group_free", "fsq_comm_create_local", "fsq_comm_free", "fsq_comm_rank", "fsq_comm_size",
     "fsq_segment_sharded", "fsq_segmentation_own_range",
@@ -94,6 +94,7 @@ def load_library():
     proto("fsq_segment_sets", ci, [vp, vp, u32, vp, vp, vp, C.POINTER(u32)])
     proto("fsq_pair_weights", ci, [vp, vp, u32, vp, C.POINTER(u32), C.POINTER(u32)])
     proto("fsq_pair_counts", ci, [vp, vp, u32, vp, vp, vp, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)])
+    proto("fsq_pair_counts_noalloc", ci, [vp, vp, u32, u32, u32, vp, vp, vp, vp, vp, C.c_char_p, C.c_size_t])
     proto("fsq_match_founders", ci, [vp, vp, vp, u64, vp, vp, vp, vp, u64, C.POINTER(u64)])
     pu32, pu64 = C.POINTER(u32), C.POINTER(u64)
     proto("fsq_msa_set_first_column", ci, [vp, u64])

@@ -14,7 +14,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIBDIR = os.path.join(HERE, "lib")
 LIB = os.path.join(LIBDIR, "libfsq_b200.so")
-SOURCES = ["fsq_capi.cu", "fsq_pbwt.cu", "fsq_dp.cu", "fsq_pack.cu", "fsq_comm.cu", "fsq_match.cu",
+SOURCES = ["fsq_capi.cu", "fsq_pbwt.cu", "fsq_dp.cu", "fsq_pack.cu", "fsq_comm.cu", "fsq_match.cu", "fsq_noalloc.cu",
            "fsq_cscan_e9.cu", "fsq_cscan_e13.cu", "fsq_cscan_e17.cu", "fsq_cscan_e21.cu", "fsq_cscan_e25.cu", "fsq_cscan_e27.cu",
            "fsq_cscan_e29.cu", "fsq_cscan_e31.cu", "fsq_cscan_e33.cu", "fsq_cscan_e53.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")

@@ -170,6 +170,26 @@ int fsq_pair_counts(fsq_ctx *ctx, const fsq_segmentation *seg, uint32_t segment,
 int fsq_match_founders(fsq_ctx *ctx, const fsq_msa *sequences, const fsq_msa *founders, uint64_t min_segment_length,
 	uint32_t *seq_idx, uint64_t *lb, uint64_t *rb, uint32_t *founder_bits, uint64_t capacity, uint64_t *count);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The counting step of
+ * fsq_pair_counts on the CALLER'S device memory, with nothing allocated: the contingency table it goes through is a
+ * static device array of FSQ_PAIR_COUNTS_NOALLOC_MAX_CELLS ints (4 MiB + 256 bytes, held by every GPU that loads the
+ * library until the process ends).  On the current device, on `stream` (a cudaStream_t; NULL = the default stream),
+ * without waiting for it:
+ *   class_lhs, class_rhs [m]   device; row -> its class (run) in the left / right segment, as fsq_segment_sets'
+ *                              class_of_row gives them; values < runs_lhs / runs_rhs
+ *   lhs, rhs, count            device; min(m, runs_lhs * runs_rhs) entries each: the distinct (lhs, rhs) pairs in ascending
+ *                              order with their counts, exactly fsq_pair_counts' output
+ *   n_pairs                    device; one word: the number of pairs, 0xffffffff when a class index was out of range
+ *                              (nothing else is then written)
+ * runs_lhs * runs_rhs > FSQ_PAIR_COUNTS_NOALLOC_MAX_CELLS is refused with FSQ_ERR_UNSUPPORTED (use fsq_pair_counts).
+ * Takes no context: a message for a non-zero return goes to `error` (up to error_size bytes, may be NULL).
+ * The first call on a device looks the table's address up (cudaGetSymbolAddress): make it outside a stream capture.
+ * All calls on a device share the table, cleared at the start of each call: calls that overlap on the GPU race. */
+#define FSQ_PAIR_COUNTS_NOALLOC_MAX_CELLS (1u << 20)
+int fsq_pair_counts_noalloc(const uint32_t *class_lhs, const uint32_t *class_rhs, uint32_t m, uint32_t runs_lhs, uint32_t runs_rhs,
+	uint32_t *lhs, uint32_t *rhs, uint32_t *count, uint32_t *n_pairs, void *stream, char *error, size_t error_size);
+
 /* ---- column-sharded operation (one process -- or thread -- per GPU) -----------------------------------------------
  *
  * The reference runs the path in one process (no counterpart).  Rank r of `size` holds the columns
