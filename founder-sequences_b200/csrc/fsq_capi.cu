@@ -195,6 +195,20 @@ void flush_phases(fsq_ctx *ctx)
 			float at = 0;
 			if (cudaSuccess == cudaEventElapsedTime(&at, ctx->call_start, p.second.first)) ctx->stats["at_" + p.first] = at;
 			if (cudaSuccess == cudaEventElapsedTime(&at, ctx->call_start, p.second.second)) ctx->stats["end_" + p.first] = at;
+			if (ctx->opt("timeline", 0))
+			{
+				// every occurrence of every phase of the last call, in order: "tl_count", "tl_id_<i>" (index into the list below),
+				// "tl_at_<i>", "tl_end_<i>" (ms from the call's start); tests/gpu_timeline_sharded.py prints them
+				static char const *names[] = {"pass_a", "stitch", "prep", "pass_b", "dp", "exchange", "traceback", "reduce", "pass_c", nullptr};
+				int id = 0;
+				while (names[id] && p.first != names[id]) ++id;
+				size_t const i = (size_t) (&p - ctx->pending.data()) - ctx->call_first_pending;
+				char key[48];
+				snprintf(key, sizeof key, "tl_id_%zu", i); ctx->stats[key] = id;
+				snprintf(key, sizeof key, "tl_end_%zu", i); ctx->stats[key] = at;
+				if (cudaSuccess == cudaEventElapsedTime(&at, ctx->call_start, p.second.first)) { snprintf(key, sizeof key, "tl_at_%zu", i); ctx->stats[key] = at; }
+				ctx->stats["tl_count"] = (double) (i + 1);
+			}
 		}
 		ctx->event_pool.push_back(p.second.first);
 		ctx->event_pool.push_back(p.second.second);
@@ -473,9 +487,14 @@ int run_stitch_plan(fsq_ctx *ctx, scan_state &S, stitch_plan const &plan, uint32
 
 // Pass A (local scans) and the prefix composition of the block summaries (composing summaries is
 // associative): an up-sweep turns the block summaries into summaries of aligned power-of-two spans in place, a down-sweep
-// turns those into the state at every block start *relative to the identity state at the first local column* -- which
-// for an alignment that starts at column 0 is the true state.  2 log2(B) levels of independent stitches.
-int local_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
+// turns those into the state at every block start *relative to the state at the first local column* -- the identity
+// state for an alignment that starts at column 0, which makes them the true states.  2 log2(B) levels of independent stitches.
+// A column shard behind the first does not know its start state before the ranks have exchanged the summaries of their
+// whole shards: it runs the up-sweep with a side chain that yields that summary, and seeds the down-sweep with the true
+// start state once it has arrived.
+typedef std::vector <std::vector <std::pair <uint32_t *, uint32_t const *>>> stitch_copies;
+
+int scan_pass_a(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
 {
 	S.g = choose_geometry(ctx, msa);
 	geometry const &g = S.g;
@@ -485,54 +504,98 @@ int local_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
 	CK(S.sum_a.alloc(ctx, bm * 4)); CK(S.sum_d.alloc(ctx, bm * 4));
 	CK(S.st_a.alloc(ctx, (bm + m) * 4)); CK(S.st_d.alloc(ctx, (bm + m) * 4));
 	CK(S.code.alloc(ctx, bm * 2)); CK(S.oldvals.alloc(ctx, bm * 4)); CK(S.R.alloc(ctx, (size_t) B * 4));
-	uint32_t *sum_a = S.sum_a.as <uint32_t>(), *sum_d = S.sum_d.as <uint32_t>();
-	uint32_t *st_a = S.st_a.as <uint32_t>(), *st_d = S.st_d.as <uint32_t>();
-
-	iota_kernel <<<(m + 255) / 256, 256, 0, ctx->stream>>>(st_a, st_d, m, (uint32_t) msa->col0);
-	CK(cudaGetLastError());
 	S.relative = 0 != msa->col0;
+	phase pa(ctx, "pass_a");
+	block_args A;
+	fill_common(A, msa, g);
+	A.mode = MODE_LOCAL;
+	A.sum_a = S.sum_a.as <uint32_t>();
+	A.sum_d = S.sum_d.as <uint32_t>();
+	CK(launch_scan(A, B, g, false, ctx->stream));
+	pa.stop();
+	ctx->stats["kernel_launches"] += 1;
+	return FSQ_OK;
+}
 
-	{
-		phase pa(ctx, "pass_a");
-		block_args A;
-		fill_common(A, msa, g);
-		A.mode = MODE_LOCAL;
-		A.sum_a = sum_a;
-		A.sum_d = sum_d;
-		CK(launch_scan(A, B, g, false, ctx->stream));
-		pa.stop();
-		ctx->stats["kernel_launches"] += 1;
-	}
-
-	phase ps(ctx, "stitch");
-	auto start_of = [&](uint64_t b) { return (uint32_t) (msa->col0 + b * g.C); };
-	auto U = [&](uint64_t i, uint32_t *&a, uint32_t *&d) { a = sum_a + i * m; d = sum_d + i * m; };
-	auto P = [&](uint64_t i, uint32_t *&a, uint32_t *&d) { a = st_a + (i + 1) * m; d = st_d + (i + 1) * m; };      // state at the end of block i
+static uint32_t sweep_levels(uint32_t B)
+{
 	uint32_t levels = 0;
 	while ((1ull << (levels + 1)) <= B) ++levels;          // 2^levels <= B
-	stitch_plan plan;
-	std::vector <std::vector <std::pair <uint32_t *, uint32_t const *>>> copies;
-	// up-sweep: U[i] <- U[i - 2^l] o U[i] for every i with (i + 1) a multiple of 2^(l + 1)
-	for (uint32_t l = 0; l < levels; ++l)
+	return levels;
+}
+
+// up-sweep: U[i] <- U[i - 2^l] o U[i] for every i with (i + 1) a multiple of 2^(l + 1).
+// total (optional, 2 m words: a then d): the summary of all B blocks.  B is a sum of powers of two, highest first; the spans
+// they stand for are complete nodes of the up-sweep, and the side chain composes them from the right as they complete --
+// (node of bit l) o (what lies behind it) in the launch of level l -- without touching U, which the down-sweep still needs.
+void plan_up_sweep(fsq_msa const *msa, scan_state &S, stitch_plan &plan, stitch_copies &copies, uint32_t *total)
+{
+	geometry const &g = S.g;
+	uint32_t const m = msa->m, B = g.B;
+	uint32_t *sum_a = S.sum_a.as <uint32_t>(), *sum_d = S.sum_d.as <uint32_t>();
+	auto start_of = [&](uint64_t b) { return (uint32_t) (msa->col0 + b * g.C); };
+	auto U = [&](uint64_t i, uint32_t *&a, uint32_t *&d) { a = sum_a + i * m; d = sum_d + i * m; };
+	uint32_t const levels = sweep_levels(B);
+	uint32_t const *tail_a = nullptr, *tail_d = nullptr;      // the summary of the blocks [B - rem, B), rem = B mod 2^l
+	for (uint32_t l = 0; l <= levels; ++l)
 	{
 		uint64_t const half = 1ull << l, span = half << 1;
-		for (uint64_t i = span - 1; i < B; i += span)
+		copies.emplace_back();
+		if (l < levels)
+			for (uint64_t i = span - 1; i < B; i += span)
+			{
+				stitch_item it;
+				memset(&it, 0, sizeof it);
+				uint32_t *la, *ld, *ra, *rd;
+				U(i - half, la, ld); U(i, ra, rd);
+				it.in_a = la; it.in_d = ld;
+				it.pi = ra; it.delta = rd;
+				it.out_a = ra; it.out_d = rd;                   // in place: the kernel holds the item in shared memory before it writes
+				it.s_mark = start_of(i + 1 - half);
+				plan.items.push_back(it);
+			}
+		if (total && (B & half))
 		{
-			stitch_item it;
-			memset(&it, 0, sizeof it);
-			uint32_t *la, *ld, *ra, *rd;
-			U(i - half, la, ld); U(i, ra, rd);
-			it.in_a = la; it.in_d = ld;
-			it.pi = ra; it.delta = rd;
-			it.out_a = ra; it.out_d = rd;                   // in place: the kernel holds the item in shared memory before it writes
-			it.s_mark = start_of(i + 1 - half);
-			plan.items.push_back(it);
+			uint64_t const rem = B & (half - 1);              // blocks behind this node
+			uint32_t *na, *nd;
+			U(B - rem - 1, na, nd);                           // complete since the launch before this one (a block summary when l == 0)
+			if (!tail_a) { tail_a = na; tail_d = nd; }
+			else
+			{
+				stitch_item it;
+				memset(&it, 0, sizeof it);
+				it.in_a = na; it.in_d = nd;
+				it.pi = tail_a; it.delta = tail_d;
+				it.out_a = total; it.out_d = total + m;
+				it.s_mark = start_of(B - rem);
+				plan.items.push_back(it);
+				tail_a = total; tail_d = total + m;
+			}
 		}
 		plan.end_level();
-		copies.emplace_back();
 	}
-	// down-sweep: with 2^l the lowest set bit of i + 1, P[i] = U[i] when i + 1 == 2^l, else P[i - 2^l] o U[i]
-	for (int l = (int) levels; l >= 0; --l)
+	if (total && tail_a != total)
+	{
+		// B is a power of two: the root is the total
+		copies.emplace_back();
+		copies.back().push_back({total, tail_a});
+		copies.back().push_back({total + m, tail_d});
+		plan.end_level();
+	}
+}
+
+// down-sweep: with 2^l the lowest set bit of i + 1, P[i] = U[i] when i + 1 == 2^l, else P[i - 2^l] o U[i]; P[i] is the state
+// at the end of block i.  With a seed (the true state at the first local column): P[i] = seed o U[i] in the first case.
+void plan_down_sweep(fsq_msa const *msa, scan_state &S, stitch_plan &plan, stitch_copies &copies, uint32_t const *seed_a, uint32_t const *seed_d)
+{
+	geometry const &g = S.g;
+	uint32_t const m = msa->m, B = g.B;
+	uint32_t *sum_a = S.sum_a.as <uint32_t>(), *sum_d = S.sum_d.as <uint32_t>();
+	uint32_t *st_a = S.st_a.as <uint32_t>(), *st_d = S.st_d.as <uint32_t>();
+	auto start_of = [&](uint64_t b) { return (uint32_t) (msa->col0 + b * g.C); };
+	auto U = [&](uint64_t i, uint32_t *&a, uint32_t *&d) { a = sum_a + i * m; d = sum_d + i * m; };
+	auto P = [&](uint64_t i, uint32_t *&a, uint32_t *&d) { a = st_a + (i + 1) * m; d = st_d + (i + 1) * m; };
+	for (int l = (int) sweep_levels(B); l >= 0; --l)
 	{
 		uint64_t const half = 1ull << l, span = half << 1;
 		copies.emplace_back();
@@ -540,58 +603,48 @@ int local_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
 		{
 			uint32_t *ua, *ud, *pa_, *pd_;
 			U(i, ua, ud); P(i, pa_, pd_);
-			if (i + 1 == half)
-			{
-				copies.back().push_back({pa_, ua});
-				copies.back().push_back({pd_, ud});
-				continue;
-			}
 			stitch_item it;
 			memset(&it, 0, sizeof it);
-			uint32_t *qa, *qd;
-			P(i - half, qa, qd);
-			it.in_a = qa; it.in_d = qd;
+			if (i + 1 == half)
+			{
+				if (!seed_a)
+				{
+					copies.back().push_back({pa_, ua});
+					copies.back().push_back({pd_, ud});
+					continue;
+				}
+				it.in_a = seed_a; it.in_d = seed_d;
+				it.s_mark = start_of(0);
+			}
+			else
+			{
+				uint32_t *qa, *qd;
+				P(i - half, qa, qd);
+				it.in_a = qa; it.in_d = qd;
+				it.s_mark = start_of(i + 1 - half);
+			}
 			it.pi = ua; it.delta = ud;
 			it.out_a = pa_; it.out_d = pd_;
-			it.s_mark = start_of(i + 1 - half);
 			plan.items.push_back(it);
 		}
 		plan.end_level();
 	}
-	{
-		int const rc = run_stitch_plan(ctx, S, plan, m, copies);
-		if (rc) return rc;
-	}
-	ps.stop();
-	return FSQ_OK;
 }
 
-// Column-sharded operation: the states of local_scan() are relative to the identity state at the first local column;
-// given the true state there (d_a, d_d on the device), every block start becomes (true state) o (relative state).
-int apply_start_state(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S, uint32_t const *d_a, uint32_t const *d_d)
+int local_scan(fsq_ctx *ctx, fsq_msa const *msa, scan_state &S)
 {
-	geometry const &g = S.g;
+	int rc = scan_pass_a(ctx, msa, S);
+	if (rc) return rc;
 	uint32_t const m = msa->m;
-	uint32_t *st_a = S.st_a.as <uint32_t>(), *st_d = S.st_d.as <uint32_t>();
+	iota_kernel <<<(m + 255) / 256, 256, 0, ctx->stream>>>(S.st_a.as <uint32_t>(), S.st_d.as <uint32_t>(), m, (uint32_t) msa->col0);
+	CK(cudaGetLastError());
 	phase ps(ctx, "stitch");
 	stitch_plan plan;
-	for (uint64_t b = 1; b <= g.B; ++b)
-	{
-		stitch_item it;
-		memset(&it, 0, sizeof it);
-		it.in_a = d_a; it.in_d = d_d;
-		it.pi = st_a + b * m; it.delta = st_d + b * m;
-		it.out_a = st_a + b * m; it.out_d = st_d + b * m;
-		it.s_mark = (uint32_t) msa->col0;
-		plan.items.push_back(it);
-	}
-	plan.end_level();
-	int const rc = run_stitch_plan(ctx, S, plan, m, {});
-	if (rc) return rc;
-	CK(cudaMemcpyAsync(st_a, d_a, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-	CK(cudaMemcpyAsync(st_d, d_d, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+	stitch_copies copies;
+	plan_up_sweep(msa, S, plan, copies, nullptr);
+	plan_down_sweep(msa, S, plan, copies, nullptr, nullptr);
+	if ((rc = run_stitch_plan(ctx, S, plan, m, copies))) return rc;
 	ps.stop();
-	S.relative = false;
 	return FSQ_OK;
 }
 
@@ -794,48 +847,69 @@ int run_prepare(fsq_run *R)
 {
 	fsq_ctx *ctx = R->ctx;
 	uint32_t const m = R->m;
-	int rc = local_scan(ctx, R->msa, R->S);
-	if (rc) return rc;
-	if (R->size > 1)
+	int rc;
+	if (R->size <= 1)
 	{
-		// this rank's summary = the state at the end of its last block relative to the identity state at c0; every rank
-		// receives all of them and composes the ones before it (composition is associative: SURVEY.md A.10)
-		geometry const &g = R->S.g;
-		CK(R->sums.alloc(ctx, ((size_t) R->size + 3) * 2 * m * 4));
-		uint32_t *all = R->sums.as <uint32_t>();
-		uint32_t *mine = all + (size_t) R->rank * 2 * m;
-		CK(cudaMemcpyAsync(mine, R->S.st_a.as <uint32_t>() + (size_t) g.B * m, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
-		CK(cudaMemcpyAsync(mine + m, R->S.st_d.as <uint32_t>() + (size_t) g.B * m, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+		if ((rc = local_scan(ctx, R->msa, R->S))) return rc;
+		if (R->S.relative) return fail(ctx, FSQ_ERR_ARG, "this entry point needs an alignment that starts at column 0");
+		return compress_starts(ctx, R->msa, R->S);
+	}
+	// Column shards.  This rank's summary = the state at the end of its last block relative to the identity state at c0: it
+	// comes out of the up-sweep (plan_up_sweep's side chain); every rank receives all of them and composes the ones before
+	// it (composition is associative: SURVEY.md A.10) into the true state at c0, with which the down-sweep starts.
+	if ((rc = scan_pass_a(ctx, R->msa, R->S))) return rc;
+	CK(R->sums.alloc(ctx, ((size_t) R->size + 3) * 2 * m * 4));
+	uint32_t *all = R->sums.as <uint32_t>();
+	uint32_t *mine = all + (size_t) R->rank * 2 * m;
+	{
+		phase ps(ctx, "stitch");
+		stitch_plan plan;
+		stitch_copies copies;
+		plan_up_sweep(R->msa, R->S, plan, copies, mine);
+		if ((rc = run_stitch_plan(ctx, R->S, plan, m, copies))) return rc;
+		ps.stop();
+	}
+	{
 		phase px(ctx, "exchange");
 		CK(R->comm->all_gather(mine, all, (size_t) 2 * m * 4, ctx->stream));
 		px.stop();
-		if (R->rank > 0)
-		{
-			uint32_t *tmp = all + (size_t) R->size * 2 * m;          // two scratch states behind the summaries
-			uint32_t const *cur = all;
-			phase ps(ctx, "stitch");
-			for (int i = 1; i < R->rank; ++i)
-			{
-				stitch_plan plan;
-				stitch_item it;
-				memset(&it, 0, sizeof it);
-				uint32_t *out = tmp + (size_t) (i & 1) * 2 * m;
-				it.in_a = cur; it.in_d = cur + m;
-				it.pi = all + (size_t) i * 2 * m; it.delta = it.pi + m;
-				it.out_a = out; it.out_d = out + m;
-				it.s_mark = (uint32_t) ((uint64_t) i * R->n_per);
-				plan.items.push_back(it);
-				plan.end_level();
-				if ((rc = run_stitch_plan(ctx, R->S, plan, m, {}))) return rc;
-				cur = out;
-			}
-			ps.stop();
-			if ((rc = apply_start_state(ctx, R->msa, R->S, cur, cur + m))) return rc;
-		}
-		R->S.relative = false;
 	}
-	else if (R->S.relative)
-		return fail(ctx, FSQ_ERR_ARG, "this entry point needs an alignment that starts at column 0");
+	{
+		phase ps(ctx, "stitch");
+		stitch_plan plan;
+		stitch_copies copies;
+		uint32_t *tmp = all + (size_t) R->size * 2 * m;          // two scratch states behind the summaries
+		uint32_t const *seed = R->rank > 0 ? all : nullptr;
+		for (int i = 1; i < R->rank; ++i)
+		{
+			stitch_item it;
+			memset(&it, 0, sizeof it);
+			uint32_t *out = tmp + (size_t) (i & 1) * 2 * m;
+			it.in_a = seed; it.in_d = seed + m;
+			it.pi = all + (size_t) i * 2 * m; it.delta = it.pi + m;
+			it.out_a = out; it.out_d = out + m;
+			it.s_mark = (uint32_t) ((uint64_t) i * R->n_per);
+			plan.items.push_back(it);
+			plan.end_level();
+			copies.emplace_back();
+			seed = out;
+		}
+		plan_down_sweep(R->msa, R->S, plan, copies, seed, seed ? seed + m : nullptr);
+		if ((rc = run_stitch_plan(ctx, R->S, plan, m, copies))) return rc;
+		uint32_t *st_a = R->S.st_a.as <uint32_t>(), *st_d = R->S.st_d.as <uint32_t>();
+		if (seed)
+		{
+			CK(cudaMemcpyAsync(st_a, seed, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+			CK(cudaMemcpyAsync(st_d, seed + m, (size_t) m * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+		}
+		else
+		{
+			iota_kernel <<<(m + 255) / 256, 256, 0, ctx->stream>>>(st_a, st_d, m, (uint32_t) R->msa->col0);
+			CK(cudaGetLastError());
+		}
+		ps.stop();
+	}
+	R->S.relative = false;
 	return compress_starts(ctx, R->msa, R->S);
 }
 
@@ -1834,7 +1908,7 @@ int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
 		}
 		return FSQ_OK;
 	}
-	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", "whole_waves", "mem_limit", "window_blocks", "halo", "trace_window", nullptr};
+	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", "whole_waves", "mem_limit", "window_blocks", "halo", "trace_window", "timeline", nullptr};
 	for (char const **k = known; *k; ++k)
 		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }
 	return fail(ctx, FSQ_ERR_ARG, "unknown option '%s'", key);
@@ -2077,11 +2151,16 @@ int fsq_segment_sharded(fsq_ctx *ctx, const fsq_msa *msa, fsq_comm *comm, uint64
 	else ctx->call_first_pending = ctx->pending.size();
 	if (!ctx->call_start) CK(cudaEventCreate(&ctx->call_start));
 	CK(cudaEventRecord(ctx->call_start, ctx->stream));
-	fsq_run run;
-	if ((rc = run_init(&run, ctx, msa, comm && comm->size > 1 ? comm : nullptr, n_total, L))) return rc;
-	rc = run_segment(&run, out);
-	// the run's buffers go back to the cache when `run` dies: nothing may still be using them
-	cudaStreamSynchronize(ctx->stream);
+	auto const t_entry = std::chrono::steady_clock::now();
+	{
+		fsq_run run;
+		if ((rc = run_init(&run, ctx, msa, comm && comm->size > 1 ? comm : nullptr, n_total, L))) return rc;
+		rc = run_segment(&run, out);
+		// the run's buffers go back to the cache when `run` dies: nothing may still be using them
+		cudaStreamSynchronize(ctx->stream);
+		ctx->stats["hms_after"] += std::chrono::duration <double, std::milli>(std::chrono::steady_clock::now() - run.t_mark).count();   // since the last read of the control words
+	}
+	ctx->stats["hms_call"] += std::chrono::duration <double, std::milli>(std::chrono::steady_clock::now() - t_entry).count();
 	return rc;
 }
 
