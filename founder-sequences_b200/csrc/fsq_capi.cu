@@ -134,6 +134,8 @@ struct fsq_segmentation
 	std::vector <uint32_t> size;
 	dbuf d_lb, d_rb, d_size;                  // ... on the device: n_reduced entries each
 	bool bounds_on_host{false};
+	hbuf h_bounds;                            // the bounds as they rode along with the control words: lb u64[stride], rb u64[stride], size u32[stride]
+	uint32_t h_bounds_stride{0};
 	uint32_t own_first{}, own_last{};         // the reduced segments whose state this rank holds (all of them on one GPU)
 	dbuf red_a, red_d;                        // their states on the device, (own_last - own_first) x m
 	hbuf h_a, h_d;                            // pinned host copies, made on first request
@@ -739,6 +741,11 @@ struct fsq_run
 	uint32_t back_bound{1u << 16};     // masks and rmq cells are rebuilt this far below the rank's first entry
 	bool single_chain{false};
 	dbuf tbx_max, tbx_lb, tbx_size, mk, lev, ctl, chunk_level, cnt, h0, toplist, states, xflags, sums;
+	// Column shards exchange, round by round, only what another rank can read of a slice: its last `tails` entries (the
+	// look-back window of the rank behind) and the window minima at the ends of its chains.  0: whole slices (one rank; or
+	// the look-back bound was given up, back_bound == 0xffffffff).
+	uint32_t tails{0};
+	dbuf xtails, xlevels;
 	uint64_t state_stride{};
 	struct window { uint32_t b0, b1; uint64_t col0, col1; };      // blocks [b0, b1) = local columns [col0, col1)
 	std::vector <window> windows;
@@ -839,6 +846,7 @@ int run_init(fsq_run *R, fsq_ctx *ctx, fsq_msa const *msa, fsq_comm *comm, uint6
 	R->t_bound = (uint32_t) (R->dp_size / L + 2);
 	R->rows_bound = 1 == R->size ? R->t_bound : (uint32_t) (R->n_per / L + 2);
 	R->halo = (uint32_t) std::max <int64_t>(1, ctx->opt("halo", 16));
+	R->back_bound = (uint32_t) std::min <int64_t>(0xffffffffll, std::max <int64_t>(64, ctx->opt("dp_back_bound", 1 << 16)));
 	return FSQ_OK;
 }
 
@@ -1022,13 +1030,36 @@ int run_reset_tables(fsq_run *R)
 		if (!R->xflags.p) CK(R->xflags.alloc(ctx, ((size_t) R->size + 1) * 16));
 		CK(R->h_ctl.alloc(ctx, N_CONTROL * 4));
 	}
+	R->tails = 0;
+	if (R->size > 1 && 0xffffffffu != R->back_bound && 0 != ctx->opt("exchange_tails", 1))
+	{
+		R->tails = (uint32_t) std::min <uint64_t>(R->n_per, (uint64_t) R->back_bound + 64);
+		CK(R->xtails.alloc(ctx, (size_t) R->size * R->tails * 4));
+		CK(R->xlevels.alloc(ctx, (size_t) R->size * R->n_chunks * 4));
+	}
 	// entries the per-column DP writes start from 0 (the first round's stand-in for "nothing known"); the ones the
-	// reference never writes keep its defaults; masks and rmq cells start from values that index inside the table
-	CK(cudaMemsetAsync(R->tbx_max.p, 0xff, R->tb_len * 4, ctx->stream));
-	CK(cudaMemsetAsync(R->tb_max(), 0, (size_t) R->n_entries * 4, ctx->stream));
-	CK(cudaMemsetAsync(R->tbx_size.p, 0xff, R->tb_len * 4, ctx->stream));
-	CK(cudaMemsetAsync(R->tbx_lb.p, 0, R->tb_len * 4, ctx->stream));
-	CK(cudaMemsetAsync(R->mk.p, 0xff, R->dp_size * 8, ctx->stream));
+	// reference never writes keep its defaults; masks and rmq cells start from values that index inside the table.
+	// With tails only this rank touches its own slice and the window below it: the rest of its copy is never read.
+	uint64_t x0 = 0, x1 = R->tb_len;                    // in table positions (entry t at t + L - 1)
+	if (R->tails)
+	{
+		uint64_t const below = (uint64_t) R->tails + 128;
+		x0 = (R->c0 > below ? R->c0 - below : 0) & ~63ull;
+		x1 = std::min <uint64_t>(R->tb_len, R->c0 + R->n_per + 64);
+	}
+	uint64_t const shift = R->L - 1;
+	uint64_t const e0 = x0 > shift ? x0 - shift : 0;    // in entries
+	uint64_t const e1 = x1 > shift ? x1 - shift : 0;
+	CK(cudaMemsetAsync(R->tbx_max.as <uint32_t>() + x0, 0xff, (x1 - x0) * 4, ctx->stream));
+	if (std::min <uint64_t>(e1, R->n_entries) > e0) CK(cudaMemsetAsync(R->tb_max() + e0, 0, (std::min <uint64_t>(e1, R->n_entries) - e0) * 4, ctx->stream));
+	CK(cudaMemsetAsync(R->tbx_size.as <uint32_t>() + x0, 0xff, (x1 - x0) * 4, ctx->stream));
+	CK(cudaMemsetAsync(R->tbx_lb.as <uint32_t>() + x0, 0, (x1 - x0) * 4, ctx->stream));
+	{
+		uint64_t const k0 = e0 & ~63ull, k1 = std::min <uint64_t>(e1, R->dp_size);
+		if (k1 > k0) CK(cudaMemsetAsync(R->mk.as <uint64_t>() + k0, 0xff, (k1 - k0) * 8, ctx->stream));
+		// (a stale mask of all zeros in block 0 would point one entry below the table)
+		if (k0 > 0) CK(cudaMemsetAsync(R->mk.p, 0xff, (size_t) std::min <uint64_t>(64, R->dp_size) * 8, ctx->stream));
+	}
 	CK(cudaMemsetAsync(R->lev.p, 0, (size_t) R->n_levels * R->n_blk * 4, ctx->stream));
 	CK(cudaMemsetAsync(R->ctl.p, 0, N_CONTROL * 4, ctx->stream));
 	R->single_chain = false;
@@ -1098,6 +1129,15 @@ dp_args run_dp_args(fsq_run const *R, fsq_run::window const *w)
 	// entries when a single rank walks its windows in order
 	D.lvl_first = 0; D.lvl_last = R->n_entries;
 	if (1 == R->size && w) { D.lvl_first = D.t_first; D.lvl_last = D.t_last; }
+	D.own_first = 0; D.own_last = R->n_entries;
+	D.lvl_gathered = nullptr; D.lvl_ranks = 0;
+	if (R->tails)
+	{
+		// what this rank holds of the table: its own entries and the window below them
+		D.lvl_first = D.w_first; D.lvl_last = R->t_last;
+		D.own_first = R->t_first; D.own_last = R->t_last;
+		D.lvl_gathered = R->xlevels.as <uint32_t>(); D.lvl_ranks = (uint32_t) R->size;
+	}
 	return D;
 }
 
@@ -1142,13 +1182,34 @@ int run_enqueue_round(fsq_run *R, uint32_t round_no, size_t w_begin, size_t w_en
 	}
 	if (R->size > 1)
 	{
+		dp_args G = run_dp_args(R, nullptr);
+		if (R->tails)
+		{
+			// the window minima at the ends of the own chains, for the guess that may follow
+			phase pd(ctx, "dp");
+			CK(launch_dp_chunk_minima(G, ctx->stream));
+			pd.stop();
+			ctx->stats["kernel_launches"] += 1;
+		}
 		phase px(ctx, "exchange");
 		R->comm->group_begin();
-		cudaError_t e1 = R->comm->all_gather(R->tbx_max.as <uint32_t>() + (size_t) R->rank * R->n_per, R->tbx_max.p, (size_t) R->n_per * 4, ctx->stream);
+		cudaError_t e1, e4 = cudaSuccess;
+		if (R->tails)
+		{
+			e1 = R->comm->all_gather(R->tbx_max.as <uint32_t>() + ((size_t) R->rank + 1) * R->n_per - R->tails, R->xtails.p, (size_t) R->tails * 4, ctx->stream);
+			e4 = R->comm->all_gather(G.chunk_level + R->n_chunks, R->xlevels.p, (size_t) R->n_chunks * 4, ctx->stream);
+		}
+		else
+			e1 = R->comm->all_gather(R->tbx_max.as <uint32_t>() + (size_t) R->rank * R->n_per, R->tbx_max.p, (size_t) R->n_per * 4, ctx->stream);
 		cudaError_t e2 = R->comm->all_gather(mine, xs, 16, ctx->stream);
 		cudaError_t e3 = R->comm->group_end();
-		if (cudaSuccess != e1 || cudaSuccess != e2 || cudaSuccess != e3)
+		if (cudaSuccess != e1 || cudaSuccess != e2 || cudaSuccess != e3 || cudaSuccess != e4)
 			return fail(ctx, FSQ_ERR_CUDA, "exchange of the DP table slices failed: %s", R->comm->error.empty() ? "CUDA error" : R->comm->error.c_str());
+		if (R->tails)
+		{
+			CK(launch_dp_scatter_tails(R->xtails.as <uint32_t>(), (uint32_t) R->size, (uint32_t) R->rank, R->tails, R->n_per, R->tbx_max.as <uint32_t>(), ctx->stream));
+			ctx->stats["kernel_launches"] += 1;
+		}
 		px.stop();
 	}
 	phase pd(ctx, "dp");
@@ -1443,6 +1504,7 @@ int run_sequential_dp(fsq_run *R, bool rescan)
 	fsq_ctx *ctx = R->ctx;
 	int rc;
 	R->single_chain = true;
+	R->tails = 0;               // whole slices from here on: every turn ends with one
 	ctx->stats["dp_fallbacks"] += 1;
 	CK(cudaMemsetAsync(R->control() + F_DONE, 0, 4, ctx->stream));
 	for (int r = 0; r < R->size; ++r)
@@ -1615,7 +1677,7 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 				if ((rc = run_enqueue_final(R, rescan, with_tail))) return rc;
 				if (with_tail && (rc = run_enqueue_fast_tail(R, true, (size_t) R->t_bound * 20 <= ((size_t) 4 << 20)))) return rc;
 				if ((rc = run_read_control(R))) return rc;
-				if (R->h[F_WINDOW_ERR] && R->size > 1 && 0xffffffffu != R->back_bound) { R->back_bound = 0xffffffffu; restart = true; break; }
+				if (R->h[F_WINDOW_ERR] && R->size > 1 && 0xffffffffu != R->back_bound) { R->back_bound = 0xffffffffu; restart = true; ctx->stats["dp_window_restarts"] += 1; break; }
 				if (R->h[F_DONE]) { tail_done = with_tail; break; }
 				if (R->h[F_SURE] && lists_too_short()) break;          // chains that are final already ran out of list: no point in settling the rest
 				if (rounds >= (uint32_t) max_rounds)
@@ -1705,6 +1767,7 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 	ctx->stats["dp_rounds"] += total_rounds;
 	ctx->stats["dp_chunks"] = R->n_chunks;
 	ctx->stats["dp_reach"] = R->h[F_REACH];
+	ctx->stats["exchange_tail_entries"] = R->tails;
 
 	fsq_segmentation *seg = new (std::nothrow) fsq_segmentation;
 	if (!seg) return fail(ctx, FSQ_ERR_NOMEM, "out of host memory");
@@ -1823,13 +1886,10 @@ int run_segment(fsq_run *R, fsq_segmentation **out)
 	seg->n_reduced = n_red;
 	if (tail_done && (size_t) R->t_bound * 20 <= ((size_t) 4 << 20))
 	{
-		uint32_t const copied = R->t_bound;
-		uint64_t const *h_lb = R->h_red.as <uint64_t>(), *h_rb = h_lb + copied;
-		uint32_t const *h_sz = (uint32_t const *) (h_rb + copied);
-		seg->lb.assign(h_lb, h_lb + n_red);
-		seg->rb.assign(h_rb, h_rb + n_red);
-		seg->size.assign(h_sz, h_sz + n_red);
-		seg->bounds_on_host = true;
+		// (the pinned block goes with the handle as it is: unpacking it here would cost every call 0.1 - 0.7 ms of host time,
+		// for arrays that only some callers ask for)
+		seg->h_bounds.adopt(R->h_red);
+		seg->h_bounds_stride = R->t_bound;
 	}
 	seg->d_lb.adopt(R->red_lb); seg->d_rb.adopt(R->red_rb); seg->d_size.adopt(R->red_size);
 	seg->own_first = seg_first; seg->own_last = seg_last;
@@ -1908,7 +1968,7 @@ int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value)
 		}
 		return FSQ_OK;
 	}
-	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", "whole_waves", "mem_limit", "window_blocks", "halo", "trace_window", "timeline", nullptr};
+	static char const *known[] = {"block_columns", "cap", "keep_dp", "warps", "kernel", "chunk", "stitch_group", "stitch_sort", "dp_chunks", "dp_max_rounds", "dp_guess_rounds", "store_states", "whole_waves", "mem_limit", "window_blocks", "halo", "trace_window", "timeline", "exchange_tails", "dp_back_bound", nullptr};
 	for (char const **k = known; *k; ++k)
 		if (0 == strcmp(*k, key)) { ctx->opts[key] = value; return FSQ_OK; }
 	return fail(ctx, FSQ_ERR_ARG, "unknown option '%s'", key);
@@ -2192,6 +2252,17 @@ static int fetch_bounds(fsq_segmentation *seg)
 	fsq_ctx *ctx = seg->ctx;
 	if (seg->bounds_on_host) return FSQ_OK;
 	uint32_t const n = seg->n_reduced;
+	if (seg->h_bounds.p)
+	{
+		uint64_t const *h_lb = seg->h_bounds.as <uint64_t>(), *h_rb = h_lb + seg->h_bounds_stride;
+		uint32_t const *h_sz = (uint32_t const *) (h_rb + seg->h_bounds_stride);
+		seg->lb.assign(h_lb, h_lb + n);
+		seg->rb.assign(h_rb, h_rb + n);
+		seg->size.assign(h_sz, h_sz + n);
+		seg->h_bounds.release();
+		seg->bounds_on_host = true;
+		return FSQ_OK;
+	}
 	seg->lb.resize(n); seg->rb.resize(n); seg->size.resize(n);
 	if (n)
 	{

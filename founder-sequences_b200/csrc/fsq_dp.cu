@@ -407,6 +407,12 @@ __global__ void __launch_bounds__(128) dp_chunk_level_kernel(dp_args const A)
 	if (A.skip_when_done && A.flags[F_DONE]) return;
 	uint32_t const c = blockIdx.x;
 	uint32_t const end = min(A.n_entries, (c + 1) * A.chunk);
+	if (end - 1 < A.own_first || end - 1 >= A.own_last)
+	{
+		// another rank's chain: its minimum arrives with the exchange
+		if (0 == threadIdx.x) A.chunk_level[A.n_chunks + c] = 0;
+		return;
+	}
 	uint32_t const D = 2 * A.flags[F_REACH] + 64;          // twice the farthest look-back seen so far
 	uint32_t const begin = end > D ? end - D : 0;
 	uint32_t v = 0xffffffffu;
@@ -429,7 +435,12 @@ __global__ void __launch_bounds__(1024) dp_level_kernel(dp_args const A)
 	for (uint32_t c0 = 0; c0 < A.n_chunks; c0 += blockDim.x)
 	{
 		uint32_t const c = c0 + threadIdx.x;
-		uint32_t const v = c < A.n_chunks ? A.chunk_level[A.n_chunks + c] : 0u;
+		uint32_t v = 0;
+		if (c < A.n_chunks)
+		{
+			if (A.lvl_gathered) { for (uint32_t r = 0; r < A.lvl_ranks; ++r) v = max(v, A.lvl_gathered[(size_t) r * A.n_chunks + c]); }
+			else v = A.chunk_level[A.n_chunks + c];
+		}
 		uint32_t s = v;                                    // inclusive running maximum inside the warp
 #pragma unroll
 		for (int o = 1; o < 32; o <<= 1)
@@ -483,10 +494,33 @@ __global__ void dp_levels_kernel(dp_args const A, uint32_t p)
 	A.lev[(size_t) p * A.n_blk + i] = (A.tb_max[smp0] < A.tb_max[prev]) ? smp0 : prev;
 }
 
+cudaError_t launch_dp_chunk_minima(dp_args const &A, cudaStream_t st)
+{
+	dp_chunk_level_kernel <<<A.n_chunks, 128, 0, st>>>(A);
+	return cudaGetLastError();
+}
+
+__global__ void dp_scatter_tails_kernel(uint32_t const *gathered, uint32_t rank, uint32_t tail, uint64_t n_per, uint32_t *tbx_max)
+{
+	// blockIdx.y: the rank whose tail this is (the ranks before this one)
+	uint32_t const q = blockIdx.y;
+	uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (q >= rank || i >= tail) return;
+	tbx_max[(uint64_t) (q + 1) * n_per - tail + i] = gathered[(size_t) q * tail + i];
+}
+
+cudaError_t launch_dp_scatter_tails(uint32_t const *gathered, uint32_t size, uint32_t rank, uint32_t tail, uint64_t n_per, uint32_t *tbx_max, cudaStream_t st)
+{
+	(void) size;
+	if (0 == rank || 0 == tail) return cudaSuccess;
+	dp_scatter_tails_kernel <<<dim3((tail + 255) / 256, rank), 256, 0, st>>>(gathered, rank, tail, n_per, tbx_max);
+	return cudaGetLastError();
+}
+
 cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st)
 {
 	// (launch_dp_rebuild is declared in fsq_internal.h)
-	dp_chunk_level_kernel <<<A.n_chunks, 128, 0, st>>>(A);
+	if (!A.lvl_gathered) dp_chunk_level_kernel <<<A.n_chunks, 128, 0, st>>>(A);
 	dp_level_kernel <<<1, 1024, 0, st>>>(A);
 	if (A.lvl_last > A.lvl_first) dp_raise_kernel <<<(A.lvl_last - A.lvl_first + 255) / 256, 256, 0, st>>>(A);
 	return launch_dp_rebuild(A, st);

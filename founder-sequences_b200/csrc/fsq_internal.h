@@ -166,9 +166,17 @@ struct dp_args
 	uint32_t chain_base;        // everything before chain chain_base is final when the rounds start
 	uint32_t w_first, w_last;   // masks and rmq cells are rebuilt for entries [w_first, w_last) (w_first a multiple of 64)
 	uint32_t lvl_first, lvl_last;   // the guess levels entries [lvl_first, lvl_last) (chains on the global grid of `chunk` entries)
+	// Column shards that exchange only what the rank behind reads (the last entries of every slice): a rank then sees the
+	// ends of its own chains only, computes their window minima at the end of a round (launch_dp_chunk_minima), and the
+	// guess takes every chain's from the gathered copies: lvl_gathered[lvl_ranks][n_chunks], zero where a rank owns nothing.
+	uint32_t own_first, own_last;   // chain ends (end - 1) in [own_first, own_last) are this rank's; 0 .. n_entries on one rank
+	uint32_t const *lvl_gathered; uint32_t lvl_ranks;
 };
 
 cudaError_t launch_dp_chains(dp_args const &A, cudaStream_t st);       // every chain once, against the table as it stands
+cudaError_t launch_dp_chunk_minima(dp_args const &A, cudaStream_t st); // chunk_level[n_chunks + c] = the window minimum at the end of chain c (own chains; 0 elsewhere)
+// The tails the ranks sent (gathered[size][tail] entries: the last `tail` of each slice of n_per) into the table copy of this rank.
+cudaError_t launch_dp_scatter_tails(uint32_t const *gathered, uint32_t size, uint32_t rank, uint32_t tail, uint64_t n_per, uint32_t *tbx_max, cudaStream_t st);
 cudaError_t launch_dp_guess(dp_args const &A, cudaStream_t st);        // between rounds: level the table, rebuild masks and rmq tables
 cudaError_t launch_dp_final(dp_args const &A, cudaStream_t st);        // the last column (entry n - L)
 cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st);      // masks and rmq tables from the table as it stands

@@ -53,7 +53,10 @@ const char *fsq_version(void);
  * (plan device memory as if this many bytes were available), "window_blocks" (scan blocks per window of top lists:
  * the exact scan and the DP then alternate over windows that share one list buffer), "halo" (rows of the ranks behind
  * it that a rank's greedy reduction starts with), "trace_window" (entries per rank exported as places where the traceback
- * path may enter it; a longer jump falls back to the traceback over the gathered table). */
+ * path may enter it; a longer jump falls back to the traceback over the gathered table), "dp_back_bound" (entries below
+ * a rank's first that its DP may look back at, 65,536: the ranks exchange this much of their slices per round, and a
+ * longer look-back falls back to whole slices), "exchange_tails" (0: whole slices from the start), "timeline" (1: the
+ * statistics "tl_count", "tl_id_<i>", "tl_at_<i>", "tl_end_<i>" list every timed phase of the last call in order). */
 int fsq_set_option(fsq_ctx *ctx, const char *key, int64_t value);
 int fsq_get_stat(const fsq_ctx *ctx, const char *key, double *value);   /* e.g. "ms_pack", "ms_pass_a", "ms_dp", "kernel_launches" */
 

@@ -58,6 +58,8 @@ def run_sharded(fsq, rows, L, parts, options=None):
                 res.cap_retries = ctx.stat("cap_retries")
                 res.dp_fallbacks = ctx.stat("dp_fallbacks")
                 res.windows = ctx.stat("windows")
+                res.tail_entries = ctx.stat("exchange_tail_entries")
+                res.window_restarts = ctx.stat("dp_window_restarts")
                 seg.free()
                 results[rank] = res
             finally:
@@ -173,3 +175,26 @@ def test_sharded_traceback_fallback_when_jumps_outgrow_the_window(fsq, oracle, s
     check_against_oracle(oracle, rows, 9, res)
     res = run_sharded(fsq, rows, 9, 4, {"block_columns": 90})
     check_against_oracle(oracle, rows, 9, res)
+
+
+@pytest.mark.parametrize("parts,back", [(2, 1024), (3, 1024), (5, 1024), (3, 64)])
+def test_sharded_exchange_of_tails(fsq, oracle, synth, parts, back):
+    """Per round the ranks exchange the last dp_back_bound + 64 entries of their slices (what the rank behind can look
+    back at) and the window minima of their chains instead of whole slices; a look-back bound that the data outgrow
+    (64 entries here) is noticed on the device and the run starts over with whole slices."""
+    m, n, L = 120, 9000, 6
+    rows = synth.synth_rows(m, n, seed=5 + parts, founders=10, gaps=True, recomb_block=300, mu=0.004)
+    opts = {"block_columns": 250, "dp_chunks": 40, "dp_back_bound": back}
+    res = run_sharded(fsq, rows, L, parts, opts)
+    check_against_oracle(oracle, rows, L, res)
+    seen = [(r.tail_entries, r.window_restarts) for r in res]
+    if back >= 128:
+        assert all(x == (back + 64, 0) for x in seen), seen
+    else:
+        assert all(x == (0, 1) for x in seen), seen
+    res = run_sharded(fsq, rows, L, parts, dict(opts, exchange_tails=0))
+    check_against_oracle(oracle, rows, L, res)
+    assert all(r.tail_entries == 0 for r in res)
+    # several rounds without the guess: every round's exchange matters
+    res = run_sharded(fsq, rows, L, parts, dict(opts, dp_guess_rounds=0, dp_max_rounds=200))
+    check_against_oracle(oracle, rows, L, res)
