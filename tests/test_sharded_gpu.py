@@ -195,6 +195,10 @@ def test_sharded_exchange_of_tails(fsq, oracle, synth, parts, back):
     res = run_sharded(fsq, rows, L, parts, dict(opts, exchange_tails=0))
     check_against_oracle(oracle, rows, L, res)
     assert all(r.tail_entries == 0 for r in res)
+    # the top lists in windows of two blocks: every round re-scans them, the exchange follows the last window
+    res = run_sharded(fsq, rows, L, parts, dict(opts, window_blocks=2))
+    check_against_oracle(oracle, rows, L, res)
+    assert res[0].windows > 1
     # several rounds without the guess: every round's exchange matters
     res = run_sharded(fsq, rows, L, parts, dict(opts, dp_guess_rounds=0, dp_max_rounds=200))
     check_against_oracle(oracle, rows, L, res)
