@@ -382,7 +382,11 @@ def run(args, rank, local_rank, world, m, n, L, founders, gaps, seed, desc, np, 
         from __graft_entry__ import load_sharded
         sharded = load_sharded()
         comm = sharded.nccl_comm(ctx, dist)
-        if not args.no_parity:
+        # the unsharded run of rank 0 holds the whole alignment (4 bits per cell) and the states of every column it can keep
+        whole_bytes = m * n_total // 2
+        if not args.no_parity and whole_bytes > 60e9:
+            parity = ("skipped: the unsharded alignment (%.0f GB packed) does not fit one GPU; the same shape on a slice is checked by tests/gpu_c5_shape_check.py" % (whole_bytes / 1e9), None)
+        elif not args.no_parity:
             verdict, digest = sharded_parity(np, torch, dist, fsq, sharded, ctx, comm, rank, world, dev, m, n, L, founders, gaps, seed)
             parity = (verdict, digest)
             if verdict != "ok":
