@@ -480,7 +480,7 @@ int run_stitch_plan(fsq_ctx *ctx, scan_state &S, stitch_plan const &plan, uint32
 		SA.n_ctas = (uint32_t) count;
 		SA.m = m;
 		SA.n_tiles = S.g.n_tiles;
-		SA.use_sort = ctx->opt("stitch_sort", 1) ? 1u : 0u;
+		SA.use_sort = (uint32_t) std::min <int64_t>(2, std::max <int64_t>(0, ctx->opt("stitch_sort", 2)));      // 0 radix passes, 1 sorting network, 2 counting (m <= 1024)
 		CK(launch_stitch(SA, ctx->stream));
 		ctx->stats["kernel_launches"] += 1;
 	}

@@ -189,6 +189,43 @@ __global__ void __launch_bounds__(1024) prep_kernel(uint32_t const *st_d, uint32
 	uint32_t const tid = threadIdx.x;
 	uint32_t const *d = st_d + (size_t) b * m;
 
+	if (p2 == blockDim.x)
+	{
+		// one value per thread (m <= 1024): the network runs in registers below 32 lanes apart and through shared memory above;
+		// a value takes its row along, so that the row's code is written straight from the sorted position
+		uint32_t *xi = (uint32_t *) (rank + p2);             // [p2] the rows, exchanged beside the values
+		uint32_t v = tid < m ? d[tid] : 0xffffffffu, row = tid;
+		for (uint32_t k = 2; k <= p2; k <<= 1)
+			for (uint32_t j = k >> 1; j > 0; j >>= 1)
+			{
+				uint32_t ov, orow;
+				if (j >= 32)
+				{
+					__syncthreads();                                // the exchange before this one has been read
+					buf[tid] = v; xi[tid] = row;
+					__syncthreads();
+					ov = buf[tid ^ j]; orow = xi[tid ^ j];
+				}
+				else
+				{
+					ov = __shfl_xor_sync(FSQ_FULL, v, j);
+					orow = __shfl_xor_sync(FSQ_FULL, row, j);
+				}
+				bool const keep_min = (0 == (tid & j)) == (0 == (tid & k));
+				// (equal values: both sides keep their own, so no row is lost or doubled)
+				if (keep_min ? ov < v : ov > v) { v = ov; row = orow; }
+			}
+		__syncthreads();
+		buf[tid] = v;
+		__syncthreads();
+		bool const head = tid < m && (0 == tid || buf[tid - 1] != v);
+		uint32_t total;
+		uint32_t const pos = block_excl_scan(head ? 1u : 0u, scratch, total);      // distinct values before this position
+		if (head) oldvals[(size_t) b * m + pos] = v;
+		if (tid < m) code[(size_t) b * m + row] = (uint16_t) (pos + (head ? 1u : 0u) - 1u);
+		if (0 == tid) R[b] = total;
+		return;
+	}
 	for (uint32_t i = tid; i < p2; i += blockDim.x) buf[i] = i < m ? d[i] : 0xffffffffu;
 	__syncthreads();
 	for (uint32_t k = 2; k <= p2; k <<= 1)
@@ -236,7 +273,7 @@ cudaError_t launch_prep(uint32_t const *st_d, uint32_t m, uint16_t *code, uint32
 {
 	uint32_t p2 = 32;
 	while (p2 < m) p2 <<= 1;
-	size_t const smem = (size_t) p2 * 6;
+	size_t const smem = (size_t) p2 * 6 + (p2 <= 1024 ? (size_t) p2 * 4 : 0);
 	cudaError_t err = cudaFuncSetAttribute(prep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
 	if (cudaSuccess != err) return err;
 	uint32_t const threads = p2 < 1024 ? p2 : 1024;
@@ -427,6 +464,136 @@ __global__ void __launch_bounds__(1024) stitch_sort_kernel(stitch_args const A)
 	}
 }
 
+// ---- boundary stitch, small m: counting instead of sorting ---------------------------------------------------------
+// The order wanted is the stable partition of the incoming positions by class.  A position's place is (rows in classes
+// before its own) + (earlier positions of its class): the second term is, inside a warp, the lanes below it that
+// __match_any_sync pairs it with, and across warps a prefix over one byte per (class, warp) -- a warp holds at most 32 of
+// a class -- summed four at a time with dp4a.  A third of the sorting network's instructions and five barriers
+// instead of eleven; the divergences come from the same sparse table.
+__global__ void __launch_bounds__(1024) stitch_count_kernel(stitch_args const A)
+{
+	extern __shared__ __align__(128) uint8_t smem_raw[];
+	__shared__ uint32_t scratch[34];
+	uint32_t const tid = threadIdx.x;
+	uint32_t const lane = tid & 31u, warp = tid >> 5;
+	uint32_t const p2 = blockDim.x;                        // power of two >= m, >= 32
+	uint32_t const m = A.m;
+	uint32_t levels = 1;                                   // sparse-table levels: spans of 2^l positions, 2^(levels - 1) <= m
+	while ((2u << (levels - 1)) <= m) ++levels;
+	uint32_t *tbl = (uint32_t *) smem_raw;                 // [p2][8] words = [class][warp] bytes: positions of the class in the warp
+	uint32_t *cstart = tbl + (size_t) p2 * 8;              // [p2] rows in the classes before this one
+	uint32_t *st = cstart + p2;                            // [levels][p2] range maxima of the incoming divergences
+	uint16_t *cls = (uint16_t *) (st + (size_t) levels * p2);      // [p2] class of a row id
+	uint16_t *sa = cls + p2;                               // [p2] incoming prefix array
+	uint16_t *srt = sa + p2;                               // [p2] incoming position at every outgoing one
+
+	uint32_t const step_end = A.item_begin[blockIdx.x + 1];
+	for (uint32_t step = A.item_begin[blockIdx.x]; step < step_end; ++step)
+	{
+		stitch_item const it = A.items[step];
+		uint32_t const s_mark = it.s_mark;
+		bool const live = tid < m;
+		// every global read of the item happens before its first write (outputs may alias the summary)
+		uint32_t const dl = live ? it.delta[tid] : 0u;
+		uint32_t const pi = live ? it.pi[tid] : 0u;
+		uint32_t const a_in = live ? (it.identity_in ? tid : it.in_a[tid]) : 0u;
+		uint32_t const d_in = live ? (it.identity_in ? it.identity_d : it.in_d[tid]) : 0u;
+		bool const start = live && (0 == tid || dl > s_mark);
+
+		// class of every row: inclusive count of class starts in summary order
+		uint32_t const bal = __ballot_sync(FSQ_FULL, start);
+		if (0 == lane) scratch[warp] = __popc(bal);
+		st[tid] = d_in;
+		if (live) sa[tid] = (uint16_t) a_in;
+#pragma unroll
+		for (uint32_t i = 0; i < 8; ++i) tbl[i * p2 + tid] = 0;
+		__syncthreads();
+		{
+			uint32_t const w = lane < (p2 >> 5) ? scratch[lane] : 0u;
+			uint32_t const incl = warp_incl_sum(w);
+			uint32_t const before = __shfl_sync(FSQ_FULL, incl - w, warp);
+			uint32_t const c = before + __popc(bal & (0xffffffffu >> (31u - lane)));      // >= 1 for every live row
+			if (live) cls[pi] = (uint16_t) (c - 1);
+		}
+		__syncthreads();
+
+		// sparse table over the incoming divergences (positions past m hold 0)
+		for (uint32_t l = 1; l < levels; ++l)
+		{
+			uint32_t const half = 1u << (l - 1);
+			uint32_t const x = st[(size_t) (l - 1) * p2 + tid];
+			uint32_t const y = tid + half < p2 ? st[(size_t) (l - 1) * p2 + tid + half] : 0u;
+			st[(size_t) l * p2 + tid] = max(x, y);
+			__syncthreads();
+		}
+
+		// positions of the own class in the own warp
+		uint32_t const c = live ? (uint32_t) cls[a_in] : 0xffffu;
+		uint32_t const same = __match_any_sync(FSQ_FULL, c);
+		uint32_t const below = __popc(same & ((1u << lane) - 1u));
+		if (live && 0 == below) ((uint8_t *) tbl)[c * 32u + warp] = (uint8_t) __popc(same);
+		__syncthreads();
+		{
+			// thread q: the size of class q, then the rows before it
+			uint32_t size_q = 0;
+#pragma unroll
+			for (uint32_t i = 0; i < 8; ++i) size_q = __dp4a(tbl[tid * 8 + i], 0x01010101u, size_q);
+			uint32_t total;
+			cstart[tid] = block_excl_scan(size_q, scratch, total);
+		}
+		__syncthreads();
+		if (live)
+		{
+			uint32_t at = cstart[c] + below;
+			uint32_t const *row = tbl + c * 8;
+#pragma unroll
+			for (uint32_t i = 0; i < 8; ++i)
+			{
+				// the bytes of the warps before this one
+				uint32_t const keep = 4 * i + 4 <= warp ? 0xffffffffu : (4 * i >= warp ? 0u : (1u << (8 * (warp - 4 * i))) - 1u);
+				at = __dp4a(row[i] & keep, 0x01010101u, at);
+			}
+			srt[at] = (uint16_t) tid;
+		}
+		__syncthreads();
+
+		if (live)
+		{
+			uint32_t const i = srt[tid];
+			uint32_t od = dl;
+			if (!start)
+			{
+				uint32_t const ip = srt[tid - 1];                 // the row before in the same class: ip < i
+				uint32_t const len = i - ip;                      // max over incoming positions ip + 1 .. i
+				uint32_t const l = 31u - __clz(len);
+				od = max(st[(size_t) l * p2 + ip + 1], st[(size_t) l * p2 + i + 1 - (1u << l)]);
+			}
+			it.out_a[tid] = sa[i];
+			it.out_d[tid] = od;
+		}
+		__syncthreads();
+		__threadfence();
+	}
+}
+
+static size_t stitch_count_smem_bytes(uint32_t m, uint32_t p2)
+{
+	uint32_t levels = 1;
+	while ((2u << (levels - 1)) <= m) ++levels;
+	return (size_t) p2 * 4 * (8 + 1 + levels) + (size_t) p2 * 2 * 3;
+}
+
+static cudaError_t launch_stitch_count(stitch_args const &A, cudaStream_t st)
+{
+	uint32_t p2 = 32;
+	while (p2 < A.m) p2 <<= 1;
+	size_t const smem = stitch_count_smem_bytes(A.m, p2);
+	cudaError_t err = cudaFuncSetAttribute(stitch_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+	if (cudaSuccess != err) return err;
+	stitch_count_kernel <<<A.n_ctas, p2, smem, st>>>(A);
+	return cudaGetLastError();
+}
+
 size_t stitch_sort_smem_bytes(uint32_t m, uint32_t p2)
 {
 	uint32_t levels = 1;
@@ -464,6 +631,7 @@ static cudaError_t launch_stitch_t(stitch_args const &A, uint32_t n_warps, cudaS
 
 cudaError_t launch_stitch(stitch_args const &A, cudaStream_t st)
 {
+	if (2 == A.use_sort && A.m <= 1024) return launch_stitch_count(A, st);
 	if (A.use_sort && A.m <= 1024) return launch_stitch_sort(A, st);
 	uint32_t const n_warps = A.n_tiles < 32 ? A.n_tiles : 32;
 	uint32_t const tpw = (A.n_tiles + n_warps - 1) / n_warps;

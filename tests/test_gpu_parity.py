@@ -275,16 +275,17 @@ def test_states_invariant_under_stitch_grouping(ctx, oracle, synth, G):
     check_states(ctx, oracle, rows, 12, columns=np.arange(1, 501, 7))
 
 
-@pytest.mark.parametrize("sort,m", [(0, 130), (1, 130), (1, 33), (1, 1000), (0, 1000), (1, 1024), (1, 1025)])
+@pytest.mark.parametrize("sort,m", [(0, 130), (1, 130), (1, 33), (1, 1000), (0, 1000), (1, 1024), (1, 1025), (2, 130), (2, 33), (2, 1000), (2, 1024), (2, 1025), (2, 31)])
 def test_states_invariant_under_stitch_kernel(ctx, oracle, synth, sort, m):
-    """The boundary stitch has two formulations (one sort with a sparse table for m <= 1024, radix passes otherwise)."""
+    """The boundary stitch has three formulations (for m <= 1024 a sorting network or a count per (class, warp), both with a
+    sparse table for the divergences; radix passes otherwise)."""
     rows = synth.synth_rows(m, 420, seed=31 + m, founders=11, gaps=True, recomb_block=37, mu=0.01)
     ctx.set_option("stitch_sort", sort)
     ctx.set_option("block_columns", 30)
     try:
         check_states(ctx, oracle, rows, 12, columns=np.arange(1, 421, 11))
     finally:
-        ctx.set_option("stitch_sort", 1)
+        ctx.set_option("stitch_sort", 2)
 
 
 @pytest.mark.parametrize("chunks,max_rounds", [(1, 12), (3, 12), (0, 12), (1000, 12), (1000, 2)])
