@@ -472,13 +472,27 @@ __global__ void dp_raise_kernel(dp_args const A)
 // below that bound asks for another round.
 __global__ void dp_masks_kernel(dp_args const A)
 {
-	uint32_t const t = A.w_first + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-	if (t >= A.w_last) return;
+	// One warp per block of 64 entries, the masks of the block one after the other: the entries that are <= every later
+	// one up to t are those of t - 1 that are also <= entry t, and t itself.  (A third of the instructions of one suffix
+	// scan per entry.)
+	uint32_t const b = A.w_first / 64 + blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+	uint32_t const base = 64 * b;
+	if (base >= A.w_last) return;
 	if (A.skip_when_done && A.flags[F_DONE]) return;
-	table_global v;
-	v.Mg = A.tb_max; v.mkg = A.mk; v.levg = A.lev; v.n_blk = A.n_blk;
-	unsigned long long const msk = make_mask(v, t);
-	if (0 == lane_id()) A.mk[t] = msk;
+	uint32_t const lane = lane_id();
+	uint32_t const count = min(64u, A.w_last - base);          // entries of this block that exist
+	uint32_t const v0 = lane < count ? A.tb_max[base + lane] : 0xffffffffu;
+	uint32_t const v1 = lane + 32 < count ? A.tb_max[base + 32 + lane] : 0xffffffffu;
+	unsigned long long run = 0, m0 = 0, m1 = 0;
+	for (uint32_t t = 0; t < count; ++t)
+	{
+		uint32_t const vt = __shfl_sync(FSQ_FULL, t < 32 ? v0 : v1, t & 31u);
+		unsigned long long const le = (unsigned long long) __ballot_sync(FSQ_FULL, v0 <= vt) | ((unsigned long long) __ballot_sync(FSQ_FULL, v1 <= vt) << 32);
+		run = (run & le) | (1ull << t);
+		if (lane == (t & 31u)) { if (t < 32) m0 = run; else m1 = run; }
+	}
+	if (lane < count) A.mk[base + lane] = m0;
+	if (lane + 32 < count) A.mk[base + 32 + lane] = m1;
 }
 
 // Level p of the rmq tables for every cell whose defining block is complete.
@@ -551,8 +565,7 @@ __global__ void dp_levels_all_kernel(dp_args const A)
 cudaError_t launch_dp_rebuild(dp_args const &A, cudaStream_t st)
 {
 	if (A.w_first >= A.w_last) return cudaSuccess;
-	uint32_t const span = A.w_last - A.w_first;
-	dp_masks_kernel <<<(span + 7) / 8, 256, 0, st>>>(A);
+	dp_masks_kernel <<<((A.w_last + 63) / 64 - A.w_first / 64 + 7) / 8, 256, 0, st>>>(A);
 	uint32_t const n_complete = A.w_last / 64;
 	uint32_t const first_blk = A.w_first / 64;
 	if (first_blk < n_complete)
