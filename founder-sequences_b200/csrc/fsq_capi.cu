@@ -417,12 +417,25 @@ __global__ void gather_stored_states_kernel(
 	uint32_t const *src = states + k * stride;
 	uint32_t const *old = oldvals + (size_t) b * m;
 	uint32_t *da = dst_a + (size_t) t * m, *dd = dst_d + (size_t) t * m;
+	auto value = [&](uint32_t w) { uint32_t const code = w >> 16; return code >= r ? base + code : old[code]; };
+	if (0 == (m & 3u))
+	{
+		// four rows per thread and access (the stored rows start at multiples of 16 bytes, the outputs too when m % 4 == 0)
+		uint4 const *src4 = reinterpret_cast <uint4 const *>(src);
+		uint4 *da4 = reinterpret_cast <uint4 *>(da), *dd4 = reinterpret_cast <uint4 *>(dd);
+		for (uint32_t i = threadIdx.x; i < m / 4; i += blockDim.x)
+		{
+			uint4 const w = src4[i];
+			da4[i] = make_uint4(w.x & 0xffffu, w.y & 0xffffu, w.z & 0xffffu, w.w & 0xffffu);
+			dd4[i] = make_uint4(value(w.x), value(w.y), value(w.z), value(w.w));
+		}
+		return;
+	}
 	for (uint32_t i = threadIdx.x; i < m; i += blockDim.x)
 	{
 		uint32_t const w = src[i];
-		uint32_t const code = w >> 16;
 		da[i] = w & 0xffffu;
-		dd[i] = code >= r ? base + code : old[code];
+		dd[i] = value(w);
 	}
 }
 

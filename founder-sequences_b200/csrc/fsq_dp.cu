@@ -21,6 +21,7 @@ struct table_global
 {
 	uint32_t const *Mg; uint64_t const *mkg; uint32_t const *levg; uint32_t n_blk;
 	__device__ __forceinline__ uint32_t M(uint32_t i) const { return Mg[i]; }
+	__device__ __forceinline__ uint32_t M_front(uint32_t i) const { return Mg[i]; }
 	__device__ __forceinline__ unsigned long long mask(uint32_t i) const { return mkg[i]; }
 	__device__ __forceinline__ uint32_t lev(uint32_t p, uint32_t i) const { return levg[(size_t) p * n_blk + i]; }
 };
@@ -35,6 +36,8 @@ struct table_ring
 	uint32_t *sM; unsigned long long *smk; uint32_t *slev;      // [DP_RING], [DP_RING], [DP_SLEV][DP_RING_BLK]
 	uint32_t lo;                                                  // entries >= lo are in the ring (lo is a multiple of 64)
 	__device__ __forceinline__ uint32_t M(uint32_t i) const { return i >= lo ? sM[i & (DP_RING - 1)] : g.Mg[i]; }
+	// an entry of the 64-block the wavefront is in: always in the ring (lo trails the wavefront by DP_RING - 128 at least)
+	__device__ __forceinline__ uint32_t M_front(uint32_t i) const { return sM[i & (DP_RING - 1)]; }
 	__device__ __forceinline__ unsigned long long mask(uint32_t i) const { return i >= lo ? smk[i & (DP_RING - 1)] : g.mkg[i]; }
 	__device__ __forceinline__ uint32_t lev(uint32_t p, uint32_t i) const
 	{
@@ -82,8 +85,8 @@ __device__ __forceinline__ unsigned long long make_mask(V const &v, uint32_t t)
 {
 	uint32_t const lane = lane_id();
 	uint32_t const blk = t & ~63u, tt = t & 63u;
-	uint32_t const v0 = lane <= tt ? v.M(blk + lane) : 0xffffffffu;
-	uint32_t const v1 = lane + 32 <= tt ? v.M(blk + 32 + lane) : 0xffffffffu;
+	uint32_t const v0 = lane <= tt ? v.M_front(blk + lane) : 0xffffffffu;
+	uint32_t const v1 = lane + 32 <= tt ? v.M_front(blk + 32 + lane) : 0xffffffffu;
 	uint32_t s0 = v0, s1 = v1;          // inclusive suffix minima inside each half (shfl_down returns the own value past lane 31)
 #pragma unroll
 	for (int o = 1; o < 32; o <<= 1)
