@@ -213,7 +213,8 @@ typedef struct fsq_local_group fsq_local_group;
 int fsq_shard_columns(uint64_t n_total, int size, int rank, uint64_t *c0, uint64_t *c1);
 
 /* NCCL communicator, one rank per GPU.  Rank 0 makes the id (an ncclUniqueId) and hands it to the others by whatever
- * means the host has (MPI, torch.distributed, a file); then every rank calls fsq_comm_create, which blocks until all have.
+ * means the host has (MPI, torch.distributed, a file); then every rank calls fsq_comm_create, which blocks until all have
+ * (it ends with one small all-gather, so that NCCL makes its connections here and not inside the first run).
  * libnccl.so.2 is opened at run time; a process that has it loaded already (PyTorch) shares that copy. */
 int fsq_comm_unique_id(uint8_t id[FSQ_COMM_ID_BYTES]);
 int fsq_comm_create(fsq_ctx *ctx, const uint8_t id[FSQ_COMM_ID_BYTES], int rank, int size, fsq_comm **out);
