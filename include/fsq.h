@@ -49,7 +49,7 @@ const char *fsq_version(void);
  * small; the bound a shape (m, n, L) ended with is remembered by the context, the option is never overwritten), "keep_dp"
  * (retain the full DP table for fsq_segmentation_dp_table), "store_states" (-1 auto, 0 re-scan for the boundary
  * states, 1 keep every column's state in pass B), "dp_chunks", "dp_max_rounds", "dp_guess_rounds" (DP chaining),
- * "kernel", "chunk", "warps", "stitch_sort", "stitch_group" (kernel selection, used by the parity tests), "mem_limit"
+ * "kernel", "chunk", "warps", "stitch_sort" (kernel selection, used by the parity tests), "mem_limit"
  * (plan device memory as if this many bytes were available), "window_blocks" (scan blocks per window of top lists:
  * the exact scan and the DP then alternate over windows that share one list buffer), "halo" (rows of the ranks behind
  * it that a rank's greedy reduction starts with), "trace_window" (entries per rank exported as places where the traceback

@@ -267,12 +267,14 @@ def test_segmentation_invariant_under_block_size(ctx, oracle, synth):
     assert all(r == results[0] for r in results)
 
 
-@pytest.mark.parametrize("G", [1, 2, 3, 7, 1000])
-def test_states_invariant_under_stitch_grouping(ctx, oracle, synth, G):
-    """The three-level stitch (groups of G blocks) composes summaries associatively: any grouping gives the same states."""
-    rows = synth.synth_rows(130, 500, seed=77, founders=9, gaps=True, recomb_block=41, mu=0.01)
-    ctx.set_option("stitch_group", G)
-    check_states(ctx, oracle, rows, 12, columns=np.arange(1, 501, 7))
+@pytest.mark.parametrize("B", [1, 2, 3, 4, 5, 7, 8, 9, 16, 17, 31, 32, 33, 63])
+def test_states_for_every_shape_of_the_sweep(ctx, oracle, synth, B):
+    """The block summaries are composed by an up-sweep and a down-sweep over a binary tree of B blocks: powers of two, their
+    neighbours, and numbers with many one bits (partial nodes at every level)."""
+    n = 504
+    C = (n + B - 1) // B
+    rows = synth.synth_rows(130, n, seed=77 + B, founders=9, gaps=True, recomb_block=41, mu=0.01)
+    check_states(ctx, oracle, rows, C, columns=np.arange(1, n + 1, 7))
 
 
 @pytest.mark.parametrize("sort,m", [(0, 130), (1, 130), (1, 33), (1, 1000), (0, 1000), (1, 1024), (1, 1025), (2, 130), (2, 33), (2, 1000), (2, 1024), (2, 1025), (2, 31)])

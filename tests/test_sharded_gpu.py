@@ -202,3 +202,14 @@ def test_sharded_exchange_of_tails(fsq, oracle, synth, parts, back):
     # several rounds without the guess: every round's exchange matters
     res = run_sharded(fsq, rows, L, parts, dict(opts, dp_guess_rounds=0, dp_max_rounds=200))
     check_against_oracle(oracle, rows, L, res)
+
+
+@pytest.mark.parametrize("B", [1, 2, 3, 4, 7, 8, 11])
+def test_sharded_start_states_for_every_shape_of_the_sweep(fsq, oracle, synth, B):
+    """A rank behind the first takes the summary of its whole shard out of the up-sweep (a side chain over the complete
+    nodes of the binary decomposition of its B blocks; the root itself when B is a power of two) and seeds the down-sweep
+    with its true start state."""
+    C, L = 64, 5
+    n = 3 * B * C
+    rows = synth.synth_rows(60, n, seed=40 + B, founders=6, gaps=True, recomb_block=53, mu=0.01)
+    check_against_oracle(oracle, rows, L, run_sharded(fsq, rows, L, 3, {"block_columns": C}))
